@@ -1,0 +1,250 @@
+"""TEST INFRASTRUCTURE ONLY -- CPU oracle for the CURL curve-layer hot path.
+
+A functional restatement (torch tensor ops on CPU, fp32 or fp64) of the reference's per-pixel
+curve layer: colour chain (reference colors.py), knot curves (reference curves.py) and their
+composition (reference model.py:137-176).  Gradients come from torch.autograd over this
+restatement, which is how the reference itself differentiates the path.
+
+Who may use it: tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+legs, as the *checker* and the *timed CPU baseline* only.  Nothing under curl_b200/ imports it; the
+product path is the CUDA extension and fails loudly without it.
+
+Parity pinning: the reference ships no tests or golden vectors for this path,
+so the oracle is pinned by execution: tests/test_oracle_pins.py requires this file to be
+BIT-IDENTICAL (fp32 and fp64, forward and backward) to the patched reference loaded from
+/root/reference by oracle/ref_loader.py, and tests/golden/*.npz (generated from the reference
+itself by oracle/make_golden.py) travel to the GPU box where the reference does not exist.
+To stay bit-identical the operation ORDER of the reference is kept (both-branch * 0/1-mask
+blends, einsum contractions, in-place channel writes), even where it is wasteful -- it is also
+what makes this a fair stand-in when timed as the reference's CPU path.
+
+The reference's curve code crashes as shipped (curves.py:56/111/155 initialise the regulariser
+accumulator to None); the oracle, like oracle/ref_loader.py, starts it at 0.0.
+"""
+import torch
+
+EPS = 6.0 / 29.0  # colors.py:43,106
+
+# ---------------------------------------------------------------------------------------------
+# Frozen colour constants, in the reference's registered shapes (colors.py:8-25, 69-86, 184).
+# ---------------------------------------------------------------------------------------------
+
+def _mat(rows, dtype):
+    # reference builds [3,3] rows=input channel, then .transpose(1,0) and two unsqueeze(0)
+    return torch.tensor(rows, dtype=torch.float).transpose(1, 0).unsqueeze(0).unsqueeze(0).to(dtype)
+
+
+def constants(dtype=torch.float32):
+    """The nine frozen parameters of CURLLayer().state_dict(), keyed like the reference."""
+    white = torch.tensor([0.950456, 1.0, 1.088754], dtype=torch.float).reshape(1, 3, 1, 1).to(dtype)
+    off = torch.tensor([16.0, 0.0, 0.0], dtype=torch.float).reshape(1, 3, 1, 1).to(dtype)
+    return {
+        # colors.py:8-15
+        "rgb2lab.rgb_to_xyz": _mat([[0.412453, 0.212671, 0.019334],
+                                    [0.357580, 0.715160, 0.119193],
+                                    [0.180423, 0.072169, 0.950227]], dtype),
+        # colors.py:16-23
+        "rgb2lab.fxfyfz_to_lab": _mat([[0.0, 500.0, 0.0],
+                                       [116.0, -500.0, 200.0],
+                                       [0.0, 0.0, -200.0]], dtype),
+        "rgb2lab.xyz_to_rgb_mult": white.clone(),          # colors.py:24
+        "rgb2lab.lab_to_fxfyfz_offset": off.clone(),       # colors.py:25
+        # colors.py:69-76
+        "lab2rgb.xyz_to_rgb": _mat([[3.2404542, -0.9692660, 0.0556434],
+                                    [-1.5371385, 1.8760108, -0.2040259],
+                                    [-0.4985314, 0.0415560, 1.0572252]], dtype),
+        # colors.py:77-84
+        "lab2rgb.lab_to_fxfyfz": _mat([[1 / 116.0, 1 / 116.0, 1 / 116.0],
+                                       [1 / 500.0, 0, 0],
+                                       [0, 0, -1 / 200.0]], dtype),
+        "lab2rgb.xyz_to_rgb_mult": white.clone(),          # colors.py:85
+        "lab2rgb.lab_to_fxfyfz_offset": off.clone(),       # colors.py:86
+        "rgb2hsv.comparison_zero": torch.tensor(0.0, dtype=torch.float).to(dtype),  # colors.py:184
+    }
+
+
+_CONST_CACHE = {}
+
+
+def _c(dtype):
+    if dtype not in _CONST_CACHE:
+        _CONST_CACHE[dtype] = constants(dtype)
+    return _CONST_CACHE[dtype]
+
+
+def _mix(img, m):
+    # colors.py:40,50,104,117 -- out[b,k,y,x] = sum_c img[b,c,y,x] * m[0,0,k,c]
+    return torch.einsum('bcyx,bykc->bkyx', img, m)
+
+
+# ---------------------------------------------------------------------------------------------
+# Colour conversions
+# ---------------------------------------------------------------------------------------------
+
+def rgb2lab(img):
+    """colors.py:27-62.  sRGB -> linear -> XYZ/white -> f(t) -> Lab, normalised to about [0,1]."""
+    k = _c(img.dtype)
+    x = img.contiguous()
+    lo = (x / 12.92) * x.le(0.04045).float()                                       # colors.py:37
+    hi = (((torch.clamp(x, min=0.0001) + 0.055) / 1.055) ** 2.4) * x.gt(0.04045).float()  # :37-38
+    x = lo + hi
+    x = _mix(x, k["rgb2lab.rgb_to_xyz"])                                           # colors.py:40
+    x = torch.mul(x, 1 / k["rgb2lab.xyz_to_rgb_mult"])                             # colors.py:41
+    lin = (x / (3.0 * EPS ** 2) + 4.0 / 29.0) * x.le(EPS ** 3).float()             # colors.py:45
+    cub = torch.clamp(x, min=0.0001) ** (1.0 / 3.0) * x.gt(EPS ** 3).float()       # colors.py:46-47
+    x = lin + cub
+    x = _mix(x, k["rgb2lab.fxfyfz_to_lab"]) - k["rgb2lab.lab_to_fxfyfz_offset"]    # colors.py:50
+    x[:, 0, :, :] = x[:, 0, :, :] / 100                                            # colors.py:57
+    x[:, 1, :, :] = (x[:, 1, :, :] / 110 + 1) / 2                                  # colors.py:58
+    x[:, 2, :, :] = (x[:, 2, :, :] / 110 + 1) / 2                                  # colors.py:59
+    return x.contiguous()
+
+
+def lab2rgb(img):
+    """colors.py:88-123.  Inverse of rgb2lab; no clamp on the output."""
+    k = _c(img.dtype)
+    x = img.contiguous()
+    c0 = torch.unsqueeze(x[:, 0, :, :] * 100, dim=1)                               # colors.py:97
+    c1 = torch.unsqueeze(((x[:, 1, :, :] * 2) - 1) * 110, dim=1)                   # colors.py:98
+    c2 = torch.unsqueeze(((x[:, 2, :, :] * 2) - 1) * 110, dim=1)                   # colors.py:99
+    x = torch.cat([c0, c1, c2], dim=1)
+    x = _mix(x + k["lab2rgb.lab_to_fxfyfz_offset"], k["lab2rgb.lab_to_fxfyfz"])    # colors.py:104-106
+    lin = (3.0 * EPS ** 2 * (x - 4.0 / 29.0)) * x.le(EPS).float()                  # colors.py:110
+    cub = (torch.clamp(x, min=0.0001) ** 3.0) * x.gt(EPS).float()                  # colors.py:111
+    x = lin + cub
+    x = torch.mul(x, k["lab2rgb.xyz_to_rgb_mult"])                                 # colors.py:114
+    x = _mix(x, k["lab2rgb.xyz_to_rgb"])                                           # colors.py:117
+    lo = x * 12.92 * x.le(0.0031308).float()                                       # colors.py:118
+    hi = ((torch.clamp(x, min=0.0001) ** (1 / 2.4) * 1.055) - 0.055) * x.gt(0.0031308).float()  # :118-119
+    return (lo + hi).contiguous()
+
+
+def _inv_or_zero(t):
+    # colors.py:186-193 -- 1/t where t != 0, else 0 (0*t keeps dtype/device, carries zero gradient)
+    out = 0.0 * t
+    nz = t != 0
+    out[nz] = 1 / (t[nz])
+    return out
+
+
+def rgb2hsv(img):
+    """colors.py:195-242.  Note the ADDITIVE hue selectors (ties add), colors.py:221-224."""
+    k = _c(img.dtype)
+    x = torch.clamp(img, 10 ** (-9), 1.0).contiguous()                              # colors.py:205-208
+    mx = torch.max(x, 1)[0]                                                        # colors.py:211
+    mn = torch.min(x, 1)[0]                                                        # colors.py:212
+    df = torch.add(mx, -1.0 * mn)                                                  # colors.py:214
+    r, g, b = x[:, 0, :, :], x[:, 1, :, :], x[:, 2, :, :]                          # colors.py:217
+    dinv = _inv_or_zero(df)                                                        # colors.py:220
+    x[:, 0, :, :] = torch.where(df == 0.0, k["rgb2hsv.comparison_zero"],
+                                ((g - b) * dinv) * r.eq(mx).float()
+                                + (2.0 + (b - r) * dinv) * g.eq(mx).float()
+                                + (4.0 + (r - g) * dinv) * b.eq(mx).float())      # colors.py:221-224
+    x[:, 0, :, :] = x[:, 0, :, :] * 60.0                                           # colors.py:225
+    x[:, 0, :, :] = x[:, 0, :, :].lt(0.0).float() * (x[:, 0, :, :] + 360) \
+        + x[:, 0, :, :].ge(0.0).float() * (x[:, 0, :, :])                          # colors.py:228-229
+    x[:, 0, :, :] = x[:, 0, :, :] / 360                                            # colors.py:231
+    minv = _inv_or_zero(mx)                                                        # colors.py:234
+    x[:, 1, :, :] = torch.where(mx == 0.0, k["rgb2hsv.comparison_zero"],
+                                mx.ne(0.0).float() * (df * minv) + mx.eq(0.0).float() * (0.0))  # :235-237
+    x[:, 2, :, :] = mx                                                             # colors.py:238
+    return torch.clamp(x, 10 ** (-9), 1.0)                                         # colors.py:240
+
+
+def hsv2rgb(img):
+    """colors.py:131-177.  Clamped-ramp HSV -> RGB; terms the reference multiplies by a literal 0
+    (m1/m3/m5 = 0) are kept so that the float result is the same expression tree."""
+    x = torch.clamp(img, 0.0, 1.0)                                                 # colors.py:141
+    h, s, v = x[:, 0, :, :], x[:, 1, :, :], x[:, 2, :, :]
+
+    def ramp(start, width):
+        return torch.clamp(h * 360 - start, 0.0, width)
+
+    m2 = (v * (1 - s) - v) / 60                                                    # colors.py:144
+    m4 = -1 * m2                                                                   # colors.py:146
+    r = v + ramp(0, 60.0) * 0 + ramp(60, 60.0) * m2 + ramp(120, 120.0) * 0 \
+        + ramp(240, 60.0) * m4 + ramp(300, 60.0) * 0                               # colors.py:149-150
+    m1 = (v - v * (1 - s)) / 60                                                    # colors.py:153
+    m3 = -1 * m1                                                                   # colors.py:155
+    g = v * (1 - s) + ramp(0, 60.0) * m1 + ramp(60, 120.0) * 0 + ramp(180, 60.0) * m3 \
+        + ramp(240, 120.0) * 0                                                     # colors.py:158-159
+    n2 = (v - v * (1 - s)) / 60                                                    # colors.py:163
+    n4 = -1 * n2                                                                   # colors.py:165
+    b = v * (1 - s) + ramp(0, 120.0) * 0 + ramp(120, 60.0) * n2 + ramp(180, 120.0) * 0 \
+        + ramp(300, 60.0) * n4                                                     # colors.py:167-168
+    out = torch.stack((r, g, b), 1).contiguous()                                   # colors.py:171-174
+    return torch.clamp(out, 0.0, 1.0)                                              # colors.py:175
+
+
+# ---------------------------------------------------------------------------------------------
+# Knot curves
+# ---------------------------------------------------------------------------------------------
+
+def apply_curve(img, C, reg, channel_in, channel_out):
+    """curves.py:4-38.  NB: no per-segment clamp -- the scale is affine in the pixel."""
+    steps_n = C.shape[1] - 1                                                       # curves.py:14
+    slope = C[:, 1:] - C[:, 0:-1]                                                  # curves.py:19
+    reg = reg + ((slope[:, 1:] - slope[:, 0:-1]) ** 2).sum(1)                      # curves.py:24
+    idx = torch.arange(0, slope.shape[1] - 1, device=img.device)                   # curves.py:29
+    chan = torch.unsqueeze(img[:, channel_in, :, :], 1)                            # curves.py:30
+    scale = C[:, 0].reshape(-1, 1, 1) + (
+        slope[:, :-1].reshape(slope.shape[0], slope.shape[1] - 1, 1, 1)
+        * (steps_n * chan - idx.reshape(1, idx.shape[0], 1, 1))).sum(1)           # curves.py:31-32
+    out = img.clone()                                                              # curves.py:34
+    out[:, channel_out, :, :] = img[:, channel_out, :, :] * scale                  # curves.py:35
+    return torch.clamp(out, 0.0, 1.0), reg                                         # curves.py:36-38
+
+
+def _adjust(img, P, wiring):
+    img = img.contiguous()
+    knots = [torch.exp(p) for p in torch.chunk(P, len(wiring), dim=1)]             # curves.py:53-54 etc.
+    reg = 0.0
+    for C, (cin, cout) in zip(knots, wiring):
+        img, reg = apply_curve(img, C, reg, cin, cout)
+    return img.clone().contiguous(), reg
+
+
+def adjust_lab(img, L):
+    """curves.py:136-180: three curves, channel c -> c."""
+    return _adjust(img, L, ((0, 0), (1, 1), (2, 2)))
+
+
+def adjust_rgb(img, R):
+    """curves.py:90-133: three curves, channel c -> c."""
+    return _adjust(img, R, ((0, 0), (1, 1), (2, 2)))
+
+
+def adjust_hsv(img, S):
+    """curves.py:41-87: hue<-f(hue), sat<-f(adjusted hue), sat<-f(sat), val<-f(val)."""
+    return _adjust(img, S, ((0, 0), (0, 1), (1, 1), (2, 2)))
+
+
+# ---------------------------------------------------------------------------------------------
+# The layer (model.py:137-176 without the three dead `feat` lines)
+# ---------------------------------------------------------------------------------------------
+
+def curl_layer(img, mask, L, R, H, num_lab_points=48, num_rgb_points=48, num_hsv_points=64):
+    lab = rgb2lab(img)                                                             # model.py:151
+    lab, reg_lab = adjust_lab(lab, L[:, :num_lab_points])                          # model.py:153
+    lab = lab * mask                                                               # model.py:154
+    rgb = lab2rgb(lab)                                                             # model.py:157
+    rgb, reg_rgb = adjust_rgb(rgb, R[:, :num_rgb_points])                          # model.py:159
+    rgb = rgb * mask                                                               # model.py:160
+    hsv = rgb2hsv(rgb)                                                             # model.py:163
+    hsv, reg_hsv = adjust_hsv(hsv, H[:, :num_hsv_points])                          # model.py:165
+    hsv = hsv * mask                                                               # model.py:166
+    res = hsv2rgb(hsv)                                                             # model.py:169
+    out = torch.clamp(img + res, 0.0, 1.0) * mask                                  # model.py:170
+    return out, (reg_rgb + reg_lab + reg_hsv)                                      # model.py:172-176
+
+
+def curl_layer_fwd_bwd(img, mask, L, R, H, gout, greg, **kw):
+    """Forward + autograd backward; returns dict of detached tensors."""
+    img = img.detach().clone().requires_grad_(True)
+    L = L.detach().clone().requires_grad_(True)
+    R = R.detach().clone().requires_grad_(True)
+    H = H.detach().clone().requires_grad_(True)
+    out, reg = curl_layer(img, mask, L, R, H, **kw)
+    loss = (out * gout).sum() + (reg * greg).sum()
+    gimg, gL, gR, gH = torch.autograd.grad(loss, (img, L, R, H))
+    return {"out": out.detach(), "reg": reg.detach(), "gimg": gimg, "gL": gL, "gR": gR, "gH": gH}

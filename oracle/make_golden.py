@@ -1,0 +1,151 @@
+"""TEST INFRASTRUCTURE ONLY -- generates tests/golden/*.npz from the REAL reference.
+
+Run in the build container (needs /root/reference):   python -m oracle.make_golden
+
+Every fixture is produced by executing the reference's own code (oracle/ref_loader.py: colors.py
+unmodified, curves.py / model.py::CURLLayer with the documented minimal patch) on CPU in fp32 and,
+on the same fp32 inputs, in fp64.  Inputs are seeded and stored in the file, so the fixtures
+regenerate bit-identically on the same torch build.  The GPU box has no reference tree; it checks
+the CUDA path (and the oracle) against these files.
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(HERE))
+from oracle import ref_loader  # noqa: E402
+
+GOLDEN_DIR = os.path.join(os.path.dirname(HERE), "tests", "golden")
+
+
+def _edge_image():
+    """1x3xHxW image made of every RGB triple from a list of branch-threshold / tie values."""
+    vals = [0.0, 1e-9, 0.0031308, 0.04045, 0.2, 0.5, 0.5000001, 1.0]
+    trip = torch.tensor([[a, b, c] for a in vals for b in vals for c in vals], dtype=torch.float32)  # 512 px
+    return trip.t().reshape(1, 3, 16, 32).contiguous()
+
+
+def layer_cases():
+    g = torch.Generator().manual_seed(20261104)
+    cases = {}
+
+    def knots(B, nl, nr, nh, sigma):
+        return (sigma * torch.randn(B, nl, generator=g), sigma * torch.randn(B, nr, generator=g),
+                sigma * torch.randn(B, nh, generator=g))
+
+    B, H, W = 2, 12, 16
+    img = torch.rand(B, 3, H, W, generator=g)
+    mask = torch.rand(B, 1, H, W, generator=g) > 0.1
+    cases["smooth"] = dict(img=img, mask=mask, knots=knots(B, 48, 48, 64, 0.1), pts=(48, 48, 64))
+
+    img = (torch.rand(B, 3, H, W, generator=g) * 255).round() / 255
+    mask = torch.rand(B, 1, H, W, generator=g) > 0.1
+    cases["uint8"] = dict(img=img, mask=mask, knots=knots(B, 48, 48, 64, 0.1), pts=(48, 48, 64))
+
+    img = _edge_image()
+    cases["edges"] = dict(img=img, mask=torch.ones(1, 1, 16, 32, dtype=torch.bool),
+                          knots=knots(1, 48, 48, 64, 0.1), pts=(48, 48, 64))
+
+    # identity curves (all knots 0 -> C == 1 -> scale == 1): exercises saturation/tie paths cleanly
+    cases["identity"] = dict(img=_edge_image(), mask=torch.ones(1, 1, 16, 32, dtype=torch.bool),
+                             knots=(torch.zeros(1, 48), torch.zeros(1, 48), torch.zeros(1, 64)),
+                             pts=(48, 48, 64))
+
+    # strong curves: heavy clamping everywhere
+    img = torch.rand(B, 3, H, W, generator=g)
+    mask = torch.rand(B, 1, H, W, generator=g) > 0.1
+    cases["strong"] = dict(img=img, mask=mask, knots=knots(B, 48, 48, 64, 0.5), pts=(48, 48, 64))
+
+    # non-default knot counts, and knot tensors wider than num_*_points (model.py:153,159,165 slices)
+    img = torch.rand(3, 3, 5, 7, generator=g)  # H*W = 35: odd, exercises the unaligned tail
+    mask = torch.rand(3, 1, 5, 7, generator=g) > 0.2
+    cases["widek"] = dict(img=img, mask=mask, knots=knots(3, 40, 33, 50, 0.1), pts=(30, 18, 40))
+
+    # float mask with fractional values (infer.py:41 passes a float mask)
+    img = torch.rand(B, 3, H, W, generator=g)
+    fmask = torch.rand(B, 1, H, W, generator=g)
+    fmask = torch.where(fmask < 0.2, torch.zeros_like(fmask), torch.where(fmask > 0.6, torch.ones_like(fmask), fmask))
+    cases["floatmask"] = dict(img=img, mask=fmask, knots=knots(B, 48, 48, 64, 0.1), pts=(48, 48, 64))
+
+    for c in cases.values():
+        Bc = c["img"].shape[0]
+        c["gout"] = torch.randn(c["img"].shape, generator=g)
+        c["greg"] = torch.rand(Bc, generator=g) + 0.5
+    return cases
+
+
+def run_layer(CURLLayer, case, dtype):
+    nl, nr, nh = case["pts"]
+    layer = CURLLayer(nl, nr, nh).to(dtype)
+    img = case["img"].to(dtype).clone().requires_grad_(True)
+    L, R, Hk = (k.to(dtype).clone().requires_grad_(True) for k in case["knots"])
+    mask = case["mask"] if case["mask"].dtype == torch.bool else case["mask"].to(dtype)
+    out, reg = layer(img, mask, L, R, Hk)
+    loss = (out * case["gout"].to(dtype)).sum() + (reg * case["greg"].to(dtype)).sum()
+    gimg, gL, gR, gH = torch.autograd.grad(loss, (img, L, R, Hk))
+    return dict(out=out.detach(), reg=reg.detach(), gimg=gimg, gL=gL, gR=gR, gH=gH)
+
+
+def stage_cases():
+    g = torch.Generator().manual_seed(4242)
+    x = torch.rand(2, 3, 9, 11, generator=g) * 1.3 - 0.15      # out-of-range values on purpose
+    e = _edge_image()
+    return {"wide": x, "edges": e, "unit": torch.rand(2, 3, 9, 11, generator=g)}
+
+
+def main():
+    os.makedirs(GOLDEN_DIR, exist_ok=True)
+    colors, curves, CURLLayer = ref_loader.load()
+
+    blob = {}
+    for name, case in layer_cases().items():
+        blob[f"{name}.img"] = case["img"].numpy()
+        blob[f"{name}.mask"] = case["mask"].numpy()
+        for k, t in zip("LRH", case["knots"]):
+            blob[f"{name}.{k}"] = t.numpy()
+        blob[f"{name}.pts"] = np.array(case["pts"], dtype=np.int64)
+        blob[f"{name}.gout"] = case["gout"].numpy()
+        blob[f"{name}.greg"] = case["greg"].numpy()
+        for tag, dtype in (("f32", torch.float32), ("f64", torch.float64)):
+            res = run_layer(CURLLayer, case, dtype)
+            for k, t in res.items():
+                blob[f"{name}.{tag}.{k}"] = t.numpy()
+    np.savez_compressed(os.path.join(GOLDEN_DIR, "layer.npz"), **blob)
+
+    blob = {}
+    mods = {"rgb2lab": colors.RGB2LAB, "lab2rgb": colors.LAB2RGB, "rgb2hsv": colors.RGB2HSV, "hsv2rgb": colors.HSV2RGB}
+    g = torch.Generator().manual_seed(777)
+    for cname, x in stage_cases().items():
+        blob[f"{cname}.x"] = x.numpy()
+        gy = torch.randn(x.shape, generator=g)
+        blob[f"{cname}.gy"] = gy.numpy()
+        for mname, M in mods.items():
+            for tag, dtype in (("f32", torch.float32), ("f64", torch.float64)):
+                xi = x.to(dtype).clone().requires_grad_(True)
+                y = M().to(dtype)(xi * 1.0)       # *1.0: the modules write in place into their input
+                (gx,) = torch.autograd.grad((y * gy.to(dtype)).sum(), xi)
+                blob[f"{cname}.{mname}.{tag}.y"] = y.detach().numpy()
+                blob[f"{cname}.{mname}.{tag}.gx"] = gx.numpy()
+        for aname, fn, width in (("adjust_lab", curves.adjust_lab, 48), ("adjust_rgb", curves.adjust_rgb, 48),
+                                 ("adjust_hsv", curves.adjust_hsv, 64)):
+            P = 0.2 * torch.randn(x.shape[0], width, generator=g)
+            blob[f"{cname}.{aname}.P"] = P.numpy()
+            for tag, dtype in (("f32", torch.float32), ("f64", torch.float64)):
+                xi = x.to(dtype).clone().requires_grad_(True)
+                Pi = P.to(dtype).clone().requires_grad_(True)
+                y, reg = fn(xi, Pi)
+                gx, gP = torch.autograd.grad((y * gy.to(dtype)).sum() + reg.sum(), (xi, Pi))
+                blob[f"{cname}.{aname}.{tag}.y"] = y.detach().numpy()
+                blob[f"{cname}.{aname}.{tag}.reg"] = reg.detach().numpy()
+                blob[f"{cname}.{aname}.{tag}.gx"] = gx.numpy()
+                blob[f"{cname}.{aname}.{tag}.gP"] = gP.numpy()
+    np.savez_compressed(os.path.join(GOLDEN_DIR, "stages.npz"), **blob)
+    for f in ("layer.npz", "stages.npz"):
+        print(f, os.path.getsize(os.path.join(GOLDEN_DIR, f)), "bytes")
+
+
+if __name__ == "__main__":
+    main()

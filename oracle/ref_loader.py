@@ -1,0 +1,61 @@
+"""TEST INFRASTRUCTURE ONLY -- loads the *real* reference curve layer for pinning the oracle.
+
+Only usable where /root/reference exists (the build container; never the GPU box).  Nothing from
+the reference is copied into this repo: the three source files are read where they lie and patched
+in memory, exactly as SURVEY.md section 8(c) documents:
+
+  * colors.py            -- imported unmodified.
+  * curves.py            -- the three `slope_sqr_diff = None` initialisers (curves.py:56,111,155)
+                            make `apply_curve` raise TypeError at curves.py:24; they are replaced by
+                            `slope_sqr_diff = 0.0` (0.0 += Tensor[B] yields the [B] tensor).
+  * model.py::CURLLayer  -- model.py:121-176 is extracted with `ast`; the three dead
+                            `torch.cat((feat, ...))` lines (model.py:152,158,164; `feat` is
+                            undefined, results unused) are dropped.  model.py itself cannot be
+                            imported (matplotlib/timm absent).
+
+Used by oracle/make_golden.py (to generate tests/golden/*.npz) and by tests/test_oracle_pins.py
+(to prove oracle/curl_oracle.py is bit-identical to the reference on CPU).
+"""
+import ast
+import importlib.util
+import os
+import sys
+import types
+
+REFERENCE_ROOT = os.environ.get("CURL_REFERENCE_ROOT", "/root/reference")
+
+
+def available() -> bool:
+    return os.path.isfile(os.path.join(REFERENCE_ROOT, "curves.py"))
+
+
+def load():
+    """Returns (colors_module, curves_module_patched, CURLLayer_class_patched)."""
+    import torch
+    import torch.nn as nn
+
+    if not available():
+        raise RuntimeError("reference tree not present at %s" % REFERENCE_ROOT)
+
+    spec = importlib.util.spec_from_file_location("_ref_colors", os.path.join(REFERENCE_ROOT, "colors.py"))
+    colors = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(colors)
+
+    with open(os.path.join(REFERENCE_ROOT, "curves.py")) as f:
+        src = f.read()
+    assert src.count("slope_sqr_diff = None") == 3, "reference curves.py changed; re-derive the patch"
+    src = src.replace("slope_sqr_diff = None", "slope_sqr_diff = 0.0")
+    curves = types.ModuleType("_ref_curves")
+    exec(compile(src, os.path.join(REFERENCE_ROOT, "curves.py"), "exec"), curves.__dict__)
+
+    with open(os.path.join(REFERENCE_ROOT, "model.py")) as f:
+        msrc = f.read()
+    tree = ast.parse(msrc)
+    cls = [n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == "CURLLayer"]
+    assert len(cls) == 1
+    lines = msrc.splitlines()[cls[0].lineno - 1: cls[0].end_lineno]
+    kept = [ln for ln in lines if "torch.cat((feat" not in ln]
+    assert len(lines) - len(kept) == 3, "reference model.py changed; re-derive the patch"
+    ns = {"torch": torch, "nn": nn, "colors": colors, "curves": curves}
+    exec(compile("\n".join(kept), os.path.join(REFERENCE_ROOT, "model.py"), "exec"), ns)
+    return colors, curves, ns["CURLLayer"]
