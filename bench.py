@@ -1,0 +1,345 @@
+#!/usr/bin/env python
+"""Benchmark of the curve-layer hot path (BASELINE.json metric: curve-layer fwd+bwd Mpixels/s).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+Workload (config.workload): BASELINE.json configs[3] -- synthetic 4K (3840x2160) RGB fp32, batch 64
+per GPU, one step = one fused forward + one fused backward (with image gradient) of the layer over
+the whole batch = 530.8 Mpx.  At N > 1 (torchrun) every rank runs the same per-GPU batch on its own
+GPU (batch sharding, no collective on the data path): weak scaling, value = N * units / max-rank time.
+
+Printed JSON (rank 0, one line):
+  value     Mpx/s with inputs resident in HBM, CUDA-event timed, max over ranks
+  e2e       the same step driven from pinned HOST buffers through the public module API: per step the
+            image + mask are copied host->device, forward+backward run, and the regulariser and knot
+            gradients are read back device->host
+  roofline  the dominant kernel (fused backward, 37 algorithmic B/px) against the measured HBM peak
+  cpu_baseline  the CPU oracle (the reference's ATen op sequence, restated; kind "port") on this
+            box's host cores over a bounded sample of the same workload
+`--impl reference` times only that CPU path (the reference has no native code and /root/reference
+does not travel to the GPU box, so the timed code is oracle/curl_oracle.py, bit-identical to it).
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+METRIC = "curve_layer_fwd_bwd_mpixels_per_s"
+UNIT = "Mpx/s"
+H4K, W4K = 2160, 3840
+FWD_BYTES_PER_PX = 25      # 12 img + 12 out + 1 bool mask            
+BWD_BYTES_PER_PX = 37      # 12 img + 12 gout + 12 gimg + 1 bool mask
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons of one GPU while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.proc = None
+            return
+        self.thread = threading.Thread(target=self._pump, daemon=True)
+        self.thread.start()
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, pw, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        rows = [r for (t, r) in self.rows if t0 - 0.05 <= t <= t1 + 0.15] or [r for (_, r) in self.rows]
+        for r in rows:
+            f = [x.strip() for x in r.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1])); pw.append(float(f[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def make_inputs(B, H, W, dev, seed):
+    g = torch.Generator(device=dev).manual_seed(seed)
+    img = torch.rand(B, 3, H, W, generator=g, device=dev)
+    mask = torch.rand(B, 1, H, W, generator=g, device=dev) > 0.1
+    L = 0.1 * torch.randn(B, 48, generator=g, device=dev)
+    R = 0.1 * torch.randn(B, 48, generator=g, device=dev)
+    Hk = 0.1 * torch.randn(B, 64, generator=g, device=dev)
+    return img, mask, L, R, Hk
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the oracle (reference op sequence) on the host cores, bounded sample
+# ------------------------------------------------------------------------------------------------
+def cpu_reference_step(sample):
+    from oracle import curl_oracle as O
+    img, mask, L, R, Hk, gout, greg = sample
+    return O.curl_layer_fwd_bwd(img, mask, L, R, Hk, gout, greg)
+
+
+def cpu_sample(h=1080, w=1920):
+    g = torch.Generator().manual_seed(1234)
+    img = torch.rand(1, 3, h, w, generator=g)
+    mask = torch.rand(1, 1, h, w, generator=g) > 0.1
+    L, R, Hk = (0.1 * torch.randn(1, n, generator=g) for n in (48, 48, 64))
+    gout = torch.randn(1, 3, h, w, generator=g)
+    return img, mask, L, R, Hk, gout, torch.ones(1)
+
+
+def time_cpu(steps, warmup, h=1080, w=1920):
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    sample = cpu_sample(h, w)
+    for _ in range(warmup):
+        cpu_reference_step(sample)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        cpu_reference_step(sample)
+    dt = (time.perf_counter() - t0) / steps
+    mpx = h * w / 1e6
+    return {"value": mpx / dt, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": "one %dx%d tile of a 4K image, batch 1, fwd+bwd with image gradient, fp32 (%.2f Mpx/step, "
+                      "%d steps, %.2f s/step); oracle/curl_oracle.py = the reference's ATen op sequence "
+                      "(bit-identical to the patched reference on CPU)" % (h, w, mpx, steps, dt)}, dt
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    steps = max(1, min(args.steps, 5))
+    warmup = max(1, min(args.warmup, 1))
+    base, dt = time_cpu(steps, warmup)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": base["value"], "unit": UNIT, "n_gpus": args.gpus,
+        "steps": steps, "warmup": warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "note": "CPU arm runs a bounded sample of the workload (see cpu_baseline.sample)"},
+        "cpu_baseline": base,
+        "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+WORKLOAD = "4K (3840x2160) synthetic RGB fp32, batch 64 per GPU, curve-layer fwd+bwd (BASELINE.json configs[3])"
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch.distributed as dist
+    import curl_b200
+    from curl_b200 import _lib
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the curve layer has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    _lib.load()
+
+    B, H, W = args.batch, args.height, args.width
+    n_px = B * H * W
+    layer = curl_b200.CURLLayer().to(dev)
+    img, mask, L, R, Hk = make_inputs(B, H, W, dev, 1234 + rank)
+    img.requires_grad_(True)
+    L.requires_grad_(True); R.requires_grad_(True); Hk.requires_grad_(True)
+    gout = torch.randn(B, 3, H, W, device=dev, generator=torch.Generator(device=dev).manual_seed(99 + rank))
+    greg = torch.ones(B, device=dev)
+
+    def step():
+        for t in (img, L, R, Hk):
+            t.grad = None
+        out, reg = layer(img, mask, L, R, Hk)
+        torch.autograd.backward([out, reg], [gout, greg])
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+
+    # ---- timed region: resident inputs, CUDA events on the launching (current) stream -------------
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
+    sampler = ClockSampler(local)
+    sampler.start()
+    time.sleep(0.25)
+    launches0 = _lib.launches
+    barrier()
+    t_wall0 = time.time()
+    start = torch.cuda.Event(enable_timing=True); end = torch.cuda.Event(enable_timing=True)
+    start.record()
+    for k in range(args.steps):
+        for t in (img, L, R, Hk):
+            t.grad = None
+        ev[k][0].record()
+        out, reg = layer(img, mask, L, R, Hk)
+        ev[k][1].record()
+        torch.autograd.backward([out, reg], [gout, greg])
+        ev[k][2].record()
+    end.record()
+    barrier()
+    t_wall1 = time.time()
+    launches = _lib.launches - launches0
+    clocks = sampler.stop(t_wall0, t_wall1)
+    ms_total = start.elapsed_time(end)
+    fwd_ms = statistics.mean(e[0].elapsed_time(e[1]) for e in ev)
+    bwd_ms = statistics.mean(e[1].elapsed_time(e[2]) for e in ev)
+    del out, reg
+
+    tt = torch.tensor([ms_total], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    ms_step = tt.item() / args.steps
+    value = world * n_px / 1e6 / (ms_step / 1e3)
+
+    # ---- e2e: pinned host buffers -> H2D -> fwd+bwd -> D2H of the step's results -------------------
+    for t in (img, L, R, Hk):
+        t.grad = None
+    h_img = torch.empty(img.shape, dtype=torch.float32, pin_memory=True)
+    h_mask = torch.empty(mask.shape, dtype=torch.bool, pin_memory=True)
+    h_img.copy_(img.detach()); h_mask.copy_(mask)
+    h_res = torch.empty(B * (1 + 160), dtype=torch.float32, pin_memory=True)
+    d_img = img.detach()          # reuse the resident buffers as the H2D destination
+    d_mask = mask
+    e2e_steps = max(1, min(args.steps, 5))
+
+    def e2e_step():
+        d_img.copy_(h_img, non_blocking=True)
+        d_mask.copy_(h_mask, non_blocking=True)
+        x = d_img.requires_grad_(True)
+        for t in (L, R, Hk):
+            t.grad = None
+        o, r = layer(x, d_mask, L, R, Hk)
+        torch.autograd.backward([o, r], [gout, greg])
+        res = torch.cat([r.detach().reshape(-1), L.grad.reshape(-1), R.grad.reshape(-1), Hk.grad.reshape(-1)])
+        h_res.copy_(res, non_blocking=True)
+        x.grad = None
+        d_img.requires_grad_(False)
+
+    e2e_step()
+    barrier()
+    s2 = torch.cuda.Event(enable_timing=True); e2 = torch.cuda.Event(enable_timing=True)
+    s2.record()
+    for _ in range(e2e_steps):
+        e2e_step()
+    e2.record()
+    barrier()
+    t2 = torch.tensor([s2.elapsed_time(e2)], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+    e2e_ms = t2.item() / e2e_steps
+    e2e_value = world * n_px / 1e6 / (e2e_ms / 1e3)
+    h2d = h_img.numel() * 4 + h_mask.numel()
+    d2h = h_res.numel() * 4
+
+    if rank == 0:
+        peak, peak_src = measured_peak()
+        bwd_gbs = n_px * BWD_BYTES_PER_PX / (bwd_ms / 1e3) / 1e9
+        fwd_gbs = n_px * FWD_BYTES_PER_PX / (fwd_ms / 1e3) / 1e9
+        step_gbs = n_px * (FWD_BYTES_PER_PX + BWD_BYTES_PER_PX) / ((fwd_ms + bwd_ms) / 1e3) / 1e9
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD if (B, H, W) == (64, H4K, W4K) else
+                       "synthetic RGB fp32 %dx%dx%d per GPU, curve-layer fwd+bwd" % (B, H, W),
+                       "batch_per_gpu": B, "height": H, "width": W, "mask": "bool, ~10% masked",
+                       "knots": "16 per curve, sigma 0.1", "image_gradient": True,
+                       "l2": "inputs exceed L2 (%.1f GB per tensor), no flush needed" % (n_px * 12 / 1e9),
+                       "parallelism": "batch-sharded, no collective" if world > 1 else "single GPU"},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": e2e_ms, "steps": e2e_steps},
+            "gpu_launches": launches,
+            "clocks": clocks,
+            "roofline": {"bound": "hbm", "kernel": "bwd_kernel<OpLayer> (fused recompute backward, 37 B/px)",
+                         "achieved": bwd_gbs, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
+                         "frac": bwd_gbs / peak, "frac_of_8TBps": bwd_gbs / 8000.0, "traffic": None,
+                         "ms_per_launch": bwd_ms},
+            "roofline_fwd": {"kernel": "fwd_kernel<OpLayer> (fused forward, 25 B/px)", "achieved": fwd_gbs,
+                             "frac": fwd_gbs / peak, "ms_per_launch": fwd_ms},
+            "roofline_step": {"bytes_per_px": FWD_BYTES_PER_PX + BWD_BYTES_PER_PX, "achieved": step_gbs,
+                              "frac": step_gbs / peak, "frac_of_8TBps": step_gbs / 8000.0},
+        }
+        if world == 1 and not args.no_cpu:
+            base, _ = time_cpu(3, 1)
+            line["cpu_baseline"] = base
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=64)
+    ap.add_argument("--height", type=int, default=H4K)
+    ap.add_argument("--width", type=int, default=W4K)
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,611 @@
+// sm_100a kernels + C ABI of the CURL curve layer (see include/curl_b200.h for the contract).
+//
+// One generic forward kernel and one generic recompute-backward kernel, instantiated per "op":
+// the fused layer (reference model.py:137-176), the four colour conversions (colors.py) and the
+// three curve groups (curves.py).  Data layout: planar NCHW fp32; one block never straddles images
+// (blockIdx.y = image), so the per-image curve coefficients live in shared memory.  The path is
+// elementwise: each pixel is read once and written once with 128-bit accesses, and nothing else
+// touches HBM (no Lab/HSV intermediates).
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/curl_b200.h"
+#include "curl_pixel.cuh"
+
+namespace curl {
+
+constexpr int THREADS = 256;
+constexpr int MAX_SEGS = 3;
+constexpr int MAX_CURVES = 10;
+
+struct KnotSeg {
+  const float* p;   // [B][ld] log-domain knots
+  float* g;         // [B][nc*K] dense gradient (backward only)
+  long long ld;
+  int nc, K;
+};
+
+struct KParams {
+  const float* in;     // [B][3][HW]
+  const void* mask;    // [B][HW] u8 or f32, or null
+  const float* gout;   // backward: upstream gradient [B][3][HW]
+  float* out;          // forward: result; backward: gradient w.r.t. `in` (nullable)
+  float* reg;          // forward: [B]
+  const float* greg;   // backward: [B] or null
+  float* partials;     // backward: [B][gridDim.x][2*NC]
+  unsigned* tickets;   // backward: [B], zero on entry
+  KnotSeg seg[MAX_SEGS];
+  int nseg;
+  int HW;
+  int linear_knots;    // 1: seg[].p holds C itself (apply_curve), 0: log-domain (C = exp(p))
+  int aux;             // op-specific: apply_curve packs channel_in | channel_out << 2
+};
+
+// ---------------------------------------------------------------------------------------------
+// Ops
+// ---------------------------------------------------------------------------------------------
+struct OpLayer {
+  static constexpr int NC = LAYER_CURVES;
+  template <int MK>
+  static __device__ __forceinline__ void fwd(const float x[3], float m, const float* ab, int, float y[3]) {
+    layer_fwd<DevMath, MK>(x, m, ab, y);
+  }
+  template <int MK>
+  static __device__ __forceinline__ void bwd(const float x[3], float m, const float* ab, int, const float gy[3],
+                                             float gx[3], float* mom) {
+    layer_bwd<DevMath, MK>(x, m, ab, gy, gx, mom);
+  }
+};
+
+template <int CONV>
+struct OpColor {
+  static constexpr int NC = 0;
+  template <int MK>
+  static __device__ __forceinline__ void fwd(const float x[3], float, const float*, int, float y[3]) {
+    if (CONV == CURL_RGB2LAB) rgb2lab_fwd<DevMath, false>(x, y, nullptr);
+    if (CONV == CURL_LAB2RGB) lab2rgb_fwd<DevMath, false>(x, y, nullptr);
+    if (CONV == CURL_RGB2HSV) rgb2hsv_fwd<DevMath, false, false>(x, y, nullptr);
+    if (CONV == CURL_HSV2RGB) hsv2rgb_fwd<DevMath, false, false>(x, y, nullptr);
+  }
+  template <int MK>
+  static __device__ __forceinline__ void bwd(const float x[3], float, const float*, int, const float gy[3],
+                                             float gx[3], float*) {
+    float y[3];
+    if (CONV == CURL_RGB2LAB) { LabJac j; rgb2lab_fwd<DevMath, true>(x, y, &j); rgb2lab_bwd(j, gy, gx); }
+    if (CONV == CURL_LAB2RGB) { RgbJac j; lab2rgb_fwd<DevMath, true>(x, y, &j); lab2rgb_bwd(j, gy, gx); }
+    if (CONV == CURL_RGB2HSV) { HsvJac j; rgb2hsv_fwd<DevMath, true, false>(x, y, &j); rgb2hsv_bwd(j, gy, gx); }
+    if (CONV == CURL_HSV2RGB) { Hsv2RgbJac j; hsv2rgb_fwd<DevMath, true, false>(x, y, &j); hsv2rgb_bwd(j, gy, gx); }
+  }
+};
+
+struct OpAdjustSelf3 {  // adjust_lab, adjust_rgb
+  static constexpr int NC = 3;
+  template <int MK>
+  static __device__ __forceinline__ void fwd(const float x[3], float, const float* ab, int, float y[3]) {
+    adjust_self3_fwd<DevMath, false>(x, ab, y, nullptr);
+  }
+  template <int MK>
+  static __device__ __forceinline__ void bwd(const float x[3], float, const float* ab, int, const float gy[3],
+                                             float gx[3], float* mom) {
+    float y[3]; Self3Jac j;
+    adjust_self3_fwd<DevMath, true>(x, ab, y, &j);
+    adjust_self3_bwd(j, gy, gx, mom);
+  }
+};
+
+struct OpAdjustHsv {
+  static constexpr int NC = 4;
+  template <int MK>
+  static __device__ __forceinline__ void fwd(const float x[3], float, const float* ab, int, float y[3]) {
+    adjust_hsv_fwd<DevMath, false, false>(x, ab, y, nullptr);
+  }
+  template <int MK>
+  static __device__ __forceinline__ void bwd(const float x[3], float, const float* ab, int, const float gy[3],
+                                             float gx[3], float* mom) {
+    float y[3]; HsvCurveJac j;
+    adjust_hsv_fwd<DevMath, true, false>(x, ab, y, &j);
+    adjust_hsv_bwd(j, ab, gy, gx, mom);
+  }
+};
+
+struct OpCurve1 {  // curves.apply_curve: one curve channel_in -> channel_out, knots given as C
+  static constexpr int NC = 1;
+  template <int MK>
+  static __device__ __forceinline__ void fwd(const float x[3], float, const float* ab, int aux, float y[3]) {
+    single_curve_fwd<DevMath>(x, aux & 3, (aux >> 2) & 3, ab[0], ab[1], y);
+  }
+  template <int MK>
+  static __device__ __forceinline__ void bwd(const float x[3], float, const float* ab, int aux, const float gy[3],
+                                             float gx[3], float* mom) {
+    single_curve_bwd<DevMath>(x, aux & 3, (aux >> 2) & 3, ab[0], ab[1], gy, gx, mom);
+  }
+};
+
+// ---------------------------------------------------------------------------------------------
+// Vector access helpers (streaming: every byte is touched exactly once)
+// ---------------------------------------------------------------------------------------------
+template <int VEC> struct Px;
+template <> struct Px<4> {
+  float v[4];
+  static __device__ __forceinline__ Px ld(const float* p) {
+    const float4 t = __ldcs(reinterpret_cast<const float4*>(p));
+    Px r; r.v[0] = t.x; r.v[1] = t.y; r.v[2] = t.z; r.v[3] = t.w; return r;
+  }
+  __device__ __forceinline__ void st(float* p) const {
+    __stcs(reinterpret_cast<float4*>(p), make_float4(v[0], v[1], v[2], v[3]));
+  }
+};
+template <> struct Px<1> {
+  float v[1];
+  static __device__ __forceinline__ Px ld(const float* p) { Px r; r.v[0] = __ldcs(p); return r; }
+  __device__ __forceinline__ void st(float* p) const { __stcs(p, v[0]); }
+};
+
+template <int MK, int VEC>
+__device__ __forceinline__ void load_mask(const void* mask, size_t idx, float m[VEC]) {
+  if (MK == MASK_NONE) {
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) m[i] = 1.0f;
+  } else if (MK == MASK_U8) {
+    const unsigned char* p = reinterpret_cast<const unsigned char*>(mask) + idx;
+    if (VEC == 4) {
+      const uchar4 t = __ldcs(reinterpret_cast<const uchar4*>(p));
+      m[0] = t.x ? 1.0f : 0.0f; m[1 % VEC] = t.y ? 1.0f : 0.0f; m[2 % VEC] = t.z ? 1.0f : 0.0f; m[3 % VEC] = t.w ? 1.0f : 0.0f;
+    } else {
+      m[0] = __ldcs(p) ? 1.0f : 0.0f;
+    }
+  } else {
+    const Px<VEC> t = Px<VEC>::ld(reinterpret_cast<const float*>(mask) + idx);
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) m[i] = t.v[i];
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Block prologue: exp() the knots of image b into shared memory, derive (alpha, beta) per curve
+// (and, for the block that owns it, the regulariser).  curves.py:19-24,53-54,105-106,152-153.
+// ---------------------------------------------------------------------------------------------
+template <int NC>
+__device__ __forceinline__ void stage_curves(const KParams& p, int b, float* s_C, float* s_ab, double* s_reg,
+                                             bool want_reg) {
+  int off = 0;
+  for (int s = 0; s < p.nseg; ++s) {
+    const int n = p.seg[s].nc * p.seg[s].K;
+    const float* src = p.seg[s].p + (size_t)b * p.seg[s].ld;
+    for (int i = threadIdx.x; i < n; i += blockDim.x)
+      s_C[off + i] = p.linear_knots ? src[i] : (float)exp((double)src[i]);
+    off += n;
+  }
+  __syncthreads();
+  if (threadIdx.x < NC) {
+    int j = threadIdx.x, o = 0, K = 0;
+    for (int s = 0; s < p.nseg; ++s) {
+      K = p.seg[s].K;
+      if (j < p.seg[s].nc) { o += j * K; break; }
+      j -= p.seg[s].nc;
+      o += p.seg[s].nc * K;
+    }
+    curve_alpha_beta(s_C + o, K, &s_ab[2 * threadIdx.x], &s_ab[2 * threadIdx.x + 1]);
+    if (want_reg) s_reg[threadIdx.x] = curve_regulariser(s_C + o, K);
+  }
+  __syncthreads();
+}
+
+// ---------------------------------------------------------------------------------------------
+// Forward
+// ---------------------------------------------------------------------------------------------
+template <class Op, int MK, int VEC>
+__global__ void __launch_bounds__(THREADS) fwd_kernel(const KParams p) {
+  constexpr int NC = Op::NC;
+  __shared__ float s_C[NC > 0 ? CURL_MAX_KNOTS : 1];
+  __shared__ float s_ab[NC > 0 ? 2 * NC : 1];
+  __shared__ double s_reg[NC > 0 ? NC : 1];
+  const int b = blockIdx.y;
+  if (NC > 0) {
+    const bool owner = (blockIdx.x == 0) && (p.reg != nullptr);
+    stage_curves<NC>(p, b, s_C, s_ab, s_reg, owner);
+    if (owner && threadIdx.x == 0) {
+      double r = 0.0;
+      for (int j = 0; j < NC; ++j) r += s_reg[j];
+      p.reg[b] = (float)r;
+    }
+  }
+  const int HW = p.HW;
+  const float* in = p.in + (size_t)b * 3 * HW;
+  float* out = p.out + (size_t)b * 3 * HW;
+  const int stride = gridDim.x * THREADS * VEC;
+  for (int i = (blockIdx.x * THREADS + threadIdx.x) * VEC; i < HW; i += stride) {
+    const Px<VEC> c0 = Px<VEC>::ld(in + i), c1 = Px<VEC>::ld(in + HW + i), c2 = Px<VEC>::ld(in + 2 * (size_t)HW + i);
+    float m[VEC];
+    load_mask<MK, VEC>(p.mask, (size_t)b * HW + i, m);
+    Px<VEC> o0, o1, o2;
+#pragma unroll
+    for (int v = 0; v < VEC; ++v) {
+      const float x[3] = {c0.v[v], c1.v[v], c2.v[v]};
+      float y[3];
+      Op::template fwd<MK>(x, m[v], s_ab, p.aux, y);
+      o0.v[v] = y[0]; o1.v[v] = y[1]; o2.v[v] = y[2];
+    }
+    o0.st(out + i); o1.st(out + HW + i); o2.st(out + 2 * (size_t)HW + i);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Backward (recompute).  Knot-gradient reduction: per-thread registers -> warp shuffles -> shared
+// memory -> one partial row per block -> one atomic ticket per block -> the last block of the
+// image folds all partial rows in a fixed order (in double) and writes the knot gradients.
+// ---------------------------------------------------------------------------------------------
+template <class Op, int MK, int VEC, bool WANT_GIN>
+__global__ void __launch_bounds__(THREADS) bwd_kernel(const KParams p) {
+  constexpr int NC = Op::NC;
+  constexpr int NM = 2 * NC;
+  constexpr int NWARPS = THREADS / 32;
+  __shared__ float s_C[NC > 0 ? CURL_MAX_KNOTS : 1];
+  __shared__ float s_ab[NC > 0 ? 2 * NC : 1];
+  __shared__ double s_mom[NC > 0 ? NM : 1];
+  __shared__ float s_part[NC > 0 ? NWARPS * NM : 1];
+  __shared__ unsigned s_ticket;
+  const int b = blockIdx.y;
+  if (NC > 0) stage_curves<NC>(p, b, s_C, s_ab, nullptr, false);
+
+  float mom[NM > 0 ? NM : 1];
+#pragma unroll
+  for (int k = 0; k < NM; ++k) mom[k] = 0.0f;
+
+  const int HW = p.HW;
+  const float* in = p.in + (size_t)b * 3 * HW;
+  const float* go = p.gout + (size_t)b * 3 * HW;
+  float* gin = WANT_GIN ? p.out + (size_t)b * 3 * HW : nullptr;
+  const int stride = gridDim.x * THREADS * VEC;
+  for (int i = (blockIdx.x * THREADS + threadIdx.x) * VEC; i < HW; i += stride) {
+    const Px<VEC> c0 = Px<VEC>::ld(in + i), c1 = Px<VEC>::ld(in + HW + i), c2 = Px<VEC>::ld(in + 2 * (size_t)HW + i);
+    const Px<VEC> g0 = Px<VEC>::ld(go + i), g1 = Px<VEC>::ld(go + HW + i), g2 = Px<VEC>::ld(go + 2 * (size_t)HW + i);
+    float m[VEC];
+    load_mask<MK, VEC>(p.mask, (size_t)b * HW + i, m);
+    Px<VEC> o0, o1, o2;
+#pragma unroll
+    for (int v = 0; v < VEC; ++v) {
+      const float x[3] = {c0.v[v], c1.v[v], c2.v[v]};
+      const float gy[3] = {g0.v[v], g1.v[v], g2.v[v]};
+      float gx[3];
+      Op::template bwd<MK>(x, m[v], s_ab, p.aux, gy, gx, mom);
+      o0.v[v] = gx[0]; o1.v[v] = gx[1]; o2.v[v] = gx[2];
+    }
+    if (WANT_GIN) { o0.st(gin + i); o1.st(gin + HW + i); o2.st(gin + 2 * (size_t)HW + i); }
+  }
+
+  if (NC > 0) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < NM; ++k) {
+      float v = mom[k];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == 0) s_part[warp * NM + k] = v;
+    }
+    __syncthreads();
+    float* row = p.partials + ((size_t)b * gridDim.x + blockIdx.x) * NM;
+    if (threadIdx.x < NM) {
+      float v = 0.0f;
+#pragma unroll
+      for (int w = 0; w < NWARPS; ++w) v += s_part[w * NM + threadIdx.x];
+      row[threadIdx.x] = v;
+      __threadfence();
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) s_ticket = atomicAdd(&p.tickets[b], 1u);
+    __syncthreads();
+    if (s_ticket != gridDim.x - 1) return;
+    __threadfence();
+    // last block of image b: fixed-order fold of the partial rows
+    const float* rows = p.partials + (size_t)b * gridDim.x * NM;
+    for (int k = warp; k < NM; k += NWARPS) {
+      double acc = 0.0;
+      for (unsigned r = lane; r < gridDim.x; r += 32) acc += (double)__ldcg(rows + (size_t)r * NM + k);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+      if (lane == 0) s_mom[k] = acc;
+    }
+    __syncthreads();
+    const double greg = p.greg ? (double)p.greg[b] : 0.0;
+    int cbase = 0, off = 0;
+    for (int s = 0; s < p.nseg; ++s) {
+      const int K = p.seg[s].K, n = p.seg[s].nc * K;
+      float* g = p.seg[s].g + (size_t)b * n;
+      for (int i = threadIdx.x; i < n; i += THREADS) {
+        const int c = i / K, kk = i - c * K;
+        g[i] = curve_knot_grad(s_C + off + c * K, K, kk, s_mom[2 * (cbase + c)], s_mom[2 * (cbase + c) + 1], greg,
+                               p.linear_knots == 0);
+      }
+      cbase += p.seg[s].nc;
+      off += n;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Host side
+// ---------------------------------------------------------------------------------------------
+static int sm_count() {
+  static int cached[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (cached[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cached[dev] = n;
+  }
+  return cached[dev];
+}
+
+// Blocks along x for one image: enough tiles to cover it, capped so the whole grid is about
+// `waves` resident waves of the machine (each block then loops over its share of the image).
+static int blocks_per_image(int B, int HW, int vec, int blocks_per_sm) {
+  const long long tiles = ((long long)HW + (long long)THREADS * vec - 1) / ((long long)THREADS * vec);
+  long long cap = ((long long)sm_count() * blocks_per_sm + B - 1) / B;
+  if (cap < 1) cap = 1;
+  long long n = tiles < cap ? tiles : cap;
+  if (n < 1) n = 1;
+  return (int)n;
+}
+
+constexpr int BWD_GRID_BLOCKS_PER_SM = 8;
+constexpr int FWD_GRID_BLOCKS_PER_SM = 16;
+
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+static bool aligned4(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 3u) == 0; }
+
+static int check_launch() { return cudaGetLastError() == cudaSuccess ? CURL_OK : CURL_ERR_LAUNCH; }
+
+template <class Op, int MK>
+static int launch_fwd(const KParams& p, int B, bool vec4, cudaStream_t st) {
+  const int vec = vec4 ? 4 : 1;
+  dim3 grid(blocks_per_image(B, p.HW, vec, FWD_GRID_BLOCKS_PER_SM), B);
+  if (vec4) fwd_kernel<Op, MK, 4><<<grid, THREADS, 0, st>>>(p);
+  else fwd_kernel<Op, MK, 1><<<grid, THREADS, 0, st>>>(p);
+  return check_launch();
+}
+
+static int bwd_grid_x(int B, int HW, int vec) { return blocks_per_image(B, HW, vec, BWD_GRID_BLOCKS_PER_SM); }
+
+template <class Op, int MK>
+static int launch_bwd(KParams& p, int B, bool vec4, void* ws, size_t ws_bytes, cudaStream_t st) {
+  const int vec = vec4 ? 4 : 1;
+  dim3 grid(bwd_grid_x(B, p.HW, vec), B);
+  if (Op::NC > 0) {
+    const size_t tick_bytes = ((size_t)B * sizeof(unsigned) + 255) / 256 * 256;
+    const size_t need = tick_bytes + (size_t)B * grid.x * 2 * Op::NC * sizeof(float);
+    if (ws == nullptr || ws_bytes < need || !aligned16(ws)) return CURL_ERR_WORKSPACE;
+    p.tickets = reinterpret_cast<unsigned*>(ws);
+    p.partials = reinterpret_cast<float*>(reinterpret_cast<char*>(ws) + tick_bytes);
+    if (cudaMemsetAsync(ws, 0, tick_bytes, st) != cudaSuccess) return CURL_ERR_LAUNCH;
+  }
+  const bool want = p.out != nullptr;
+  if (vec4) {
+    if (want) bwd_kernel<Op, MK, 4, true><<<grid, THREADS, 0, st>>>(p);
+    else bwd_kernel<Op, MK, 4, false><<<grid, THREADS, 0, st>>>(p);
+  } else {
+    if (want) bwd_kernel<Op, MK, 1, true><<<grid, THREADS, 0, st>>>(p);
+    else bwd_kernel<Op, MK, 1, false><<<grid, THREADS, 0, st>>>(p);
+  }
+  return check_launch();
+}
+
+static bool can_vec4(const KParams& p, int mask_kind) {
+  if (p.HW % 4 != 0) return false;
+  if (!aligned16(p.in) || (p.out && !aligned16(p.out)) || (p.gout && !aligned16(p.gout))) return false;
+  if (mask_kind == CURL_MASK_U8 && !aligned4(p.mask)) return false;
+  if (mask_kind == CURL_MASK_F32 && !aligned16(p.mask)) return false;
+  return true;
+}
+
+static int check_shape(int B, int H, int W) {
+  if (B <= 0 || H <= 0 || W <= 0) return CURL_ERR_BAD_ARG;
+  if ((long long)H * W > 0x3fffffffLL || B > 65535) return CURL_ERR_BAD_ARG;
+  return CURL_OK;
+}
+
+}  // namespace curl
+
+using namespace curl;
+
+extern "C" {
+
+int curl_abi_version(void) { return CURL_ABI_VERSION; }
+
+const char* curl_strerror(int code) {
+  switch (code) {
+    case CURL_OK: return "success";
+    case CURL_ERR_BAD_ARG: return "bad argument (null pointer, non-positive size, K < 3 or unknown enum)";
+    case CURL_ERR_TOO_MANY_KNOTS: return "too many knots per image (CURL_MAX_KNOTS)";
+    case CURL_ERR_WORKSPACE: return "workspace missing, misaligned or too small (see curl_bwd_workspace_bytes)";
+    case CURL_ERR_LAUNCH: return "CUDA launch failed";
+    case CURL_ERR_MISALIGNED: return "pointer not 4-byte aligned";
+    default: return "unknown error";
+  }
+}
+
+size_t curl_bwd_workspace_bytes(int B, int H, int W) {
+  if (check_shape(B, H, W) != CURL_OK) return 0;
+  // sized for the scalar path (most blocks) and the widest op (the layer: 20 moments)
+  const int HW = H * W;
+  int gx = bwd_grid_x(B, HW, 1);
+  const int gx4 = bwd_grid_x(B, HW, 4);
+  if (gx4 > gx) gx = gx4;
+  const size_t tick_bytes = ((size_t)B * sizeof(unsigned) + 255) / 256 * 256;
+  return tick_bytes + (size_t)B * gx * 2 * LAYER_CURVES * sizeof(float);
+}
+
+static int layer_params(KParams& p, const float* img, const void* mask, int mask_kind, const float* L, int64_t ldL,
+                        const float* R, int64_t ldR, const float* Hk, int64_t ldH, int B, int H, int W, int K_lab,
+                        int K_rgb, int K_hsv) {
+  int rc = check_shape(B, H, W);
+  if (rc != CURL_OK) return rc;
+  if (!img || !L || !R || !Hk) return CURL_ERR_BAD_ARG;
+  if (K_lab < 3 || K_rgb < 3 || K_hsv < 3) return CURL_ERR_BAD_ARG;
+  if (mask_kind < CURL_MASK_NONE || mask_kind > CURL_MASK_F32) return CURL_ERR_BAD_ARG;
+  if ((mask_kind != CURL_MASK_NONE) != (mask != nullptr)) return CURL_ERR_BAD_ARG;
+  if (ldL < 3 * (int64_t)K_lab || ldR < 3 * (int64_t)K_rgb || ldH < 4 * (int64_t)K_hsv) return CURL_ERR_BAD_ARG;
+  if (3 * K_lab + 3 * K_rgb + 4 * K_hsv > CURL_MAX_KNOTS) return CURL_ERR_TOO_MANY_KNOTS;
+  if (!aligned4(img) || !aligned4(L) || !aligned4(R) || !aligned4(Hk)) return CURL_ERR_MISALIGNED;
+  p = KParams{};
+  p.in = img; p.mask = mask; p.HW = H * W; p.nseg = 3;
+  p.seg[0] = KnotSeg{L, nullptr, (long long)ldL, 3, K_lab};
+  p.seg[1] = KnotSeg{R, nullptr, (long long)ldR, 3, K_rgb};
+  p.seg[2] = KnotSeg{Hk, nullptr, (long long)ldH, 4, K_hsv};
+  return CURL_OK;
+}
+
+int curl_layer_fwd_f32(const float* img, const void* mask, int mask_kind, const float* L, int64_t ldL,
+                       const float* R, int64_t ldR, const float* Hk, int64_t ldH, float* out, float* reg, int B,
+                       int H, int W, int K_lab, int K_rgb, int K_hsv, void* stream) {
+  KParams p;
+  int rc = layer_params(p, img, mask, mask_kind, L, ldL, R, ldR, Hk, ldH, B, H, W, K_lab, K_rgb, K_hsv);
+  if (rc != CURL_OK) return rc;
+  if (!out || !reg) return CURL_ERR_BAD_ARG;
+  if (!aligned4(out)) return CURL_ERR_MISALIGNED;
+  p.out = out; p.reg = reg;
+  const bool v4 = can_vec4(p, mask_kind);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  switch (mask_kind) {
+    case CURL_MASK_NONE: return launch_fwd<OpLayer, MASK_NONE>(p, B, v4, st);
+    case CURL_MASK_U8: return launch_fwd<OpLayer, MASK_U8>(p, B, v4, st);
+    default: return launch_fwd<OpLayer, MASK_F32>(p, B, v4, st);
+  }
+}
+
+int curl_layer_bwd_f32(const float* img, const void* mask, int mask_kind, const float* L, int64_t ldL,
+                       const float* R, int64_t ldR, const float* Hk, int64_t ldH, const float* gout,
+                       const float* greg, float* gimg, float* gL, float* gR, float* gH, void* workspace,
+                       size_t workspace_bytes, int B, int H, int W, int K_lab, int K_rgb, int K_hsv, void* stream) {
+  KParams p;
+  int rc = layer_params(p, img, mask, mask_kind, L, ldL, R, ldR, Hk, ldH, B, H, W, K_lab, K_rgb, K_hsv);
+  if (rc != CURL_OK) return rc;
+  if (!gout || !gL || !gR || !gH) return CURL_ERR_BAD_ARG;
+  if (!aligned4(gout) || (gimg && !aligned4(gimg))) return CURL_ERR_MISALIGNED;
+  p.gout = gout; p.greg = greg; p.out = gimg;
+  p.seg[0].g = gL; p.seg[1].g = gR; p.seg[2].g = gH;
+  const bool v4 = can_vec4(p, mask_kind);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  switch (mask_kind) {
+    case CURL_MASK_NONE: return launch_bwd<OpLayer, MASK_NONE>(p, B, v4, workspace, workspace_bytes, st);
+    case CURL_MASK_U8: return launch_bwd<OpLayer, MASK_U8>(p, B, v4, workspace, workspace_bytes, st);
+    default: return launch_bwd<OpLayer, MASK_F32>(p, B, v4, workspace, workspace_bytes, st);
+  }
+}
+
+int curl_color_fwd_f32(int conversion, const float* in, float* out, int B, int H, int W, void* stream) {
+  int rc = check_shape(B, H, W);
+  if (rc != CURL_OK) return rc;
+  if (!in || !out) return CURL_ERR_BAD_ARG;
+  if (!aligned4(in) || !aligned4(out)) return CURL_ERR_MISALIGNED;
+  KParams p{};
+  p.in = in; p.out = out; p.HW = H * W;
+  const bool v4 = can_vec4(p, CURL_MASK_NONE);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  switch (conversion) {
+    case CURL_RGB2LAB: return launch_fwd<OpColor<CURL_RGB2LAB>, MASK_NONE>(p, B, v4, st);
+    case CURL_LAB2RGB: return launch_fwd<OpColor<CURL_LAB2RGB>, MASK_NONE>(p, B, v4, st);
+    case CURL_RGB2HSV: return launch_fwd<OpColor<CURL_RGB2HSV>, MASK_NONE>(p, B, v4, st);
+    case CURL_HSV2RGB: return launch_fwd<OpColor<CURL_HSV2RGB>, MASK_NONE>(p, B, v4, st);
+    default: return CURL_ERR_BAD_ARG;
+  }
+}
+
+int curl_color_bwd_f32(int conversion, const float* in, const float* gout, float* gin, int B, int H, int W,
+                       void* stream) {
+  int rc = check_shape(B, H, W);
+  if (rc != CURL_OK) return rc;
+  if (!in || !gout || !gin) return CURL_ERR_BAD_ARG;
+  if (!aligned4(in) || !aligned4(gout) || !aligned4(gin)) return CURL_ERR_MISALIGNED;
+  KParams p{};
+  p.in = in; p.gout = gout; p.out = gin; p.HW = H * W;
+  const bool v4 = can_vec4(p, CURL_MASK_NONE);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  switch (conversion) {
+    case CURL_RGB2LAB: return launch_bwd<OpColor<CURL_RGB2LAB>, MASK_NONE>(p, B, v4, nullptr, 0, st);
+    case CURL_LAB2RGB: return launch_bwd<OpColor<CURL_LAB2RGB>, MASK_NONE>(p, B, v4, nullptr, 0, st);
+    case CURL_RGB2HSV: return launch_bwd<OpColor<CURL_RGB2HSV>, MASK_NONE>(p, B, v4, nullptr, 0, st);
+    case CURL_HSV2RGB: return launch_bwd<OpColor<CURL_HSV2RGB>, MASK_NONE>(p, B, v4, nullptr, 0, st);
+    default: return CURL_ERR_BAD_ARG;
+  }
+}
+
+static int adjust_params(KParams& p, int group, const float* in, const float* P, int64_t ldP, int B, int H, int W,
+                         int K) {
+  int rc = check_shape(B, H, W);
+  if (rc != CURL_OK) return rc;
+  if (!in || !P || K < 3) return CURL_ERR_BAD_ARG;
+  if (group < CURL_ADJUST_LAB || group > CURL_ADJUST_HSV) return CURL_ERR_BAD_ARG;
+  const int nc = (group == CURL_ADJUST_HSV) ? 4 : 3;
+  if (ldP < (int64_t)nc * K) return CURL_ERR_BAD_ARG;
+  if (nc * K > CURL_MAX_KNOTS) return CURL_ERR_TOO_MANY_KNOTS;
+  if (!aligned4(in) || !aligned4(P)) return CURL_ERR_MISALIGNED;
+  p = KParams{};
+  p.in = in; p.HW = H * W; p.nseg = 1;
+  p.seg[0] = KnotSeg{P, nullptr, (long long)ldP, nc, K};
+  return CURL_OK;
+}
+
+int curl_adjust_fwd_f32(int group, const float* in, const float* P, int64_t ldP, float* out, float* reg, int B,
+                        int H, int W, int K, void* stream) {
+  KParams p;
+  int rc = adjust_params(p, group, in, P, ldP, B, H, W, K);
+  if (rc != CURL_OK) return rc;
+  if (!out || !reg) return CURL_ERR_BAD_ARG;
+  if (!aligned4(out)) return CURL_ERR_MISALIGNED;
+  p.out = out; p.reg = reg;
+  const bool v4 = can_vec4(p, CURL_MASK_NONE);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (group == CURL_ADJUST_HSV) return launch_fwd<OpAdjustHsv, MASK_NONE>(p, B, v4, st);
+  return launch_fwd<OpAdjustSelf3, MASK_NONE>(p, B, v4, st);
+}
+
+int curl_adjust_bwd_f32(int group, const float* in, const float* P, int64_t ldP, const float* gout,
+                        const float* greg, float* gin, float* gP, void* workspace, size_t workspace_bytes, int B,
+                        int H, int W, int K, void* stream) {
+  KParams p;
+  int rc = adjust_params(p, group, in, P, ldP, B, H, W, K);
+  if (rc != CURL_OK) return rc;
+  if (!gout || !gP) return CURL_ERR_BAD_ARG;
+  if (!aligned4(gout) || (gin && !aligned4(gin))) return CURL_ERR_MISALIGNED;
+  p.gout = gout; p.greg = greg; p.out = gin; p.seg[0].g = gP;
+  const bool v4 = can_vec4(p, CURL_MASK_NONE);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (group == CURL_ADJUST_HSV) return launch_bwd<OpAdjustHsv, MASK_NONE>(p, B, v4, workspace, workspace_bytes, st);
+  return launch_bwd<OpAdjustSelf3, MASK_NONE>(p, B, v4, workspace, workspace_bytes, st);
+}
+
+int curl_apply_curve_fwd_f32(const float* in, const float* C, int64_t ldC, int channel_in, int channel_out,
+                             float* out, float* reg, int B, int H, int W, int K, void* stream) {
+  int rc = check_shape(B, H, W);
+  if (rc != CURL_OK) return rc;
+  if (!in || !C || !out || !reg || K < 3 || ldC < K) return CURL_ERR_BAD_ARG;
+  if (channel_in < 0 || channel_in > 2 || channel_out < 0 || channel_out > 2) return CURL_ERR_BAD_ARG;
+  if (K > CURL_MAX_KNOTS) return CURL_ERR_TOO_MANY_KNOTS;
+  if (!aligned4(in) || !aligned4(C) || !aligned4(out)) return CURL_ERR_MISALIGNED;
+  KParams p{};
+  p.in = in; p.out = out; p.reg = reg; p.HW = H * W; p.nseg = 1; p.linear_knots = 1;
+  p.aux = channel_in | (channel_out << 2);
+  p.seg[0] = KnotSeg{C, nullptr, (long long)ldC, 1, K};
+  return launch_fwd<OpCurve1, MASK_NONE>(p, B, can_vec4(p, CURL_MASK_NONE), reinterpret_cast<cudaStream_t>(stream));
+}
+
+int curl_apply_curve_bwd_f32(const float* in, const float* C, int64_t ldC, int channel_in, int channel_out,
+                             const float* gout, const float* greg, float* gin, float* gC, void* workspace,
+                             size_t workspace_bytes, int B, int H, int W, int K, void* stream) {
+  int rc = check_shape(B, H, W);
+  if (rc != CURL_OK) return rc;
+  if (!in || !C || !gout || !gC || K < 3 || ldC < K) return CURL_ERR_BAD_ARG;
+  if (channel_in < 0 || channel_in > 2 || channel_out < 0 || channel_out > 2) return CURL_ERR_BAD_ARG;
+  if (K > CURL_MAX_KNOTS) return CURL_ERR_TOO_MANY_KNOTS;
+  if (!aligned4(in) || !aligned4(C) || !aligned4(gout) || (gin && !aligned4(gin))) return CURL_ERR_MISALIGNED;
+  KParams p{};
+  p.in = in; p.gout = gout; p.greg = greg; p.out = gin; p.HW = H * W; p.nseg = 1; p.linear_knots = 1;
+  p.aux = channel_in | (channel_out << 2);
+  p.seg[0] = KnotSeg{C, gC, (long long)ldC, 1, K};
+  return launch_bwd<OpCurve1, MASK_NONE>(p, B, can_vec4(p, CURL_MASK_NONE), workspace, workspace_bytes,
+                                         reinterpret_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

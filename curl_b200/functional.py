@@ -1,0 +1,264 @@
+"""torch.autograd.Function wrappers over the C ABI (include/curl_b200.h).
+
+Call chain: module/function API (colors.py, curves.py, model.py) -> *Fn.apply -> ctypes ->
+libcurl_b200.so -> sm_100a kernels on torch's current stream.  Backward recomputes the forward
+inside the kernel, so the only tensors saved for backward are the op's inputs.
+"""
+import torch
+
+from . import _lib
+
+
+def _stream(dev):
+    return torch.cuda.current_stream(dev).cuda_stream
+
+
+def _ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def _image(x, name):
+    """Validates an NCHW fp32 CUDA image and returns it contiguous (the reference calls
+    .contiguous() itself: colors.py:35,95,208; curves.py:50,99,146)."""
+    if not isinstance(x, torch.Tensor):
+        raise TypeError("%s must be a torch.Tensor" % name)
+    if not x.is_cuda:
+        raise RuntimeError("curl_b200: %s must be a CUDA tensor (this path has no CPU implementation)" % name)
+    if x.dtype != torch.float32:
+        raise TypeError("curl_b200: %s must be float32, got %s" % (name, x.dtype))
+    if x.dim() != 4 or x.shape[1] != 3:
+        raise ValueError("curl_b200: %s must have shape [B, 3, H, W], got %s" % (name, tuple(x.shape)))
+    if x.numel() == 0:
+        raise ValueError("curl_b200: %s is empty" % name)
+    return x.contiguous()
+
+
+def _knots(P, n, name, dev):
+    """Validates a [B, >= n] fp32 knot tensor; returns (tensor, row_stride) with unit column stride."""
+    if not isinstance(P, torch.Tensor) or P.dim() != 2:
+        raise ValueError("curl_b200: %s must be a 2-D tensor [B, >= %d]" % (name, n))
+    if P.device != dev:
+        raise RuntimeError("curl_b200: %s is on %s, image is on %s" % (name, P.device, dev))
+    if P.dtype != torch.float32:
+        raise TypeError("curl_b200: %s must be float32, got %s" % (name, P.dtype))
+    if P.shape[1] < n:
+        raise ValueError("curl_b200: %s has %d columns, needs at least %d" % (name, P.shape[1], n))
+    if P.stride(1) != 1 or (P.shape[0] > 1 and P.stride(0) < n):
+        P = P.contiguous()
+    return P, (P.stride(0) if P.shape[0] > 1 else max(P.stride(0), n))
+
+
+def _mask(mask, img):
+    """Returns (mask_tensor_or_None, mask_kind).  bool/uint8 -> 1 byte per pixel; anything else is
+    converted to fp32 and multiplied in at every stage like the reference (model.py:154,160,166,170)."""
+    if mask is None:
+        return None, _lib.MASK_NONE
+    B, _, H, W = img.shape
+    if not isinstance(mask, torch.Tensor):
+        raise TypeError("curl_b200: mask must be a torch.Tensor or None")
+    if mask.device != img.device:
+        raise RuntimeError("curl_b200: mask is on %s, image is on %s" % (mask.device, img.device))
+    if mask.requires_grad:
+        raise RuntimeError("curl_b200: gradients w.r.t. the mask are not supported")
+    if mask.dim() == 3:
+        mask = mask.unsqueeze(1)
+    if mask.dim() != 4 or mask.shape[1] != 1 or mask.shape[2:] != (H, W) or mask.shape[0] not in (1, B):
+        raise ValueError("curl_b200: mask must have shape [B, 1, H, W], got %s" % (tuple(mask.shape),))
+    if mask.shape[0] != B:
+        mask = mask.expand(B, 1, H, W)
+    if mask.dtype in (torch.bool, torch.uint8):
+        return mask.contiguous(), _lib.MASK_U8
+    return mask.to(torch.float32).contiguous(), _lib.MASK_F32
+
+
+def _workspace(B, H, W, dev):
+    n = _lib.load().curl_bwd_workspace_bytes(B, H, W)
+    return torch.empty(n, dtype=torch.uint8, device=dev), n
+
+
+class CurlLayerFn(torch.autograd.Function):
+    """Fused CURLLayer.forward (reference model.py:137-176) and its recompute backward."""
+
+    @staticmethod
+    def forward(ctx, img, mask, L, R, H, k_lab, k_rgb, k_hsv):
+        lib = _lib.load()
+        img = _image(img, "img")
+        dev = img.device
+        L, ldL = _knots(L, 3 * k_lab, "L", dev)
+        R, ldR = _knots(R, 3 * k_rgb, "R", dev)
+        H, ldH = _knots(H, 4 * k_hsv, "H", dev)
+        B, _, h, w = img.shape
+        for P, nm in ((L, "L"), (R, "R"), (H, "H")):
+            if P.shape[0] != B:
+                raise ValueError("curl_b200: %s has batch %d, image has %d" % (nm, P.shape[0], B))
+        mask, kind = _mask(mask, img)
+        out = torch.empty_like(img)
+        reg = torch.empty(B, dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            rc = lib.curl_layer_fwd_f32(_ptr(img), _ptr(mask), kind, _ptr(L), ldL, _ptr(R), ldR, _ptr(H), ldH,
+                                        _ptr(out), _ptr(reg), B, h, w, k_lab, k_rgb, k_hsv, _stream(dev))
+        _lib.check(rc, "curl_layer_fwd_f32")
+        _lib.count_launch()
+        ctx.save_for_backward(img, mask, L, R, H)
+        ctx.cfg = (kind, ldL, ldR, ldH, k_lab, k_rgb, k_hsv)
+        return out, reg
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, gout, greg):
+        lib = _lib.load()
+        img, mask, L, R, H = ctx.saved_tensors
+        kind, ldL, ldR, ldH, k_lab, k_rgb, k_hsv = ctx.cfg
+        dev = img.device
+        B, _, h, w = img.shape
+        gout = gout.contiguous() if gout is not None else torch.zeros_like(img)
+        greg = greg.contiguous() if greg is not None else None
+        want_gimg = ctx.needs_input_grad[0]
+        gimg = torch.empty_like(img) if want_gimg else None
+        gL = torch.empty(B, 3 * k_lab, dtype=torch.float32, device=dev)
+        gR = torch.empty(B, 3 * k_rgb, dtype=torch.float32, device=dev)
+        gH = torch.empty(B, 4 * k_hsv, dtype=torch.float32, device=dev)
+        ws, ws_bytes = _workspace(B, h, w, dev)
+        with torch.cuda.device(dev):
+            rc = lib.curl_layer_bwd_f32(_ptr(img), _ptr(mask), kind, _ptr(L), ldL, _ptr(R), ldR, _ptr(H), ldH,
+                                        _ptr(gout), _ptr(greg), _ptr(gimg), _ptr(gL), _ptr(gR), _ptr(gH),
+                                        _ptr(ws), ws_bytes, B, h, w, k_lab, k_rgb, k_hsv, _stream(dev))
+        _lib.check(rc, "curl_layer_bwd_f32")
+        _lib.count_launch()
+
+        def widen(g, P):
+            # columns beyond num_*_points were sliced away by the layer: zero gradient
+            if g.shape[1] == P.shape[1]:
+                return g
+            full = torch.zeros_like(P, memory_format=torch.contiguous_format)
+            full[:, :g.shape[1]] = g
+            return full
+
+        return gimg, None, widen(gL, L), widen(gR, R), widen(gH, H), None, None, None
+
+
+class ColorFn(torch.autograd.Function):
+    """Stand-alone colour conversion (reference colors.py modules)."""
+
+    @staticmethod
+    def forward(ctx, img, conversion):
+        lib = _lib.load()
+        img = _image(img, "img")
+        B, _, h, w = img.shape
+        out = torch.empty_like(img)
+        with torch.cuda.device(img.device):
+            rc = lib.curl_color_fwd_f32(conversion, _ptr(img), _ptr(out), B, h, w, _stream(img.device))
+        _lib.check(rc, "curl_color_fwd_f32")
+        _lib.count_launch()
+        ctx.save_for_backward(img)
+        ctx.conversion = conversion
+        return out
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, gout):
+        lib = _lib.load()
+        (img,) = ctx.saved_tensors
+        B, _, h, w = img.shape
+        gout = gout.contiguous()
+        gin = torch.empty_like(img)
+        with torch.cuda.device(img.device):
+            rc = lib.curl_color_bwd_f32(ctx.conversion, _ptr(img), _ptr(gout), _ptr(gin), B, h, w, _stream(img.device))
+        _lib.check(rc, "curl_color_bwd_f32")
+        _lib.count_launch()
+        return gin, None
+
+
+class AdjustFn(torch.autograd.Function):
+    """Stand-alone curve group (reference curves.adjust_lab / adjust_rgb / adjust_hsv)."""
+
+    @staticmethod
+    def forward(ctx, img, P, group):
+        lib = _lib.load()
+        img = _image(img, "img")
+        nc = 4 if group == _lib.ADJUST_HSV else 3
+        if P.dim() != 2 or P.shape[1] < 3 * nc:
+            raise ValueError("curl_b200: curve parameters must be [B, %d*K] with K >= 3" % nc)
+        K = -(-P.shape[1] // nc)          # torch.chunk(P, nc, dim=1) chunk size (curves.py:53,105,152)
+        if K * nc != P.shape[1]:
+            raise ValueError("curl_b200: parameter width %d is not a multiple of %d curves" % (P.shape[1], nc))
+        P, ldP = _knots(P, nc * K, "P", img.device)
+        B, _, h, w = img.shape
+        if P.shape[0] != B:
+            raise ValueError("curl_b200: P has batch %d, image has %d" % (P.shape[0], B))
+        out = torch.empty_like(img)
+        reg = torch.empty(B, dtype=torch.float32, device=img.device)
+        with torch.cuda.device(img.device):
+            rc = lib.curl_adjust_fwd_f32(group, _ptr(img), _ptr(P), ldP, _ptr(out), _ptr(reg), B, h, w, K,
+                                         _stream(img.device))
+        _lib.check(rc, "curl_adjust_fwd_f32")
+        _lib.count_launch()
+        ctx.save_for_backward(img, P)
+        ctx.cfg = (group, ldP, K, nc)
+        return out, reg
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, gout, greg):
+        lib = _lib.load()
+        img, P = ctx.saved_tensors
+        group, ldP, K, nc = ctx.cfg
+        dev = img.device
+        B, _, h, w = img.shape
+        gout = gout.contiguous() if gout is not None else torch.zeros_like(img)
+        greg = greg.contiguous() if greg is not None else None
+        gin = torch.empty_like(img) if ctx.needs_input_grad[0] else None
+        gP = torch.empty(B, nc * K, dtype=torch.float32, device=dev)
+        ws, ws_bytes = _workspace(B, h, w, dev)
+        with torch.cuda.device(dev):
+            rc = lib.curl_adjust_bwd_f32(group, _ptr(img), _ptr(P), ldP, _ptr(gout), _ptr(greg), _ptr(gin), _ptr(gP),
+                                         _ptr(ws), ws_bytes, B, h, w, K, _stream(dev))
+        _lib.check(rc, "curl_adjust_bwd_f32")
+        _lib.count_launch()
+        return gin, gP, None
+
+
+class ApplyCurveFn(torch.autograd.Function):
+    """One curve with knots C given directly (reference curves.apply_curve, curves.py:4-38)."""
+
+    @staticmethod
+    def forward(ctx, img, C, channel_in, channel_out):
+        lib = _lib.load()
+        img = _image(img, "img")
+        if C.dim() != 2 or C.shape[1] < 3:
+            raise ValueError("curl_b200: C must be [B, K] with K >= 3")
+        K = C.shape[1]
+        C, ldC = _knots(C, K, "C", img.device)
+        B, _, h, w = img.shape
+        if C.shape[0] != B:
+            raise ValueError("curl_b200: C has batch %d, image has %d" % (C.shape[0], B))
+        out = torch.empty_like(img)
+        reg = torch.empty(B, dtype=torch.float32, device=img.device)
+        with torch.cuda.device(img.device):
+            rc = lib.curl_apply_curve_fwd_f32(_ptr(img), _ptr(C), ldC, channel_in, channel_out, _ptr(out), _ptr(reg),
+                                              B, h, w, K, _stream(img.device))
+        _lib.check(rc, "curl_apply_curve_fwd_f32")
+        _lib.count_launch()
+        ctx.save_for_backward(img, C)
+        ctx.cfg = (ldC, K, channel_in, channel_out)
+        return out, reg
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, gout, greg):
+        lib = _lib.load()
+        img, C = ctx.saved_tensors
+        ldC, K, cin, cout = ctx.cfg
+        dev = img.device
+        B, _, h, w = img.shape
+        gout = gout.contiguous() if gout is not None else torch.zeros_like(img)
+        greg = greg.contiguous() if greg is not None else None
+        gin = torch.empty_like(img) if ctx.needs_input_grad[0] else None
+        gC = torch.empty(B, K, dtype=torch.float32, device=dev)
+        ws, ws_bytes = _workspace(B, h, w, dev)
+        with torch.cuda.device(dev):
+            rc = lib.curl_apply_curve_bwd_f32(_ptr(img), _ptr(C), ldC, cin, cout, _ptr(gout), _ptr(greg), _ptr(gin),
+                                              _ptr(gC), _ptr(ws), ws_bytes, B, h, w, K, _stream(dev))
+        _lib.check(rc, "curl_apply_curve_bwd_f32")
+        _lib.count_launch()
+        return gin, gC, None, None

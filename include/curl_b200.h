@@ -1,0 +1,126 @@
+/*
+ * curl_b200 -- C ABI of the B200 (sm_100a) CURL curve-layer library (libcurl_b200.so).
+ *
+ * The reference (danielbulhosa/CURL) is pure Python and has no FFI of its own: its boundary for this
+ * path is the nn.Module / function API of colors.py, curves.py and model.py::CURLLayer.  This
+ * header is the C ABI inserted *underneath* that API ("Level 2"); each entry point
+ * names the reference interface it replaces.  curl_b200/ (Python) binds it with ctypes and mirrors
+ * the reference module API on top; INTEGRATION.md shows the binding a reference maintainer would add.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer owned by the caller, except where noted; nothing is
+ *     allocated, freed or synchronised inside the library; work is enqueued on `stream`
+ *     (a cudaStream_t passed as void*; NULL = legacy default stream) of the CURRENT device.
+ *   - images are planar NCHW fp32, contiguous: img[B][3][H][W].  mask is [B][1][H][W].
+ *   - return 0 on success, a negative CURL_ERR_* otherwise; nothing is thrown across the ABI.
+ *   - re-entrant across host threads as long as the streams (and workspaces) differ.
+ *   - all calls are CUDA-graph capturable (no host synchronisation, no host-side reads).
+ */
+#ifndef CURL_B200_H_
+#define CURL_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CURL_ABI_VERSION 1
+
+/* error codes */
+#define CURL_OK 0
+#define CURL_ERR_BAD_ARG (-1)        /* null pointer, non-positive size, K < 3, unknown enum */
+#define CURL_ERR_TOO_MANY_KNOTS (-2) /* total knots per image exceed CURL_MAX_KNOTS */
+#define CURL_ERR_WORKSPACE (-3)      /* workspace missing or too small */
+#define CURL_ERR_LAUNCH (-4)         /* cudaGetLastError() after the launch was not cudaSuccess */
+#define CURL_ERR_MISALIGNED (-5)     /* a base pointer is not 4-byte aligned */
+
+#define CURL_MAX_KNOTS 1024
+
+/* mask_kind: how `mask` is to be read (reference: data.py:190 gives bool, infer.py:41 gives float) */
+#define CURL_MASK_NONE 0 /* mask == NULL, treated as all ones                              */
+#define CURL_MASK_U8 1   /* 1 byte per pixel, zero / non-zero (torch.bool or torch.uint8)    */
+#define CURL_MASK_F32 2  /* fp32 per pixel, arbitrary values, multiplied in at every stage   */
+
+/* colour conversions (reference colors.py) */
+#define CURL_RGB2LAB 0 /* colors.py:27-62   RGB2LAB.forward */
+#define CURL_LAB2RGB 1 /* colors.py:88-123  LAB2RGB.forward */
+#define CURL_RGB2HSV 2 /* colors.py:195-242 RGB2HSV.forward */
+#define CURL_HSV2RGB 3 /* colors.py:131-177 HSV2RGB.forward */
+
+/* curve groups (reference curves.py) */
+#define CURL_ADJUST_LAB 0 /* curves.py:136-180 adjust_lab: 3 curves c->c                 */
+#define CURL_ADJUST_RGB 1 /* curves.py:90-133  adjust_rgb: 3 curves c->c                 */
+#define CURL_ADJUST_HSV 2 /* curves.py:41-87   adjust_hsv: 4 curves 0->0, 0->1, 1->1, 2->2 */
+
+int curl_abi_version(void);
+const char* curl_strerror(int code);
+
+/*
+ * Fused forward of the whole layer.  Replaces CURLLayer.forward (model.py:137-176):
+ *   rgb2lab -> adjust_lab -> *mask -> lab2rgb -> adjust_rgb -> *mask -> rgb2hsv -> adjust_hsv ->
+ *   *mask -> hsv2rgb -> clamp(img + residual, 0, 1) * mask,   reg = reg_rgb + reg_lab + reg_hsv.
+ * L, R, Hk: log-domain knots, row b at L + b*ldL (ld in elements, so column-sliced views such as
+ * curves[:, :48] (model.py:197-199) need no copy); 3*K_lab, 3*K_rgb, 4*K_hsv leading columns read.
+ * out[B][3][H][W], reg[B].  One kernel launch.
+ */
+int curl_layer_fwd_f32(const float* img, const void* mask, int mask_kind,
+                       const float* L, int64_t ldL, const float* R, int64_t ldR,
+                       const float* Hk, int64_t ldH,
+                       float* out, float* reg,
+                       int B, int H, int W, int K_lab, int K_rgb, int K_hsv, void* stream);
+
+/*
+ * Fused backward of the layer.  Replaces torch.autograd over model.py:137-176 (SURVEY.md 8a row
+ * a10).  Recomputes the forward per pixel from img (no saved activations), writes
+ *   gimg[B][3][H][W]   (may be NULL: skipped, e.g. when img does not require grad),
+ *   gL[B][3*K_lab], gR[B][3*K_rgb], gH[B][4*K_hsv]   dense, gradient w.r.t. the LOG-domain knots,
+ * given gout[B][3][H][W] and greg[B] (may be NULL = zeros).  Knot gradients are reduced in the
+ * kernel: registers -> warp shuffles -> shared memory -> one partial row per block in
+ * `workspace`, one atomic ticket per block, and the last block of each image folds the partials in
+ * a fixed order (bitwise deterministic).  One memset node + one kernel launch.
+ */
+int curl_layer_bwd_f32(const float* img, const void* mask, int mask_kind,
+                       const float* L, int64_t ldL, const float* R, int64_t ldR,
+                       const float* Hk, int64_t ldH,
+                       const float* gout, const float* greg,
+                       float* gimg, float* gL, float* gR, float* gH,
+                       void* workspace, size_t workspace_bytes,
+                       int B, int H, int W, int K_lab, int K_rgb, int K_hsv, void* stream);
+
+/* Bytes of device workspace the two *_bwd_f32 entry points need for this shape (host-only call). */
+size_t curl_bwd_workspace_bytes(int B, int H, int W);
+
+/* Stand-alone colour conversion, forward.  Replaces colors.<Module>.forward(img). */
+int curl_color_fwd_f32(int conversion, const float* in, float* out, int B, int H, int W, void* stream);
+/* ... and its backward: gin = J(in)^T gout (recomputes the forward from `in`). */
+int curl_color_bwd_f32(int conversion, const float* in, const float* gout, float* gin,
+                       int B, int H, int W, void* stream);
+
+/* Stand-alone curve group, forward.  Replaces curves.adjust_lab / adjust_rgb / adjust_hsv(img, P):
+ * P[B][>= n_curves*K] log-domain knots with row stride ldP; out[B][3][H][W]; reg[B]. */
+int curl_adjust_fwd_f32(int group, const float* in, const float* P, int64_t ldP,
+                        float* out, float* reg, int B, int H, int W, int K, void* stream);
+/* ... and its backward: gin[B][3][H][W] (nullable), gP[B][n_curves*K] dense. */
+int curl_adjust_bwd_f32(int group, const float* in, const float* P, int64_t ldP,
+                        const float* gout, const float* greg, float* gin, float* gP,
+                        void* workspace, size_t workspace_bytes,
+                        int B, int H, int W, int K, void* stream);
+
+/* One curve, knots given directly as C[B][>=K] (NOT log-domain), scale from channel_in applied to
+ * channel_out, then the whole-image clamp.  Replaces curves.apply_curve(img, C, slope_sqr_diff,
+ * channel_in, channel_out) (curves.py:4-38); reg[B] receives this curve's regulariser term (the
+ * caller adds it to its running slope_sqr_diff). */
+int curl_apply_curve_fwd_f32(const float* in, const float* C, int64_t ldC, int channel_in, int channel_out,
+                             float* out, float* reg, int B, int H, int W, int K, void* stream);
+/* ... and its backward: gin[B][3][H][W] (nullable), gC[B][K] dense (gradient w.r.t. C itself). */
+int curl_apply_curve_bwd_f32(const float* in, const float* C, int64_t ldC, int channel_in, int channel_out,
+                             const float* gout, const float* greg, float* gin, float* gC,
+                             void* workspace, size_t workspace_bytes,
+                             int B, int H, int W, int K, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CURL_B200_H_ */

@@ -1,0 +1,42 @@
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+LAYER_CASES = ["smooth", "uint8", "edges", "identity", "strong", "widek", "floatmask"]
+STAGE_CASES = ["wide", "edges", "unit"]
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+
+
+@pytest.fixture(scope="session")
+def layer_golden():
+    return np.load(os.path.join(GOLDEN, "layer.npz"))
+
+
+@pytest.fixture(scope="session")
+def stage_golden():
+    return np.load(os.path.join(GOLDEN, "stages.npz"))
+
+
+def rel_to_max(a, ref):
+    """max |a - ref| relative to the max-norm of ref (the knot-gradient criterion)."""
+    a = np.asarray(a, dtype=np.float64)
+    ref = np.asarray(ref, dtype=np.float64)
+    return float(np.abs(a - ref).max() / max(np.abs(ref).max(), 1e-30))
+
+
+def frac_over(a, ref, tol):
+    """fraction of elements whose abs error exceeds tol"""
+    a = np.asarray(a, dtype=np.float64)
+    ref = np.asarray(ref, dtype=np.float64)
+    return float((np.abs(a - ref) > tol).mean())

@@ -1,0 +1,91 @@
+"""TEST INFRASTRUCTURE ONLY: builds and binds tests/hostsim/pixel_sim.cpp (host instantiation of the
+kernel's per-pixel templates).  See the header of pixel_sim.cpp."""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+SRC = os.path.join(HERE, "pixel_sim.cpp")
+HDR = os.path.join(HERE, "..", "..", "curl_b200", "csrc", "curl_pixel.cuh")
+OUT = os.path.join(HERE, "_build", "libpixel_sim.so")
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is not None:
+        return _lib
+    newest = max(os.path.getmtime(SRC), os.path.getmtime(HDR))
+    if not os.path.exists(OUT) or os.path.getmtime(OUT) < newest:
+        os.makedirs(os.path.dirname(OUT), exist_ok=True)
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-shared", "-fPIC", "-o", OUT, SRC])
+    _lib = ctypes.CDLL(OUT)
+    return _lib
+
+
+def _f(a):
+    return None if a is None else a.ctypes.data_as(ctypes.c_void_p)
+
+
+def _c(a, dtype=np.float32):
+    return None if a is None else np.ascontiguousarray(a, dtype=dtype)
+
+
+def _mask(mask):
+    if mask is None:
+        return None, 0
+    if mask.dtype == np.bool_ or mask.dtype == np.uint8:
+        return np.ascontiguousarray(mask).view(np.uint8), 1
+    return np.ascontiguousarray(mask, dtype=np.float32), 2
+
+
+def layer(img, mask, L, R, H, pts=(48, 48, 64), gout=None, greg=None):
+    """Returns dict(out, reg) or, when gout is given, dict(gimg, gL, gR, gH)."""
+    img = _c(img); L = _c(L); R = _c(R); H = _c(H)
+    B, _, h, w = img.shape
+    m, kind = _mask(mask)
+    Kl, Kr, Kh = pts[0] // 3, pts[1] // 3, pts[2] // 4
+    i64 = ctypes.c_int64
+    if gout is None:
+        out = np.empty_like(img); reg = np.empty(B, np.float32)
+        rc = lib().sim_layer(0, _f(img), _f(m), kind, _f(L), i64(L.shape[1]), _f(R), i64(R.shape[1]), _f(H),
+                             i64(H.shape[1]), _f(out), _f(reg), None, None, None, None, None, None, B, h * w, Kl, Kr, Kh)
+        assert rc == 0
+        return dict(out=out, reg=reg)
+    gout = _c(gout); greg = _c(greg)
+    gimg = np.empty_like(img)
+    gL = np.zeros((B, 3 * Kl), np.float32); gR = np.zeros((B, 3 * Kr), np.float32); gH = np.zeros((B, 4 * Kh), np.float32)
+    rc = lib().sim_layer(1, _f(img), _f(m), kind, _f(L), i64(L.shape[1]), _f(R), i64(R.shape[1]), _f(H), i64(H.shape[1]),
+                         None, None, _f(gout), _f(greg), _f(gimg), _f(gL), _f(gR), _f(gH), B, h * w, Kl, Kr, Kh)
+    assert rc == 0
+    return dict(gimg=gimg, gL=gL, gR=gR, gH=gH)
+
+
+def color(conv, x, gy=None):
+    x = _c(x)
+    B, _, h, w = x.shape
+    out = np.empty_like(x)
+    gy = _c(gy)
+    rc = lib().sim_color(0 if gy is None else 1, conv, _f(x), _f(gy), _f(out), B, h * w)
+    assert rc == 0
+    return out
+
+
+def adjust(group, x, P, K, gy=None, greg=None):
+    x = _c(x); P = _c(P)
+    B, _, h, w = x.shape
+    nc = 4 if group == 2 else 3
+    i64 = ctypes.c_int64
+    if gy is None:
+        out = np.empty_like(x); reg = np.empty(B, np.float32)
+        rc = lib().sim_adjust(0, group, _f(x), _f(P), i64(P.shape[1]), _f(out), _f(reg), None, None, None, None, B, h * w, K)
+        assert rc == 0
+        return dict(y=out, reg=reg)
+    gy = _c(gy); greg = _c(greg)
+    gx = np.empty_like(x); gP = np.zeros((B, nc * K), np.float32)
+    rc = lib().sim_adjust(1, group, _f(x), _f(P), i64(P.shape[1]), None, None, _f(gy), _f(greg), _f(gx), _f(gP), B, h * w, K)
+    assert rc == 0
+    return dict(gx=gx, gP=gP)

@@ -1,0 +1,168 @@
+// TEST INFRASTRUCTURE ONLY -- host instantiation of curl_b200/csrc/curl_pixel.cuh.
+//
+// The per-pixel forward/backward functions the sm_100a kernels are built from are plain templates
+// over a math policy.  This file instantiates them with HostMath (double-precision libm rounded to
+// fp32 in place of MUFU.LG2/EX2/RCP) behind a small C interface so that the CPU-only test suite
+// can check the hand-derived reverse-mode code, the tie/clamp/branch semantics and the knot-gradient
+// moment expansion against the oracle without a GPU.  It is compiled by tests/ on demand into
+// tests/hostsim/_build/ and is never part of, linked into, or reachable from the product library.
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <vector>
+
+#include "../../curl_b200/csrc/curl_pixel.cuh"
+
+using namespace curl;
+
+namespace {
+
+struct Seg { const float* p; int64_t ld; int nc, K; float* g; };
+
+struct Curves {
+  std::vector<float> C, ab;
+  double reg = 0.0;
+  void stage(const Seg* segs, int nseg, int b) {
+    C.clear(); ab.clear(); reg = 0.0;
+    for (int s = 0; s < nseg; ++s) {
+      const int n = segs[s].nc * segs[s].K;
+      for (int i = 0; i < n; ++i) C.push_back((float)exp((double)segs[s].p[(size_t)b * segs[s].ld + i]));
+    }
+    int off = 0;
+    for (int s = 0; s < nseg; ++s)
+      for (int c = 0; c < segs[s].nc; ++c) {
+        float a, bt;
+        curve_alpha_beta(C.data() + off, segs[s].K, &a, &bt);
+        ab.push_back(a); ab.push_back(bt);
+        reg += curve_regulariser(C.data() + off, segs[s].K);
+        off += segs[s].K;
+      }
+  }
+  void grads(const Seg* segs, int nseg, int b, const std::vector<double>& mom, double greg) const {
+    int off = 0, cb = 0;
+    for (int s = 0; s < nseg; ++s) {
+      const int K = segs[s].K;
+      for (int c = 0; c < segs[s].nc; ++c) {
+        for (int i = 0; i < K; ++i)
+          segs[s].g[(size_t)b * segs[s].nc * K + c * K + i] =
+              curve_knot_grad(C.data() + off, K, i, mom[2 * (cb + c)], mom[2 * (cb + c) + 1], greg, true);
+        off += K;
+      }
+      cb += segs[s].nc;
+    }
+  }
+};
+
+float mask_at(const void* mask, int kind, size_t i) {
+  if (kind == MASK_NONE) return 1.0f;
+  if (kind == MASK_U8) return ((const unsigned char*)mask)[i] ? 1.0f : 0.0f;
+  return ((const float*)mask)[i];
+}
+
+template <int MK>
+void layer_fwd_mk(const float x[3], float m, const float* ab, float y[3]) { layer_fwd<HostMath, MK>(x, m, ab, y); }
+template <int MK>
+void layer_bwd_mk(const float x[3], float m, const float* ab, const float gy[3], float gx[3], float* mom) {
+  layer_bwd<HostMath, MK>(x, m, ab, gy, gx, mom);
+}
+
+}  // namespace
+
+extern "C" {
+
+int sim_layer(int do_bwd, const float* img, const void* mask, int mask_kind, const float* L, int64_t ldL,
+              const float* R, int64_t ldR, const float* Hk, int64_t ldH, float* out, float* reg,
+              const float* gout, const float* greg, float* gimg, float* gL, float* gR, float* gH, int B, int HW,
+              int Kl, int Kr, int Kh) {
+  Seg segs[3] = {{L, ldL, 3, Kl, gL}, {R, ldR, 3, Kr, gR}, {Hk, ldH, 4, Kh, gH}};
+  Curves cv;
+  for (int b = 0; b < B; ++b) {
+    cv.stage(segs, 3, b);
+    if (reg) reg[b] = (float)cv.reg;
+    std::vector<float> mom(20, 0.0f);
+    std::vector<double> momd(20, 0.0);
+    for (int i = 0; i < HW; ++i) {
+      const size_t o = (size_t)b * 3 * HW + i;
+      const float x[3] = {img[o], img[o + HW], img[o + 2 * (size_t)HW]};
+      const float m = mask_at(mask, mask_kind, (size_t)b * HW + i);
+      if (!do_bwd) {
+        float y[3];
+        if (mask_kind == MASK_NONE) layer_fwd_mk<MASK_NONE>(x, m, cv.ab.data(), y);
+        else if (mask_kind == MASK_U8) layer_fwd_mk<MASK_U8>(x, m, cv.ab.data(), y);
+        else layer_fwd_mk<MASK_F32>(x, m, cv.ab.data(), y);
+        out[o] = y[0]; out[o + HW] = y[1]; out[o + 2 * (size_t)HW] = y[2];
+      } else {
+        const float gy[3] = {gout[o], gout[o + HW], gout[o + 2 * (size_t)HW]};
+        float gx[3];
+        for (auto& v : mom) v = 0.0f;
+        if (mask_kind == MASK_NONE) layer_bwd_mk<MASK_NONE>(x, m, cv.ab.data(), gy, gx, mom.data());
+        else if (mask_kind == MASK_U8) layer_bwd_mk<MASK_U8>(x, m, cv.ab.data(), gy, gx, mom.data());
+        else layer_bwd_mk<MASK_F32>(x, m, cv.ab.data(), gy, gx, mom.data());
+        for (int k = 0; k < 20; ++k) momd[k] += (double)mom[k];
+        if (gimg) { gimg[o] = gx[0]; gimg[o + HW] = gx[1]; gimg[o + 2 * (size_t)HW] = gx[2]; }
+      }
+    }
+    if (do_bwd) cv.grads(segs, 3, b, momd, greg ? (double)greg[b] : 0.0);
+  }
+  return 0;
+}
+
+int sim_color(int do_bwd, int conv, const float* in, const float* gout, float* out, int B, int HW) {
+  for (int b = 0; b < B; ++b)
+    for (int i = 0; i < HW; ++i) {
+      const size_t o = (size_t)b * 3 * HW + i;
+      const float x[3] = {in[o], in[o + HW], in[o + 2 * (size_t)HW]};
+      float y[3], r[3];
+      float gy[3] = {0, 0, 0};
+      if (do_bwd) { gy[0] = gout[o]; gy[1] = gout[o + HW]; gy[2] = gout[o + 2 * (size_t)HW]; }
+      switch (conv) {
+        case 0: { LabJac j; rgb2lab_fwd<HostMath, true>(x, y, &j); rgb2lab_bwd(j, gy, r); break; }
+        case 1: { RgbJac j; lab2rgb_fwd<HostMath, true>(x, y, &j); lab2rgb_bwd(j, gy, r); break; }
+        case 2: { HsvJac j; rgb2hsv_fwd<HostMath, true, false>(x, y, &j); rgb2hsv_bwd(j, gy, r); break; }
+        case 3: { Hsv2RgbJac j; hsv2rgb_fwd<HostMath, true, false>(x, y, &j); hsv2rgb_bwd(j, gy, r); break; }
+        default: return -1;
+      }
+      const float* w = do_bwd ? r : y;
+      out[o] = w[0]; out[o + HW] = w[1]; out[o + 2 * (size_t)HW] = w[2];
+    }
+  return 0;
+}
+
+int sim_adjust(int do_bwd, int group, const float* in, const float* P, int64_t ldP, float* out, float* reg,
+               const float* gout, const float* greg, float* gin, float* gP, int B, int HW, int K) {
+  const int nc = group == 2 ? 4 : 3;
+  Seg segs[1] = {{P, ldP, nc, K, gP}};
+  Curves cv;
+  for (int b = 0; b < B; ++b) {
+    cv.stage(segs, 1, b);
+    if (reg) reg[b] = (float)cv.reg;
+    std::vector<double> momd(2 * nc, 0.0);
+    for (int i = 0; i < HW; ++i) {
+      const size_t o = (size_t)b * 3 * HW + i;
+      const float x[3] = {in[o], in[o + HW], in[o + 2 * (size_t)HW]};
+      float y[3], gx[3];
+      float gy[3] = {0, 0, 0};
+      float mom[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+      if (do_bwd) { gy[0] = gout[o]; gy[1] = gout[o + HW]; gy[2] = gout[o + 2 * (size_t)HW]; }
+      if (group == 2) {
+        HsvCurveJac j;
+        adjust_hsv_fwd<HostMath, true, false>(x, cv.ab.data(), y, &j);
+        adjust_hsv_bwd(j, cv.ab.data(), gy, gx, mom);
+      } else {
+        Self3Jac j;
+        adjust_self3_fwd<HostMath, true>(x, cv.ab.data(), y, &j);
+        adjust_self3_bwd(j, gy, gx, mom);
+      }
+      if (!do_bwd) { out[o] = y[0]; out[o + HW] = y[1]; out[o + 2 * (size_t)HW] = y[2]; }
+      else {
+        for (int k = 0; k < 2 * nc; ++k) momd[k] += (double)mom[k];
+        if (gin) { gin[o] = gx[0]; gin[o + HW] = gx[1]; gin[o + 2 * (size_t)HW] = gx[2]; }
+      }
+    }
+    if (do_bwd) cv.grads(segs, 1, b, momd, greg ? (double)greg[b] : 0.0);
+  }
+  return 0;
+}
+
+}  // extern "C"

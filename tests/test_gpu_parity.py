@@ -1,0 +1,298 @@
+"""GPU parity tests: the CUDA path (through the module API -> autograd.Function -> C ABI) against
+the committed golden fixtures (generated from the reference itself) and against the CPU oracle on
+seeded inputs.  Run on the B200 box: python -m pytest tests -m gpu."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import parity
+from conftest import LAYER_CASES, STAGE_CASES, ROOT
+
+pytestmark = pytest.mark.gpu
+
+REPORT = {}
+
+
+def _dev():
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    return torch.device("cuda:0")
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _write_report():
+    yield
+    out = os.path.join(ROOT, "gpurun_out")
+    os.makedirs(out, exist_ok=True)
+    with open(os.path.join(out, "parity_report.json"), "w") as f:
+        json.dump(REPORT, f, indent=1, sort_keys=True)
+
+
+def _run_layer(case, g, dev, want_gimg=True):
+    import curl_b200
+    pts = tuple(int(v) for v in g[f"{case}.pts"])
+    layer = curl_b200.CURLLayer(*pts).to(dev)
+    img = torch.from_numpy(g[f"{case}.img"]).to(dev).requires_grad_(want_gimg)
+    mask = torch.from_numpy(g[f"{case}.mask"]).to(dev)
+    L, R, H = (torch.from_numpy(g[f"{case}.{k}"]).to(dev).requires_grad_(True) for k in "LRH")
+    out, reg = layer(img, mask, L, R, H)
+    gout = torch.from_numpy(g[f"{case}.gout"]).to(dev)
+    greg = torch.from_numpy(g[f"{case}.greg"]).to(dev)
+    torch.autograd.backward([out, reg], [gout, greg])
+    res = dict(out=out.detach(), reg=reg.detach(), gL=L.grad, gR=R.grad, gH=H.grad)
+    if want_gimg:
+        res["gimg"] = img.grad
+    return {k: v.cpu().numpy() for k, v in res.items()}
+
+
+@pytest.mark.parametrize("case", LAYER_CASES)
+def test_layer_vs_golden(case, layer_golden):
+    g = layer_golden
+    ours = _run_layer(case, g, _dev())
+    r32 = {k: g[f"{case}.f32.{k}"] for k in ("out", "reg", "gimg", "gL", "gR", "gH")}
+    r64 = {k: g[f"{case}.f64.{k}"] for k in ("out", "reg", "gimg", "gL", "gR", "gH")}
+    rep = {}
+    rep["out"] = parity.check_image(case, ours["out"], r32["out"], r64["out"])
+    assert parity.rel_to_max(ours["reg"], r64["reg"]) <= 1e-5
+    gscale = float(np.abs(r64["gimg"]).max())
+    rep["gimg"] = parity.check_image(case, ours["gimg"], r32["gimg"], r64["gimg"], scale=gscale)
+    for k in ("gL", "gR", "gH"):
+        assert ours[k].shape == r32[k].shape
+        if case == "identity":
+            continue  # every pixel of this case sits on a tie/clamp bound; see parity.py
+        rep[k] = parity.check_knots(case, ours[k], r32[k], r64[k])
+    REPORT[f"layer.{case}"] = rep
+
+
+def test_layer_no_gimg_matches(layer_golden):
+    a = _run_layer("smooth", layer_golden, _dev(), want_gimg=True)
+    b = _run_layer("smooth", layer_golden, _dev(), want_gimg=False)
+    for k in ("out", "reg", "gL", "gR", "gH"):
+        assert np.array_equal(a[k], b[k]), k   # deterministic reduction: bitwise equal
+
+
+@pytest.mark.parametrize("case", STAGE_CASES)
+@pytest.mark.parametrize("mod", ["rgb2lab", "lab2rgb", "rgb2hsv", "hsv2rgb"])
+def test_color_modules_vs_golden(case, mod, stage_golden):
+    import curl_b200.colors as C
+    g = stage_golden
+    dev = _dev()
+    M = {"rgb2lab": C.RGB2LAB, "lab2rgb": C.LAB2RGB, "rgb2hsv": C.RGB2HSV, "hsv2rgb": C.HSV2RGB}[mod]().to(dev)
+    x = torch.from_numpy(g[f"{case}.x"]).to(dev).requires_grad_(True)
+    y = M(x)
+    y.backward(torch.from_numpy(g[f"{case}.gy"]).to(dev))
+    y32, y64 = g[f"{case}.{mod}.f32.y"], g[f"{case}.{mod}.f64.y"]
+    gx32, gx64 = g[f"{case}.{mod}.f32.gx"], g[f"{case}.{mod}.f64.gx"]
+    name = "smooth" if case == "unit" and mod != "rgb2hsv" else "edges"
+    scale = max(1.0, float(np.abs(y64).max()))   # lab2rgb of out-of-gamut input reaches |20|
+    rep = dict(y=parity.check_image(name, y.detach().cpu().numpy(), y32, y64, scale=scale))
+    gscale = float(np.abs(gx64).max())
+    rep["gx"] = parity.check_image("edges", x.grad.cpu().numpy(), gx32, gx64, scale=gscale, tol=2e-5)
+    REPORT[f"color.{mod}.{case}"] = rep
+
+
+@pytest.mark.parametrize("case", STAGE_CASES)
+@pytest.mark.parametrize("fn", ["adjust_lab", "adjust_rgb", "adjust_hsv"])
+def test_adjust_vs_golden(case, fn, stage_golden):
+    import curl_b200.curves as V
+    g = stage_golden
+    dev = _dev()
+    x = torch.from_numpy(g[f"{case}.x"]).to(dev).requires_grad_(True)
+    P = torch.from_numpy(g[f"{case}.{fn}.P"]).to(dev).requires_grad_(True)
+    y, reg = getattr(V, fn)(x, P)
+    torch.autograd.backward([y, reg], [torch.from_numpy(g[f"{case}.gy"]).to(dev), torch.ones_like(reg)])
+    pre = f"{case}.{fn}"
+    name = "smooth" if case == "unit" else "edges"
+    rep = dict(y=parity.check_image(name, y.detach().cpu().numpy(), g[f"{pre}.f32.y"], g[f"{pre}.f64.y"]))
+    assert parity.rel_to_max(reg.detach().cpu().numpy(), g[f"{pre}.f64.reg"]) <= 1e-5
+    gscale = float(np.abs(g[f"{pre}.f64.gx"]).max())
+    rep["gx"] = parity.check_image(name, x.grad.cpu().numpy(), g[f"{pre}.f32.gx"], g[f"{pre}.f64.gx"], scale=gscale)
+    rep["gP"] = parity.check_knots(name, P.grad.cpu().numpy(), g[f"{pre}.f32.gP"], g[f"{pre}.f64.gP"])
+    REPORT[f"{fn}.{case}"] = rep
+
+
+def test_apply_curve_vs_oracle():
+    import curl_b200.curves as V
+    from oracle import curl_oracle as O
+    dev = _dev()
+    gen = torch.Generator().manual_seed(5)
+    x = torch.rand(2, 3, 10, 12, generator=gen) * 1.2 - 0.1
+    C = torch.exp(0.2 * torch.randn(2, 16, generator=gen))
+    gy = torch.randn(2, 3, 10, 12, generator=gen)
+    for cin, cout in ((0, 0), (0, 1), (2, 1), (2, 2)):
+        xr = x.clone().requires_grad_(True); Cr = C.clone().requires_grad_(True)
+        yr, rr = O.apply_curve(xr, Cr, 0.0, cin, cout)
+        torch.autograd.backward([yr, rr], [gy, torch.ones(2)])
+        xg = x.to(dev).requires_grad_(True); Cg = C.to(dev).requires_grad_(True)
+        yg, rg = V.apply_curve(xg, Cg, None, cin, cout)
+        torch.autograd.backward([yg, rg], [gy.to(dev), torch.ones(2, device=dev)])
+        assert (yg.cpu() - yr).abs().max().item() <= 1e-6
+        assert parity.rel_to_max(rg.detach().cpu().numpy(), rr.detach().numpy()) <= 1e-5
+        assert parity.rel_to_max(xg.grad.cpu().numpy(), xr.grad.numpy()) <= 1e-5
+        assert parity.rel_to_max(Cg.grad.cpu().numpy(), Cr.grad.numpy()) <= 1e-4
+
+
+@pytest.mark.parametrize("shape,maskdtype", [((4, 3, 64, 96), torch.bool), ((1, 3, 37, 53), torch.bool),
+                                             ((2, 3, 128, 128), None), ((2, 3, 40, 40), torch.float32)])
+def test_layer_vs_oracle_seeded(shape, maskdtype):
+    """Fresh seeded inputs (not in the fixtures), oracle evaluated on this box's CPU in fp32 and fp64."""
+    import curl_b200
+    from oracle import curl_oracle as O
+    dev = _dev()
+    gen = torch.Generator().manual_seed(1234 + shape[2])
+    B, _, H, W = shape
+    img = torch.rand(shape, generator=gen)
+    if maskdtype is None:
+        mask, omask = None, torch.ones(B, 1, H, W, dtype=torch.bool)
+    elif maskdtype == torch.bool:
+        mask = torch.rand(B, 1, H, W, generator=gen) > 0.1
+        omask = mask
+    else:
+        mask = (torch.rand(B, 1, H, W, generator=gen) > 0.1).float()
+        omask = mask
+    L, R, Hk = (0.1 * torch.randn(B, n, generator=gen) for n in (48, 48, 64))
+    gout = torch.randn(shape, generator=gen)
+    greg = torch.rand(B, generator=gen)
+    r32 = O.curl_layer_fwd_bwd(img, omask, L, R, Hk, gout, greg)
+    m64 = omask if omask.dtype == torch.bool else omask.double()
+    r64 = O.curl_layer_fwd_bwd(img.double(), m64, L.double(), R.double(), Hk.double(), gout.double(), greg.double())
+    layer = curl_b200.CURLLayer().to(dev)
+    ig = img.to(dev).requires_grad_(True)
+    Lg, Rg, Hg = (t.to(dev).requires_grad_(True) for t in (L, R, Hk))
+    out, reg = layer(ig, None if mask is None else mask.to(dev), Lg, Rg, Hg)
+    torch.autograd.backward([out, reg], [gout.to(dev), greg.to(dev)])
+    n = lambda t: t.detach().cpu().numpy()
+    rep = dict(out=parity.check_image("smooth", n(out), n(r32["out"]), n(r64["out"])))
+    gscale = float(r64["gimg"].abs().max())
+    rep["gimg"] = parity.check_image("smooth", n(ig.grad), n(r32["gimg"]), n(r64["gimg"]), scale=gscale)
+    for k, t in (("gL", Lg), ("gR", Rg), ("gH", Hg)):
+        rep[k] = parity.check_knots("smooth", n(t.grad), n(r32[k]), n(r64[k]))
+    REPORT[f"seeded.{shape}.{maskdtype}"] = rep
+
+
+def test_strided_knot_views_and_single_vector_form():
+    """GCURLNet passes column slices of one [B,160] tensor (model.py:197-199): no copy, same result."""
+    import curl_b200
+    dev = _dev()
+    gen = torch.Generator().manual_seed(9)
+    img = torch.rand(3, 3, 32, 48, generator=gen).to(dev)
+    cp = (0.1 * torch.randn(3, 160, generator=gen)).to(dev).requires_grad_(True)
+    layer = curl_b200.CURLLayer().to(dev)
+    out_a, reg_a = layer(img, cp)                       # forward(img, curve_params)
+    (out_a.sum() + reg_a.sum()).backward()
+    ga = cp.grad.clone()
+    L, R, H = (cp.detach()[:, a:b].contiguous().requires_grad_(True) for a, b in ((0, 48), (48, 96), (96, 160)))
+    out_b, reg_b = layer(img, torch.ones(3, 1, 32, 48, dtype=torch.bool, device=dev), L, R, H)
+    (out_b.sum() + reg_b.sum()).backward()
+    assert torch.equal(out_a, out_b) and torch.equal(reg_a, reg_b)
+    assert torch.equal(ga, torch.cat([L.grad, R.grad, H.grad], 1))
+
+
+def test_masked_pixels_are_zero_and_inputs_untouched():
+    import curl_b200
+    dev = _dev()
+    gen = torch.Generator().manual_seed(3)
+    img = torch.rand(2, 3, 64, 64, generator=gen).to(dev)
+    keep = img.clone()
+    mask = (torch.rand(2, 1, 64, 64, generator=gen) > 0.5).to(dev)
+    L, R, H = ((0.1 * torch.randn(2, n, generator=gen)).to(dev) for n in (48, 48, 64))
+    out, _ = curl_b200.CURLLayer().to(dev)(img, mask, L, R, H)
+    assert torch.equal(img, keep)
+    assert (out * (~mask)).abs().max().item() == 0.0
+    assert out.min().item() >= 0.0 and out.max().item() <= 1.0
+
+
+def test_full_size_properties():
+    """BASELINE config sizes (1080p batch 16 forward; 4K batch 4 fwd+bwd): size-independent checks --
+    range, mask zeros, determinism, batch-shard equality (no cross-image coupling), knot-gradient
+    additivity over pixels (gradient of two row-halves sums to the gradient of the whole)."""
+    import curl_b200
+    dev = _dev()
+    gen = torch.Generator(device=dev).manual_seed(1234)
+    layer = curl_b200.CURLLayer().to(dev)
+    B, H, W = 16, 1080, 1920
+    img = torch.rand(B, 3, H, W, generator=gen, device=dev)
+    mask = torch.rand(B, 1, H, W, generator=gen, device=dev) > 0.1
+    L, R, Hk = (0.1 * torch.randn(B, n, generator=gen, device=dev) for n in (48, 48, 64))
+    out, reg = layer(img, mask, L, R, Hk)
+    out2, reg2 = layer(img, mask, L, R, Hk)
+    assert torch.equal(out, out2) and torch.equal(reg, reg2)
+    assert out.min().item() >= 0.0 and out.max().item() <= 1.0
+    assert out.masked_select(~mask.expand_as(out)).abs().max().item() == 0.0
+    o_lo, r_lo = layer(img[:5], mask[:5], L[:5], R[:5], Hk[:5])      # shard == slice of the whole
+    assert torch.equal(o_lo, out[:5]) and torch.equal(r_lo, reg[:5])
+    del out2, o_lo
+
+    B, H, W = 4, 2160, 3840
+    img = torch.rand(B, 3, H, W, generator=gen, device=dev)
+    mask = torch.rand(B, 1, H, W, generator=gen, device=dev) > 0.1
+    Ls = [(0.1 * torch.randn(B, n, generator=gen, device=dev)).requires_grad_(True) for n in (48, 48, 64)]
+    gout = torch.randn(B, 3, H, W, generator=gen, device=dev)
+
+    def grads(sl):
+        for t in Ls:
+            t.grad = None
+        o, r = layer(img[:, :, sl].contiguous(), mask[:, :, sl].contiguous(), *Ls)
+        o.backward(gout[:, :, sl].contiguous())
+        return [t.grad.clone() for t in Ls]
+
+    whole = grads(slice(0, H))
+    again = grads(slice(0, H))
+    top, bot = grads(slice(0, H // 2)), grads(slice(H // 2, H))
+    for w, a, t, b in zip(whole, again, top, bot):
+        assert torch.equal(w, a)                                       # deterministic reduction
+        assert parity.rel_to_max((t + b).cpu().numpy(), w.cpu().numpy()) <= 1e-5
+
+
+def test_cuda_graph_capture():
+    import curl_b200
+    dev = _dev()
+    gen = torch.Generator().manual_seed(11)
+    layer = curl_b200.CURLLayer().to(dev)
+    img = torch.rand(2, 3, 64, 64, generator=gen).to(dev)
+    L, R, H = ((0.1 * torch.randn(2, n, generator=gen)).to(dev) for n in (48, 48, 64))
+    mask = torch.ones(2, 1, 64, 64, dtype=torch.bool, device=dev)
+    ref, _ = layer(img, mask, L, R, H)
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        layer(img, mask, L, R, H)
+    torch.cuda.current_stream().wait_stream(s)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        out, reg = layer(img, mask, L, R, H)
+    out.zero_()
+    graph.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(out, ref)
+
+
+def test_errors():
+    import curl_b200
+    dev = _dev()
+    layer = curl_b200.CURLLayer().to(dev)
+    img = torch.rand(1, 3, 8, 8, device=dev)
+    z = lambda n: torch.zeros(1, n, device=dev)
+    with pytest.raises(RuntimeError):
+        layer(img.cpu(), None, z(48), z(48), z(64))
+    with pytest.raises(TypeError):
+        layer(img.double(), None, z(48), z(48), z(64))
+    with pytest.raises(ValueError):
+        layer(img, None, z(47), z(48), z(64))
+    with pytest.raises(ValueError):
+        layer(img[:, :2], None, z(48), z(48), z(64))
+    with pytest.raises(ValueError):
+        layer(img, torch.ones(1, 3, 8, 8, device=dev), z(48), z(48), z(64))
+    # non-contiguous image is accepted (the reference calls .contiguous())
+    nc = torch.rand(1, 8, 8, 3, device=dev).permute(0, 3, 1, 2)
+    a, _ = layer(nc, None, z(48), z(48), z(64))
+    b, _ = layer(nc.contiguous(), None, z(48), z(48), z(64))
+    assert torch.equal(a, b)
+    # a checkpoint with different frozen constants is refused, not ignored
+    bad = curl_b200.CURLLayer().to(dev)
+    with torch.no_grad():
+        bad.rgb2lab.rgb_to_xyz.mul_(1.01)
+    with pytest.raises(RuntimeError):
+        bad(img, None, z(48), z(48), z(64))
