@@ -15,7 +15,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libcurl_b200.so")
 SOURCES = [os.path.join(CSRC, "curl_kernels.cu")]
-DEPS = SOURCES + [os.path.join(CSRC, "curl_pixel.cuh"), os.path.join(HERE, "..", "include", "curl_b200.h")]
+DEPS = SOURCES + [os.path.join(CSRC, "curl_pixel.cuh"), os.path.join(CSRC, "curl_vec.cuh"), os.path.join(HERE, "..", "include", "curl_b200.h")]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
@@ -42,7 +42,8 @@ def build(force=False, verbose=False):
     """Compile the library if missing or older than its sources.  Returns the path."""
     if not force and not is_stale():
         return LIB
-    cmd = [nvcc_path()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB] + SOURCES
+    extra = os.environ.get("CURL_NVCC_EXTRA", "").split()   # experiments only, e.g. -DBWD_MIN_BLOCKS=2
+    cmd = [nvcc_path()] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB] + SOURCES
     proc = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     if proc.returncode != 0:
         raise RuntimeError("nvcc failed:\n" + " ".join(cmd) + "\n" + proc.stdout)

@@ -15,6 +15,9 @@
 namespace curl {
 
 constexpr int THREADS = 256;
+#ifndef BWD_MIN_BLOCKS
+#define BWD_MIN_BLOCKS 1
+#endif
 constexpr int MAX_SEGS = 3;
 constexpr int MAX_CURVES = 10;
 
@@ -42,123 +45,140 @@ struct KParams {
 };
 
 // ---------------------------------------------------------------------------------------------
-// Ops
+// Ops.  T is the lane type: F2 (two pixels per value, packed FFMA2/FMUL2/FADD2) on the aligned
+// path, float on the unaligned tail path.
 // ---------------------------------------------------------------------------------------------
 struct OpLayer {
   static constexpr int NC = LAYER_CURVES;
-  template <int MK>
-  static __device__ __forceinline__ void fwd(const float x[3], float m, const float* ab, int, float y[3]) {
-    layer_fwd<DevMath, MK>(x, m, ab, y);
+  template <int MK, class T>
+  static __device__ __forceinline__ void fwd(const T x[3], T m, const float* ab, int, T y[3]) {
+    layer_fwd<T, MK>(x, m, ab, y);
   }
-  template <int MK>
-  static __device__ __forceinline__ void bwd(const float x[3], float m, const float* ab, int, const float gy[3],
-                                             float gx[3], float* mom) {
-    layer_bwd<DevMath, MK>(x, m, ab, gy, gx, mom);
+  template <int MK, bool WANT_GX, class T>
+  static __device__ __forceinline__ void bwd(const T x[3], T m, const float* ab, int, const T gy[3], T gx[3], T* mom) {
+    layer_bwd<T, MK, WANT_GX>(x, m, ab, gy, gx, mom);
   }
 };
 
 template <int CONV>
 struct OpColor {
   static constexpr int NC = 0;
-  template <int MK>
-  static __device__ __forceinline__ void fwd(const float x[3], float, const float*, int, float y[3]) {
-    if (CONV == CURL_RGB2LAB) rgb2lab_fwd<DevMath, false>(x, y, nullptr);
-    if (CONV == CURL_LAB2RGB) lab2rgb_fwd<DevMath, false>(x, y, nullptr);
-    if (CONV == CURL_RGB2HSV) rgb2hsv_fwd<DevMath, false, false>(x, y, nullptr);
-    if (CONV == CURL_HSV2RGB) hsv2rgb_fwd<DevMath, false, false>(x, y, nullptr);
+  template <int MK, class T>
+  static __device__ __forceinline__ void fwd(const T x[3], T, const float*, int, T y[3]) {
+    if (CONV == CURL_RGB2LAB) rgb2lab_fwd<T, false>(x, y, nullptr);
+    if (CONV == CURL_LAB2RGB) lab2rgb_fwd<T, false>(x, y, nullptr);
+    if (CONV == CURL_RGB2HSV) rgb2hsv_fwd<T, false, false>(x, y, nullptr);
+    if (CONV == CURL_HSV2RGB) hsv2rgb_fwd<T, false, false>(x, y, nullptr);
   }
-  template <int MK>
-  static __device__ __forceinline__ void bwd(const float x[3], float, const float*, int, const float gy[3],
-                                             float gx[3], float*) {
-    float y[3];
-    if (CONV == CURL_RGB2LAB) { LabJac j; rgb2lab_fwd<DevMath, true>(x, y, &j); rgb2lab_bwd(j, gy, gx); }
-    if (CONV == CURL_LAB2RGB) { RgbJac j; lab2rgb_fwd<DevMath, true>(x, y, &j); lab2rgb_bwd(j, gy, gx); }
-    if (CONV == CURL_RGB2HSV) { HsvJac j; rgb2hsv_fwd<DevMath, true, false>(x, y, &j); rgb2hsv_bwd(j, gy, gx); }
-    if (CONV == CURL_HSV2RGB) { Hsv2RgbJac j; hsv2rgb_fwd<DevMath, true, false>(x, y, &j); hsv2rgb_bwd(j, gy, gx); }
+  template <int MK, bool WANT_GX, class T>
+  static __device__ __forceinline__ void bwd(const T x[3], T, const float*, int, const T gy[3], T gx[3], T*) {
+    T y[3];
+    if (CONV == CURL_RGB2LAB) { LabJac<T> j; rgb2lab_fwd<T, true>(x, y, &j); rgb2lab_bwd(j, gy, gx); }
+    if (CONV == CURL_LAB2RGB) { RgbJac<T> j; lab2rgb_fwd<T, true>(x, y, &j); lab2rgb_bwd(j, gy, gx); }
+    if (CONV == CURL_RGB2HSV) { HsvJac<T> j; rgb2hsv_fwd<T, true, false>(x, y, &j); rgb2hsv_bwd(j, gy, gx); }
+    if (CONV == CURL_HSV2RGB) { Hsv2RgbJac<T> j; hsv2rgb_fwd<T, true, false>(x, y, &j); hsv2rgb_bwd<T, false>(j, gy, gx); }
   }
 };
 
 struct OpAdjustSelf3 {  // adjust_lab, adjust_rgb
   static constexpr int NC = 3;
-  template <int MK>
-  static __device__ __forceinline__ void fwd(const float x[3], float, const float* ab, int, float y[3]) {
-    adjust_self3_fwd<DevMath, false>(x, ab, y, nullptr);
+  template <int MK, class T>
+  static __device__ __forceinline__ void fwd(const T x[3], T, const float* ab, int, T y[3]) {
+    adjust_self3_fwd<T, false>(x, ab, y, nullptr);
   }
-  template <int MK>
-  static __device__ __forceinline__ void bwd(const float x[3], float, const float* ab, int, const float gy[3],
-                                             float gx[3], float* mom) {
-    float y[3]; Self3Jac j;
-    adjust_self3_fwd<DevMath, true>(x, ab, y, &j);
+  template <int MK, bool WANT_GX, class T>
+  static __device__ __forceinline__ void bwd(const T x[3], T, const float* ab, int, const T gy[3], T gx[3], T* mom) {
+    T y[3]; Self3Jac<T> j;
+    adjust_self3_fwd<T, true>(x, ab, y, &j);
     adjust_self3_bwd(j, gy, gx, mom);
   }
 };
 
 struct OpAdjustHsv {
   static constexpr int NC = 4;
-  template <int MK>
-  static __device__ __forceinline__ void fwd(const float x[3], float, const float* ab, int, float y[3]) {
-    adjust_hsv_fwd<DevMath, false, false>(x, ab, y, nullptr);
+  template <int MK, class T>
+  static __device__ __forceinline__ void fwd(const T x[3], T, const float* ab, int, T y[3]) {
+    adjust_hsv_fwd<T, false, false>(x, ab, y, nullptr);
   }
-  template <int MK>
-  static __device__ __forceinline__ void bwd(const float x[3], float, const float* ab, int, const float gy[3],
-                                             float gx[3], float* mom) {
-    float y[3]; HsvCurveJac j;
-    adjust_hsv_fwd<DevMath, true, false>(x, ab, y, &j);
+  template <int MK, bool WANT_GX, class T>
+  static __device__ __forceinline__ void bwd(const T x[3], T, const float* ab, int, const T gy[3], T gx[3], T* mom) {
+    T y[3]; HsvCurveJac<T> j;
+    adjust_hsv_fwd<T, true, false>(x, ab, y, &j);
     adjust_hsv_bwd(j, ab, gy, gx, mom);
   }
 };
 
 struct OpCurve1 {  // curves.apply_curve: one curve channel_in -> channel_out, knots given as C
   static constexpr int NC = 1;
-  template <int MK>
-  static __device__ __forceinline__ void fwd(const float x[3], float, const float* ab, int aux, float y[3]) {
-    single_curve_fwd<DevMath>(x, aux & 3, (aux >> 2) & 3, ab[0], ab[1], y);
+  template <int MK, class T>
+  static __device__ __forceinline__ void fwd(const T x[3], T, const float* ab, int aux, T y[3]) {
+    single_curve_fwd<T>(x, aux & 3, (aux >> 2) & 3, ab[0], ab[1], y);
   }
-  template <int MK>
-  static __device__ __forceinline__ void bwd(const float x[3], float, const float* ab, int aux, const float gy[3],
-                                             float gx[3], float* mom) {
-    single_curve_bwd<DevMath>(x, aux & 3, (aux >> 2) & 3, ab[0], ab[1], gy, gx, mom);
+  template <int MK, bool WANT_GX, class T>
+  static __device__ __forceinline__ void bwd(const T x[3], T, const float* ab, int aux, const T gy[3], T gx[3], T* mom) {
+    single_curve_bwd<T>(x, aux & 3, (aux >> 2) & 3, ab[0], ab[1], gy, gx, mom);
   }
 };
 
 // ---------------------------------------------------------------------------------------------
-// Vector access helpers (streaming: every byte is touched exactly once)
+// Pixel groups: what one thread handles per loop iteration (streaming 128-bit accesses: every
+// byte is touched exactly once).  Group<4>: four consecutive pixels as two packed F2 lanes.
 // ---------------------------------------------------------------------------------------------
-template <int VEC> struct Px;
-template <> struct Px<4> {
-  float v[4];
-  static __device__ __forceinline__ Px ld(const float* p) {
+template <int VEC> struct Group;
+template <> struct Group<4> {
+  using T = F2;
+  static constexpr int LANES = 2;   // values of type T per channel
+  T v[2];
+  static __device__ __forceinline__ Group ld(const float* p) {
     const float4 t = __ldcs(reinterpret_cast<const float4*>(p));
-    Px r; r.v[0] = t.x; r.v[1] = t.y; r.v[2] = t.z; r.v[3] = t.w; return r;
+    Group r; r.v[0] = F2(t.x, t.y); r.v[1] = F2(t.z, t.w); return r;
   }
   __device__ __forceinline__ void st(float* p) const {
-    __stcs(reinterpret_cast<float4*>(p), make_float4(v[0], v[1], v[2], v[3]));
+    __stcs(reinterpret_cast<float4*>(p), make_float4(v[0].lo(), v[0].hi(), v[1].lo(), v[1].hi()));
   }
 };
-template <> struct Px<1> {
-  float v[1];
-  static __device__ __forceinline__ Px ld(const float* p) { Px r; r.v[0] = __ldcs(p); return r; }
+template <> struct Group<2> {   // two consecutive pixels: one packed lane, 64-bit accesses
+  using T = F2;
+  static constexpr int LANES = 1;
+  T v[1];
+  static __device__ __forceinline__ Group ld(const float* p) {
+    const float2 t = __ldcs(reinterpret_cast<const float2*>(p));
+    Group r; r.v[0] = F2(t.x, t.y); return r;
+  }
+  __device__ __forceinline__ void st(float* p) const {
+    __stcs(reinterpret_cast<float2*>(p), make_float2(v[0].lo(), v[0].hi()));
+  }
+};
+template <> struct Group<1> {
+  using T = float;
+  static constexpr int LANES = 1;
+  T v[1];
+  static __device__ __forceinline__ Group ld(const float* p) { Group r; r.v[0] = __ldcs(p); return r; }
   __device__ __forceinline__ void st(float* p) const { __stcs(p, v[0]); }
 };
 
 template <int MK, int VEC>
-__device__ __forceinline__ void load_mask(const void* mask, size_t idx, float m[VEC]) {
+__device__ __forceinline__ Group<VEC> load_mask(const void* mask, size_t idx) {
+  Group<VEC> g;
   if (MK == MASK_NONE) {
 #pragma unroll
-    for (int i = 0; i < VEC; ++i) m[i] = 1.0f;
+    for (int i = 0; i < Group<VEC>::LANES; ++i) g.v[i] = typename Group<VEC>::T(1.0f);
   } else if (MK == MASK_U8) {
     const unsigned char* p = reinterpret_cast<const unsigned char*>(mask) + idx;
-    if (VEC == 4) {
+    if constexpr (VEC == 4) {
       const uchar4 t = __ldcs(reinterpret_cast<const uchar4*>(p));
-      m[0] = t.x ? 1.0f : 0.0f; m[1 % VEC] = t.y ? 1.0f : 0.0f; m[2 % VEC] = t.z ? 1.0f : 0.0f; m[3 % VEC] = t.w ? 1.0f : 0.0f;
+      g.v[0] = F2(t.x ? 1.0f : 0.0f, t.y ? 1.0f : 0.0f);
+      g.v[1] = F2(t.z ? 1.0f : 0.0f, t.w ? 1.0f : 0.0f);
+    } else if constexpr (VEC == 2) {
+      const uchar2 t = __ldcs(reinterpret_cast<const uchar2*>(p));
+      g.v[0] = F2(t.x ? 1.0f : 0.0f, t.y ? 1.0f : 0.0f);
     } else {
-      m[0] = __ldcs(p) ? 1.0f : 0.0f;
+      g.v[0] = __ldcs(p) ? 1.0f : 0.0f;
     }
   } else {
-    const Px<VEC> t = Px<VEC>::ld(reinterpret_cast<const float*>(mask) + idx);
-#pragma unroll
-    for (int i = 0; i < VEC; ++i) m[i] = t.v[i];
+    g = Group<VEC>::ld(reinterpret_cast<const float*>(mask) + idx);
   }
+  return g;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -214,19 +234,78 @@ __global__ void __launch_bounds__(THREADS) fwd_kernel(const KParams p) {
   const float* in = p.in + (size_t)b * 3 * HW;
   float* out = p.out + (size_t)b * 3 * HW;
   const int stride = gridDim.x * THREADS * VEC;
+  using G = Group<VEC>;
+  using T = typename G::T;
   for (int i = (blockIdx.x * THREADS + threadIdx.x) * VEC; i < HW; i += stride) {
-    const Px<VEC> c0 = Px<VEC>::ld(in + i), c1 = Px<VEC>::ld(in + HW + i), c2 = Px<VEC>::ld(in + 2 * (size_t)HW + i);
-    float m[VEC];
-    load_mask<MK, VEC>(p.mask, (size_t)b * HW + i, m);
-    Px<VEC> o0, o1, o2;
+    const G c0 = G::ld(in + i), c1 = G::ld(in + HW + i), c2 = G::ld(in + 2 * (size_t)HW + i);
+    const G m = load_mask<MK, VEC>(p.mask, (size_t)b * HW + i);
+    G o0, o1, o2;
 #pragma unroll
-    for (int v = 0; v < VEC; ++v) {
-      const float x[3] = {c0.v[v], c1.v[v], c2.v[v]};
-      float y[3];
-      Op::template fwd<MK>(x, m[v], s_ab, p.aux, y);
+    for (int v = 0; v < G::LANES; ++v) {
+      const T x[3] = {c0.v[v], c1.v[v], c2.v[v]};
+      T y[3];
+      Op::template fwd<MK, T>(x, m.v[v], s_ab, p.aux, y);
       o0.v[v] = y[0]; o1.v[v] = y[1]; o2.v[v] = y[2];
     }
     o0.st(out + i); o1.st(out + HW + i); o2.st(out + 2 * (size_t)HW + i);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Knot-gradient reduction shared by the backward kernels: per-thread registers -> warp shuffles ->
+// shared memory -> one partial row per block -> ONE atomic ticket per block -> the last block of the
+// image folds all partial rows in a fixed order (in double, bitwise deterministic) and expands the
+// 2 moments per curve into the knot gradients (curve_knot_grad).
+// ---------------------------------------------------------------------------------------------
+template <int NC, class T>
+__device__ __forceinline__ void finish_knot_grads(const KParams& p, int b, const T* mom, const float* s_C,
+                                                  double* s_mom, float* s_part, unsigned* s_ticket_p) {
+  constexpr int NM = 2 * NC;
+  constexpr int NWARPS = THREADS / 32;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < NM; ++k) {
+    float v = vhsum(mom[k]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) s_part[warp * NM + k] = v;
+  }
+  __syncthreads();
+  float* row = p.partials + ((size_t)b * gridDim.x + blockIdx.x) * NM;
+  if (threadIdx.x < NM) {
+    float v = 0.0f;
+#pragma unroll
+    for (int w = 0; w < NWARPS; ++w) v += s_part[w * NM + threadIdx.x];
+    row[threadIdx.x] = v;
+    __threadfence();
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) *s_ticket_p = atomicAdd(&p.tickets[b], 1u);
+  __syncthreads();
+  if (*s_ticket_p != gridDim.x - 1) return;
+  __threadfence();
+  // last block of image b: fixed-order fold of the partial rows
+  const float* rows = p.partials + (size_t)b * gridDim.x * NM;
+  for (int k = warp; k < NM; k += NWARPS) {
+    double acc = 0.0;
+    for (unsigned r = lane; r < gridDim.x; r += 32) acc += (double)__ldcg(rows + (size_t)r * NM + k);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0) s_mom[k] = acc;
+  }
+  __syncthreads();
+  const double greg = p.greg ? (double)p.greg[b] : 0.0;
+  int cbase = 0, off = 0;
+  for (int s = 0; s < p.nseg; ++s) {
+    const int K = p.seg[s].K, n = p.seg[s].nc * K;
+    float* g = p.seg[s].g + (size_t)b * n;
+    for (int i = threadIdx.x; i < n; i += THREADS) {
+      const int c = i / K, kk = i - c * K;
+      g[i] = curve_knot_grad(s_C + off + c * K, K, kk, s_mom[2 * (cbase + c)], s_mom[2 * (cbase + c) + 1], greg,
+                             p.linear_knots == 0);
+    }
+    cbase += p.seg[s].nc;
+    off += n;
   }
 }
 
@@ -236,7 +315,7 @@ __global__ void __launch_bounds__(THREADS) fwd_kernel(const KParams p) {
 // image folds all partial rows in a fixed order (in double) and writes the knot gradients.
 // ---------------------------------------------------------------------------------------------
 template <class Op, int MK, int VEC, bool WANT_GIN>
-__global__ void __launch_bounds__(THREADS) bwd_kernel(const KParams p) {
+__global__ void __launch_bounds__(THREADS, BWD_MIN_BLOCKS) bwd_kernel(const KParams p) {
   constexpr int NC = Op::NC;
   constexpr int NM = 2 * NC;
   constexpr int NWARPS = THREADS / 32;
@@ -248,9 +327,11 @@ __global__ void __launch_bounds__(THREADS) bwd_kernel(const KParams p) {
   const int b = blockIdx.y;
   if (NC > 0) stage_curves<NC>(p, b, s_C, s_ab, nullptr, false);
 
-  float mom[NM > 0 ? NM : 1];
+  using G = Group<VEC>;
+  using T = typename G::T;
+  T mom[NM > 0 ? NM : 1];
 #pragma unroll
-  for (int k = 0; k < NM; ++k) mom[k] = 0.0f;
+  for (int k = 0; k < NM; ++k) mom[k] = T(0.0f);
 
   const int HW = p.HW;
   const float* in = p.in + (size_t)b * 3 * HW;
@@ -258,69 +339,164 @@ __global__ void __launch_bounds__(THREADS) bwd_kernel(const KParams p) {
   float* gin = WANT_GIN ? p.out + (size_t)b * 3 * HW : nullptr;
   const int stride = gridDim.x * THREADS * VEC;
   for (int i = (blockIdx.x * THREADS + threadIdx.x) * VEC; i < HW; i += stride) {
-    const Px<VEC> c0 = Px<VEC>::ld(in + i), c1 = Px<VEC>::ld(in + HW + i), c2 = Px<VEC>::ld(in + 2 * (size_t)HW + i);
-    const Px<VEC> g0 = Px<VEC>::ld(go + i), g1 = Px<VEC>::ld(go + HW + i), g2 = Px<VEC>::ld(go + 2 * (size_t)HW + i);
-    float m[VEC];
-    load_mask<MK, VEC>(p.mask, (size_t)b * HW + i, m);
-    Px<VEC> o0, o1, o2;
+    const G c0 = G::ld(in + i), c1 = G::ld(in + HW + i), c2 = G::ld(in + 2 * (size_t)HW + i);
+    const G g0 = G::ld(go + i), g1 = G::ld(go + HW + i), g2 = G::ld(go + 2 * (size_t)HW + i);
+    const G m = load_mask<MK, VEC>(p.mask, (size_t)b * HW + i);
+    G o0, o1, o2;
 #pragma unroll
-    for (int v = 0; v < VEC; ++v) {
-      const float x[3] = {c0.v[v], c1.v[v], c2.v[v]};
-      const float gy[3] = {g0.v[v], g1.v[v], g2.v[v]};
-      float gx[3];
-      Op::template bwd<MK>(x, m[v], s_ab, p.aux, gy, gx, mom);
+    for (int v = 0; v < G::LANES; ++v) {
+      const T x[3] = {c0.v[v], c1.v[v], c2.v[v]};
+      const T gy[3] = {g0.v[v], g1.v[v], g2.v[v]};
+      T gx[3];
+      Op::template bwd<MK, WANT_GIN, T>(x, m.v[v], s_ab, p.aux, gy, gx, mom);
       o0.v[v] = gx[0]; o1.v[v] = gx[1]; o2.v[v] = gx[2];
     }
     if (WANT_GIN) { o0.st(gin + i); o1.st(gin + HW + i); o2.st(gin + 2 * (size_t)HW + i); }
   }
 
-  if (NC > 0) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (NC > 0) finish_knot_grads<NC, T>(p, b, mom, s_C, s_mom, s_part, &s_ticket);
+}
+
+// ---------------------------------------------------------------------------------------------
+// TMA (bulk async copy) helpers.  The backward kernel needs ~230 registers per thread, so only 8
+// warps fit on an SM: far too few to hide HBM latency with ordinary loads.  Instead one elected
+// thread streams each tile's six input planes into a shared-memory ring with cp.async.bulk
+// (SASS UBLKCP), completion tracked by an mbarrier per stage; the loads of the next STAGES-1 tiles
+// are always in flight and cost no registers.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, unsigned long long* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
+constexpr int TMA_TILE = THREADS * 2;   // pixels per tile: one packed pair per thread
+constexpr int TMA_STAGES = 6;
+constexpr int TMA_PLANES = 6;           // x0 x1 x2 g0 g1 g2
+constexpr size_t TMA_SMEM_BYTES = (size_t)TMA_STAGES * TMA_PLANES * TMA_TILE * sizeof(float);
+
+// Backward, aligned path (HW % 4 == 0, 16-byte aligned bases).  Same math as bwd_kernel<.., 2, ..>.
+template <class Op, int MK, bool WANT_GIN>
+__global__ void __launch_bounds__(THREADS, BWD_MIN_BLOCKS) bwd_tma_kernel(const KParams p) {
+  constexpr int NC = Op::NC;
+  constexpr int NM = 2 * NC;
+  constexpr int NWARPS = THREADS / 32;
+  extern __shared__ __align__(128) float s_ring[];   // [STAGES][PLANES][TILE]
+  __shared__ __align__(8) unsigned long long s_full[TMA_STAGES];
+  __shared__ float s_C[NC > 0 ? CURL_MAX_KNOTS : 1];
+  __shared__ float s_ab[NC > 0 ? 2 * NC : 1];
+  __shared__ double s_mom[NC > 0 ? NM : 1];
+  __shared__ float s_part[NC > 0 ? NWARPS * NM : 1];
+  __shared__ unsigned s_ticket;
+  const int b = blockIdx.y;
+  const int HW = p.HW;
+  const float* in = p.in + (size_t)b * 3 * HW;
+  const float* go = p.gout + (size_t)b * 3 * HW;
+  float* gin = WANT_GIN ? p.out + (size_t)b * 3 * HW : nullptr;
+  const int n_tiles = (HW + TMA_TILE - 1) / TMA_TILE;
+  const int n_my = ((int)blockIdx.x < n_tiles) ? (n_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+
+  auto issue = [&](int it) {   // called by thread 0 only
+    const int s = it % TMA_STAGES;
+    const int px0 = (blockIdx.x + it * gridDim.x) * TMA_TILE;
+    const int n = min(TMA_TILE, HW - px0);
+    const unsigned bytes = (unsigned)n * sizeof(float);
+    float* dst = s_ring + (size_t)s * TMA_PLANES * TMA_TILE;
+    mbar_expect_tx(&s_full[s], bytes * TMA_PLANES);
 #pragma unroll
-    for (int k = 0; k < NM; ++k) {
-      float v = mom[k];
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-      if (lane == 0) s_part[warp * NM + k] = v;
+    for (int c = 0; c < 3; ++c) {
+      bulk_g2s(dst + c * TMA_TILE, in + (size_t)c * HW + px0, bytes, &s_full[s]);
+      bulk_g2s(dst + (3 + c) * TMA_TILE, go + (size_t)c * HW + px0, bytes, &s_full[s]);
     }
-    __syncthreads();
-    float* row = p.partials + ((size_t)b * gridDim.x + blockIdx.x) * NM;
-    if (threadIdx.x < NM) {
-      float v = 0.0f;
+  };
+
+  if (threadIdx.x == 0) {
 #pragma unroll
-      for (int w = 0; w < NWARPS; ++w) v += s_part[w * NM + threadIdx.x];
-      row[threadIdx.x] = v;
-      __threadfence();
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) s_ticket = atomicAdd(&p.tickets[b], 1u);
-    __syncthreads();
-    if (s_ticket != gridDim.x - 1) return;
-    __threadfence();
-    // last block of image b: fixed-order fold of the partial rows
-    const float* rows = p.partials + (size_t)b * gridDim.x * NM;
-    for (int k = warp; k < NM; k += NWARPS) {
-      double acc = 0.0;
-      for (unsigned r = lane; r < gridDim.x; r += 32) acc += (double)__ldcg(rows + (size_t)r * NM + k);
+    for (int s = 0; s < TMA_STAGES; ++s) mbar_init(&s_full[s], 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+  if (threadIdx.x == 0)
+    for (int it = 0; it < TMA_STAGES && it < n_my; ++it) issue(it);
+  if (NC > 0) stage_curves<NC>(p, b, s_C, s_ab, nullptr, false);
+
+  using T = F2;
+  T mom[NM > 0 ? NM : 1];
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-      if (lane == 0) s_mom[k] = acc;
+  for (int k = 0; k < NM; ++k) mom[k] = T(0.0f);
+
+  // The mask plane is only 4-byte aligned in general, so it cannot ride the bulk copies; it is
+  // fetched with an ordinary load one whole iteration ahead (raw bits kept in one register pair).
+  auto mask_raw = [&](int it) -> float2 {
+    const int px = (blockIdx.x + it * gridDim.x) * TMA_TILE + threadIdx.x * 2;
+    float2 r = make_float2(1.0f, 1.0f);
+    if (MK == MASK_NONE || it >= n_my || px >= HW) return r;
+    if (MK == MASK_U8) {
+      const unsigned short u = __ldcs(reinterpret_cast<const unsigned short*>(
+          reinterpret_cast<const unsigned char*>(p.mask) + (size_t)b * HW + px));
+      r.x = __uint_as_float((unsigned)u);
+    } else {
+      r = __ldcs(reinterpret_cast<const float2*>(reinterpret_cast<const float*>(p.mask) + (size_t)b * HW + px));
     }
-    __syncthreads();
-    const double greg = p.greg ? (double)p.greg[b] : 0.0;
-    int cbase = 0, off = 0;
-    for (int s = 0; s < p.nseg; ++s) {
-      const int K = p.seg[s].K, n = p.seg[s].nc * K;
-      float* g = p.seg[s].g + (size_t)b * n;
-      for (int i = threadIdx.x; i < n; i += THREADS) {
-        const int c = i / K, kk = i - c * K;
-        g[i] = curve_knot_grad(s_C + off + c * K, K, kk, s_mom[2 * (cbase + c)], s_mom[2 * (cbase + c) + 1], greg,
-                               p.linear_knots == 0);
-      }
-      cbase += p.seg[s].nc;
-      off += n;
+    return r;
+  };
+  float2 m_next = mask_raw(0);
+
+  for (int it = 0; it < n_my; ++it) {
+    const int s = it % TMA_STAGES;
+    const int px = (blockIdx.x + it * gridDim.x) * TMA_TILE + threadIdx.x * 2;
+    const bool valid = px < HW;     // HW is even: a pair is either fully inside or fully outside
+    const float2 m_raw = m_next;
+    m_next = mask_raw(it + 1);
+    T m = T(1.0f);
+    if (MK == MASK_U8) {
+      const unsigned u = __float_as_uint(m_raw.x);
+      m = F2((u & 0xffu) ? 1.0f : 0.0f, (u & 0xff00u) ? 1.0f : 0.0f);
+    } else if (MK == MASK_F32) {
+      m = F2(m_raw.x, m_raw.y);
+    }
+    mbar_wait(&s_full[s], (unsigned)(it / TMA_STAGES) & 1u);
+    const float* src = s_ring + (size_t)s * TMA_PLANES * TMA_TILE + threadIdx.x * 2;
+    T x[3], gy[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const float2 a = *reinterpret_cast<const float2*>(src + c * TMA_TILE);
+      const float2 g = *reinterpret_cast<const float2*>(src + (3 + c) * TMA_TILE);
+      x[c] = valid ? F2(a.x, a.y) : F2(0.5f);
+      gy[c] = valid ? F2(g.x, g.y) : F2(0.0f);
+    }
+    __syncthreads();                                    // every thread has read stage s
+    if (threadIdx.x == 0 && it + TMA_STAGES < n_my) issue(it + TMA_STAGES);
+    if (!valid) m = T(0.0f);
+    T gx[3];
+    Op::template bwd<MK, WANT_GIN, T>(x, m, s_ab, p.aux, gy, gx, mom);
+    if (WANT_GIN && valid) {
+#pragma unroll
+      for (int c = 0; c < 3; ++c)
+        __stcs(reinterpret_cast<float2*>(gin + (size_t)c * HW + px), make_float2(gx[c].lo(), gx[c].hi()));
     }
   }
+  if (NC > 0) finish_knot_grads<NC, T>(p, b, mom, s_C, s_mom, s_part, &s_ticket);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -350,6 +526,7 @@ static int blocks_per_image(int B, int HW, int vec, int blocks_per_sm) {
 }
 
 constexpr int BWD_GRID_BLOCKS_PER_SM = 8;
+constexpr int BWD_VEC = 2;   // pixels per thread per iteration on the aligned backward path
 constexpr int FWD_GRID_BLOCKS_PER_SM = 16;
 
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
@@ -370,7 +547,7 @@ static int bwd_grid_x(int B, int HW, int vec) { return blocks_per_image(B, HW, v
 
 template <class Op, int MK>
 static int launch_bwd(KParams& p, int B, bool vec4, void* ws, size_t ws_bytes, cudaStream_t st) {
-  const int vec = vec4 ? 4 : 1;
+  const int vec = vec4 ? BWD_VEC : 1;
   dim3 grid(bwd_grid_x(B, p.HW, vec), B);
   if (Op::NC > 0) {
     const size_t tick_bytes = ((size_t)B * sizeof(unsigned) + 255) / 256 * 256;
@@ -382,8 +559,15 @@ static int launch_bwd(KParams& p, int B, bool vec4, void* ws, size_t ws_bytes, c
   }
   const bool want = p.out != nullptr;
   if (vec4) {
-    if (want) bwd_kernel<Op, MK, 4, true><<<grid, THREADS, 0, st>>>(p);
-    else bwd_kernel<Op, MK, 4, false><<<grid, THREADS, 0, st>>>(p);
+    if (want) {
+      if (cudaFuncSetAttribute(bwd_tma_kernel<Op, MK, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               (int)TMA_SMEM_BYTES) != cudaSuccess) return CURL_ERR_LAUNCH;
+      bwd_tma_kernel<Op, MK, true><<<grid, THREADS, TMA_SMEM_BYTES, st>>>(p);
+    } else {
+      if (cudaFuncSetAttribute(bwd_tma_kernel<Op, MK, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               (int)TMA_SMEM_BYTES) != cudaSuccess) return CURL_ERR_LAUNCH;
+      bwd_tma_kernel<Op, MK, false><<<grid, THREADS, TMA_SMEM_BYTES, st>>>(p);
+    }
   } else {
     if (want) bwd_kernel<Op, MK, 1, true><<<grid, THREADS, 0, st>>>(p);
     else bwd_kernel<Op, MK, 1, false><<<grid, THREADS, 0, st>>>(p);
@@ -430,7 +614,7 @@ size_t curl_bwd_workspace_bytes(int B, int H, int W) {
   // sized for the scalar path (most blocks) and the widest op (the layer: 20 moments)
   const int HW = H * W;
   int gx = bwd_grid_x(B, HW, 1);
-  const int gx4 = bwd_grid_x(B, HW, 4);
+  const int gx4 = bwd_grid_x(B, HW, BWD_VEC);
   if (gx4 > gx) gx = gx4;
   const size_t tick_bytes = ((size_t)B * sizeof(unsigned) + 255) / 256 * 256;
   return tick_bytes + (size_t)B * gx * 2 * LAYER_CURVES * sizeof(float);

@@ -1,22 +1,22 @@
 // Per-pixel arithmetic of the CURL curve layer: colour conversions, affine knot curves, and their
-// hand-derived reverse-mode derivatives.  Everything here is a pure function of one pixel (plus
-// the per-image curve coefficients), written once and instantiated
-//   * in the sm_100a kernels (curl_kernels.cu) with DevMath  -> MUFU.LG2 / MUFU.EX2 / MUFU.RCP,
-//   * in the host-side derivation check (tests/hostsim) with HostMath -> double-precision libm,
-//     which is test infrastructure only and is never linked into the product library.
+// hand-derived reverse-mode derivatives.  Everything here is a pure function of one pixel (or, with
+// the packed lane type F2, of two pixels) plus the per-image curve coefficients.  It is written once
+// as templates over the lane type T (curl_vec.cuh) and instantiated
+//   * in the sm_100a kernels (curl_kernels.cu) with T = F2 (FFMA2/FMUL2/FADD2 + MUFU) and
+//     T = float (unaligned tail path),
+//   * in the host-side derivation check (tests/hostsim) with T = float on the CPU, which is test
+//     infrastructure only and is never linked into the product library.
 //
 // Semantics follow the reference (danielbulhosa/CURL) line by line; citations are file:line in
 // that tree.  Where the reference evaluates "both branches * 0/1 mask" the kernel uses a select,
 // which is value-identical for finite data.
+//
+// Backward convention: every forward stage can emit a small "Jac" record holding the local
+// derivative factors with all clamp gates (inclusive: torch.clamp passes gradient on [lo, hi]) and
+// branch selectors already multiplied in, so the reverse sweep is straight-line packed arithmetic.
 #pragma once
 
-#if defined(__CUDACC__)
-#define CURL_HD __host__ __device__ __forceinline__
-#else
-#define CURL_HD inline
-#endif
-
-#include <math.h>
+#include "curl_vec.cuh"
 
 namespace curl {
 
@@ -29,13 +29,17 @@ constexpr float SRGB_T = 0.04045f;                       // colors.py:37
 constexpr float SRGB_INV_SLOPE = (float)(1.0 / 12.92);   // colors.py:37
 constexpr float SRGB_A = (float)(1.0 / 1.055);           // colors.py:38  (x + 0.055) / 1.055
 constexpr float SRGB_B = (float)(0.055 / 1.055);
+constexpr float SRGB_DK = (float)(2.4 / 1.055);          // d/dx u^2.4 = 2.4/1.055 u^1.4
 constexpr float F_T = (float)(EPS * EPS * EPS);          // colors.py:45
 constexpr float F_SLOPE = (float)(1.0 / (3.0 * EPS * EPS));
 constexpr float F_OFF = (float)(4.0 / 29.0);
 constexpr float FINV_T = (float)EPS;                     // colors.py:110
 constexpr float FINV_SLOPE = (float)(3.0 * EPS * EPS);
+constexpr float FINV_OFF = (float)(-3.0 * EPS * EPS * 4.0 / 29.0);
 constexpr float LIN_T = 0.0031308f;                      // colors.py:118
 constexpr float LIN_SLOPE = 12.92f;
+constexpr float GAM_E = (float)(1.0 / 2.4 - 1.0);        // v^(1/2.4) = v * v^(1/2.4 - 1)
+constexpr float GAM_DK = (float)(1.055 / 2.4);
 // RGB -> XYZ (colors.py:8-13), each column pre-divided by the D65 white (colors.py:24,41).
 constexpr double WX = 0.950456, WY = 1.0, WZ = 1.088754;
 constexpr float M00 = (float)(0.412453 / WX), M10 = (float)(0.357580 / WX), M20 = (float)(0.180423 / WX);
@@ -56,41 +60,6 @@ constexpr float N01 = (float)(-0.9692660 * WX), N11 = (float)(1.8760108 * WY), N
 constexpr float N02 = (float)(0.0556434 * WX), N12 = (float)(-0.2040259 * WY), N22 = (float)(1.0572252 * WZ);
 constexpr float HSV_LO = 1e-9f;                          // colors.py:205,240
 }  // namespace k
-
-// ------------------------------------------------------------------------------------------------
-// Math policies
-// ------------------------------------------------------------------------------------------------
-#if defined(__CUDACC__)
-struct DevMath {
-  static __device__ __forceinline__ float lg2(float x) {
-    float y;
-    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-    return y;
-  }
-  static __device__ __forceinline__ float ex2(float x) {
-    float y;
-    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-    return y;
-  }
-  static __device__ __forceinline__ float rcp(float x) {
-    float y;
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-    return y;
-  }
-  static __device__ __forceinline__ float sat(float x) { return __saturatef(x); }
-  static __device__ __forceinline__ float fmax_(float a, float b) { return fmaxf(a, b); }
-  static __device__ __forceinline__ float fmin_(float a, float b) { return fminf(a, b); }
-};
-#endif
-
-struct HostMath {  // test-only: correctly rounded stand-ins for the MUFU ops
-  static inline float lg2(float x) { return (float)log2((double)x); }
-  static inline float ex2(float x) { return (float)exp2((double)x); }
-  static inline float rcp(float x) { return (float)(1.0 / (double)x); }
-  static inline float sat(float x) { return x < 0.f ? 0.f : (x > 1.f ? 1.f : (x == x ? x : 0.f)); }
-  static inline float fmax_(float a, float b) { return a > b ? a : b; }
-  static inline float fmin_(float a, float b) { return a < b ? a : b; }
-};
 
 enum MaskKind { MASK_NONE = 0, MASK_U8 = 1, MASK_F32 = 2 };
 
@@ -140,191 +109,176 @@ CURL_HD float curve_knot_grad(const float* C, int K, int i, double S0, double S1
 
 // ------------------------------------------------------------------------------------------------
 // Stage: RGB -> normalised Lab            (reference colors.py:27-62)
+// Powers share one MUFU.LG2 + one MUFU.EX2 between value and derivative:
+//   u^2.4 = u * u^1.4, u^1.4 = u * 2^(0.4 lg u);   t^(1/3) = t * t^(-2/3), t^(-2/3) = 2^(-2/3 lg t).
 // ------------------------------------------------------------------------------------------------
-struct LabJac {   // local derivatives kept by the backward pass
-  float d_lin[3];  // d lin_c / d x_c
-  float d_f[3];    // d f_k / d t_k
+template <class T>
+struct LabJac {
+  T d_lin[3];  // d lin_c / d x_c
+  T d_f[3];    // d f_k / d t_k
 };
 
-template <class M, bool WANT_JAC>
-CURL_HD void rgb2lab_fwd(const float x[3], float lab[3], LabJac* jac) {
-  float lin[3];
+template <class T, bool JAC>
+CURL_HD void rgb2lab_fwd(const T x[3], T lab[3], LabJac<T>* jac) {
+  T lin[3];
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
     // colors.py:37-38.  In the pow branch x > 0.04045 so the reference's clamp(min=1e-4) is inert.
-    const float u = fmaf(x[c], k::SRGB_A, k::SRGB_B);
-    const float l = M::lg2(u);
-    const float hi = M::ex2(2.4f * l);
-    const bool lo_branch = x[c] <= k::SRGB_T;
-    lin[c] = lo_branch ? x[c] * k::SRGB_INV_SLOPE : hi;
-    if (WANT_JAC) {
-      // d/dx ((x+.055)/1.055)^2.4 = 2.4/1.055 * u^1.4
-      const float dhi = (float)(2.4 / 1.055) * M::ex2(1.4f * l);
-      jac->d_lin[c] = lo_branch ? k::SRGB_INV_SLOPE : dhi;
-    }
+    const T u = vfma(x[c], T(k::SRGB_A), T(k::SRGB_B));
+    const T u14 = vmul(u, vex2(vmul(vlg2(u), T(0.4f))));
+    const T hi = vmul(u, u14);
+    lin[c] = vsel_le(x[c], T(k::SRGB_T), vmul(x[c], T(k::SRGB_INV_SLOPE)), hi);
+    if (JAC) jac->d_lin[c] = vsel_le(x[c], T(k::SRGB_T), T(k::SRGB_INV_SLOPE), vmul(u14, T(k::SRGB_DK)));
   }
-  float t[3];
-  t[0] = fmaf(lin[2], k::M20, fmaf(lin[1], k::M10, lin[0] * k::M00));  // colors.py:40-41
-  t[1] = fmaf(lin[2], k::M21, fmaf(lin[1], k::M11, lin[0] * k::M01));
-  t[2] = fmaf(lin[2], k::M22, fmaf(lin[1], k::M12, lin[0] * k::M02));
-  float f[3];
+  T t[3];
+  t[0] = vfma(lin[2], T(k::M20), vfma(lin[1], T(k::M10), vmul(lin[0], T(k::M00))));  // colors.py:40-41
+  t[1] = vfma(lin[2], T(k::M21), vfma(lin[1], T(k::M11), vmul(lin[0], T(k::M01))));
+  t[2] = vfma(lin[2], T(k::M22), vfma(lin[1], T(k::M12), vmul(lin[0], T(k::M02))));
+  T f[3];
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
     // colors.py:45-47.  In the cube-root branch t > eps^3 > 1e-4 so the clamp is inert.
-    const float l = M::lg2(t[c]);
-    const float cr = M::ex2(l * (float)(1.0 / 3.0));
-    const bool lo_branch = t[c] <= k::F_T;
-    f[c] = lo_branch ? fmaf(t[c], k::F_SLOPE, k::F_OFF) : cr;
-    if (WANT_JAC) {
-      // d/dt t^(1/3) = (1/3) t^(-2/3)
-      const float dcr = (float)(1.0 / 3.0) * M::ex2(l * (float)(-2.0 / 3.0));
-      jac->d_f[c] = lo_branch ? k::F_SLOPE : dcr;
-    }
+    const T e = vex2(vmul(vlg2(t[c]), T((float)(-2.0 / 3.0))));   // t^(-2/3)
+    const T cr = vmul(t[c], e);
+    f[c] = vsel_le(t[c], T(k::F_T), vfma(t[c], T(k::F_SLOPE), T(k::F_OFF)), cr);
+    if (JAC) jac->d_f[c] = vsel_le(t[c], T(k::F_T), T(k::F_SLOPE), vmul(e, T((float)(1.0 / 3.0))));
   }
-  lab[0] = fmaf(f[1], k::LN_S, k::LN_O);           // colors.py:50,57
-  lab[1] = fmaf(f[0] - f[1], k::AN_S, 0.5f);       // colors.py:50,58
-  lab[2] = fmaf(f[1] - f[2], k::BN_S, 0.5f);       // colors.py:50,59
+  lab[0] = vfma(f[1], T(k::LN_S), T(k::LN_O));               // colors.py:50,57
+  lab[1] = vfma(vsub(f[0], f[1]), T(k::AN_S), T(0.5f));      // colors.py:50,58
+  lab[2] = vfma(vsub(f[1], f[2]), T(k::BN_S), T(0.5f));      // colors.py:50,59
 }
 
-CURL_HD void rgb2lab_bwd(const LabJac& jac, const float glab[3], float gx[3]) {
-  const float ga = glab[1] * k::AN_S, gb = glab[2] * k::BN_S;
-  float gt[3];
-  gt[0] = ga * jac.d_f[0];
-  gt[1] = (fmaf(glab[0], k::LN_S, gb) - ga) * jac.d_f[1];
-  gt[2] = -gb * jac.d_f[2];
-  gx[0] = fmaf(gt[2], k::M02, fmaf(gt[1], k::M01, gt[0] * k::M00)) * jac.d_lin[0];
-  gx[1] = fmaf(gt[2], k::M12, fmaf(gt[1], k::M11, gt[0] * k::M10)) * jac.d_lin[1];
-  gx[2] = fmaf(gt[2], k::M22, fmaf(gt[1], k::M21, gt[0] * k::M20)) * jac.d_lin[2];
+template <class T>
+CURL_HD void rgb2lab_bwd(const LabJac<T>& jac, const T glab[3], T gx[3]) {
+  const T ga = vmul(glab[1], T(k::AN_S)), gb = vmul(glab[2], T(k::BN_S));
+  T gt[3];
+  gt[0] = vmul(ga, jac.d_f[0]);
+  gt[1] = vmul(vsub(vfma(glab[0], T(k::LN_S), gb), ga), jac.d_f[1]);
+  gt[2] = vneg(vmul(gb, jac.d_f[2]));
+  gx[0] = vmul(vfma(gt[2], T(k::M02), vfma(gt[1], T(k::M01), vmul(gt[0], T(k::M00)))), jac.d_lin[0]);
+  gx[1] = vmul(vfma(gt[2], T(k::M12), vfma(gt[1], T(k::M11), vmul(gt[0], T(k::M10)))), jac.d_lin[1]);
+  gx[2] = vmul(vfma(gt[2], T(k::M22), vfma(gt[1], T(k::M21), vmul(gt[0], T(k::M20)))), jac.d_lin[2]);
 }
 
 // ------------------------------------------------------------------------------------------------
 // Stage: normalised Lab -> RGB (unclamped)      (reference colors.py:88-123)
 // ------------------------------------------------------------------------------------------------
+template <class T>
 struct RgbJac {
-  float d_finv[3];  // d finv_k / d f_k
-  float d_gam[3];   // d rgb_c / d v_c
+  T d_finv[3];  // d finv_k / d f_k
+  T d_gam[3];   // d rgb_c / d v_c
 };
 
-template <class M, bool WANT_JAC>
-CURL_HD void lab2rgb_fwd(const float lab[3], float rgb[3], RgbJac* jac) {
-  float f[3];
-  f[1] = fmaf(lab[0], k::FY_S, k::FY_O);           // colors.py:97,104
-  f[0] = fmaf(lab[1], k::FX_S, f[1] + k::FX_O);    // colors.py:98,104
-  f[2] = fmaf(lab[2], k::FZ_S, f[1] + k::FZ_O);    // colors.py:99,104
-  float xyz[3];
+template <class T, bool JAC>
+CURL_HD void lab2rgb_fwd(const T lab[3], T rgb[3], RgbJac<T>* jac) {
+  T f[3];
+  f[1] = vfma(lab[0], T(k::FY_S), T(k::FY_O));                    // colors.py:97,104
+  f[0] = vfma(lab[1], T(k::FX_S), vadd(f[1], T(k::FX_O)));        // colors.py:98,104
+  f[2] = vfma(lab[2], T(k::FZ_S), vadd(f[1], T(k::FZ_O)));        // colors.py:99,104
+  T xyz[3];
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
     // colors.py:110-111.  In the cube branch f > eps > 1e-4 so the clamp is inert.
-    const bool lo_branch = f[c] <= k::FINV_T;
-    const float sq = f[c] * f[c];
-    xyz[c] = lo_branch ? k::FINV_SLOPE * (f[c] - k::F_OFF) : sq * f[c];
-    if (WANT_JAC) jac->d_finv[c] = lo_branch ? k::FINV_SLOPE : 3.0f * sq;
+    const T sq = vmul(f[c], f[c]);
+    xyz[c] = vsel_le(f[c], T(k::FINV_T), vfma(f[c], T(k::FINV_SLOPE), T(k::FINV_OFF)), vmul(sq, f[c]));
+    if (JAC) jac->d_finv[c] = vsel_le(f[c], T(k::FINV_T), T(k::FINV_SLOPE), vmul(sq, T(3.0f)));
   }
-  float v[3];
-  v[0] = fmaf(xyz[2], k::N20, fmaf(xyz[1], k::N10, xyz[0] * k::N00));  // colors.py:114,117
-  v[1] = fmaf(xyz[2], k::N21, fmaf(xyz[1], k::N11, xyz[0] * k::N01));
-  v[2] = fmaf(xyz[2], k::N22, fmaf(xyz[1], k::N12, xyz[0] * k::N02));
+  T v[3];
+  v[0] = vfma(xyz[2], T(k::N20), vfma(xyz[1], T(k::N10), vmul(xyz[0], T(k::N00))));  // colors.py:114,117
+  v[1] = vfma(xyz[2], T(k::N21), vfma(xyz[1], T(k::N11), vmul(xyz[0], T(k::N01))));
+  v[2] = vfma(xyz[2], T(k::N22), vfma(xyz[1], T(k::N12), vmul(xyz[0], T(k::N02))));
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
     // colors.py:118-119.  In the pow branch v > 0.0031308 > 1e-4 so the clamp is inert.
-    const float l = M::lg2(v[c]);
-    const float pw = M::ex2(l * (float)(1.0 / 2.4));
-    const bool lo_branch = v[c] <= k::LIN_T;
-    rgb[c] = lo_branch ? v[c] * k::LIN_SLOPE : fmaf(pw, 1.055f, -0.055f);
-    if (WANT_JAC) {
-      // d/dv 1.055 v^(1/2.4) = (1.055/2.4) v^(1/2.4 - 1)
-      const float dpw = (float)(1.055 / 2.4) * M::ex2(l * (float)(1.0 / 2.4 - 1.0));
-      jac->d_gam[c] = lo_branch ? k::LIN_SLOPE : dpw;
-    }
+    const T e = vex2(vmul(vlg2(v[c]), T(k::GAM_E)));               // v^(1/2.4 - 1)
+    const T hi = vfma(vmul(v[c], e), T(1.055f), T(-0.055f));
+    rgb[c] = vsel_le(v[c], T(k::LIN_T), vmul(v[c], T(k::LIN_SLOPE)), hi);
+    if (JAC) jac->d_gam[c] = vsel_le(v[c], T(k::LIN_T), T(k::LIN_SLOPE), vmul(e, T(k::GAM_DK)));
   }
 }
 
-CURL_HD void lab2rgb_bwd(const RgbJac& jac, const float grgb[3], float glab[3]) {
-  const float gv0 = grgb[0] * jac.d_gam[0], gv1 = grgb[1] * jac.d_gam[1], gv2 = grgb[2] * jac.d_gam[2];
-  const float gf0 = fmaf(gv2, k::N02, fmaf(gv1, k::N01, gv0 * k::N00)) * jac.d_finv[0];
-  const float gf1 = fmaf(gv2, k::N12, fmaf(gv1, k::N11, gv0 * k::N10)) * jac.d_finv[1];
-  const float gf2 = fmaf(gv2, k::N22, fmaf(gv1, k::N21, gv0 * k::N20)) * jac.d_finv[2];
-  glab[0] = (gf0 + gf1 + gf2) * k::FY_S;
-  glab[1] = gf0 * k::FX_S;
-  glab[2] = gf2 * k::FZ_S;
+template <class T>
+CURL_HD void lab2rgb_bwd(const RgbJac<T>& jac, const T grgb[3], T glab[3]) {
+  const T gv0 = vmul(grgb[0], jac.d_gam[0]), gv1 = vmul(grgb[1], jac.d_gam[1]), gv2 = vmul(grgb[2], jac.d_gam[2]);
+  const T gf0 = vmul(vfma(gv2, T(k::N02), vfma(gv1, T(k::N01), vmul(gv0, T(k::N00)))), jac.d_finv[0]);
+  const T gf1 = vmul(vfma(gv2, T(k::N12), vfma(gv1, T(k::N11), vmul(gv0, T(k::N10)))), jac.d_finv[1]);
+  const T gf2 = vmul(vfma(gv2, T(k::N22), vfma(gv1, T(k::N21), vmul(gv0, T(k::N20)))), jac.d_finv[2]);
+  glab[0] = vmul(vadd(vadd(gf0, gf1), gf2), T(k::FY_S));
+  glab[1] = vmul(gf0, T(k::FX_S));
+  glab[2] = vmul(gf2, T(k::FZ_S));
 }
 
 // ------------------------------------------------------------------------------------------------
 // Stage: RGB -> HSV                             (reference colors.py:195-242)
 // Hue uses ADDITIVE selectors: on ties the per-channel terms add (colors.py:221-224).
 // max/min route their gradient to the FIRST index attaining them (torch CPU semantics).
+// Backward, with gh/gs/gv the upstream gradients:
+//   gdf = gh kdf_h + gs kdf_s ;  gmx = gv + gs kmx_s + gdf ;  gx_c = gh hc_c + gmx amax_c - gdf amin_c
 // ------------------------------------------------------------------------------------------------
+template <class T>
 struct HsvJac {
-  float xc[3];       // clamped inputs
-  float dinv, minv;  // 1/df (0 if df == 0), 1/mx
-  float df;
-  float sel[3];      // [x_c == mx] as 0/1
-  int imax, imin;
-  bool pass_in[3];   // 1e-9 <= x_c <= 1
-  bool pass_h, pass_s;
+  T hc[3];      // direct hue terms: pass_h/6 * (1/df) * (selector difference) * pass_in_c
+  T amax[3];    // one-hot first argmax  * pass_in_c
+  T amin[3];    // one-hot first argmin  * pass_in_c
+  T kdf_h, kdf_s, kmx_s;
 };
 
-template <class M, bool WANT_JAC, bool IN_UNIT>
-CURL_HD void rgb2hsv_fwd(const float x[3], float hsv[3], HsvJac* jac) {
-  float xc[3];
+template <class T, bool JAC, bool IN_UNIT>
+CURL_HD void rgb2hsv_fwd(const T x[3], T hsv[3], HsvJac<T>* jac) {
+  T xc[3];
 #pragma unroll
-  for (int c = 0; c < 3; ++c) {
-    // colors.py:205.  IN_UNIT: caller guarantees 0 <= x <= 1, only the lower bound can bite.
-    xc[c] = IN_UNIT ? M::fmax_(x[c], k::HSV_LO) : M::fmin_(M::fmax_(x[c], k::HSV_LO), 1.0f);
-    if (WANT_JAC) jac->pass_in[c] = (xc[c] == x[c]);
-  }
-  const float mx = M::fmax_(xc[0], M::fmax_(xc[1], xc[2]));   // colors.py:211
-  const float mn = M::fmin_(xc[0], M::fmin_(xc[1], xc[2]));   // colors.py:212
-  const float df = mx - mn;                                    // colors.py:214
-  const bool grey = (df == 0.0f);
-  const float dinv = grey ? 0.0f : M::rcp(df);                 // colors.py:186-193,220
-  const float s0 = (xc[0] == mx) ? 1.0f : 0.0f;
-  const float s1 = (xc[1] == mx) ? 1.0f : 0.0f;
-  const float s2 = (xc[2] == mx) ? 1.0f : 0.0f;
-  // colors.py:221-224 (grey pixels: dinv == 0 gives 0 + 2*s1 + 4*s2, which `where` replaces by 0)
-  float hr = ((xc[1] - xc[2]) * dinv) * s0 + fmaf(xc[2] - xc[0], dinv, 2.0f) * s1 +
-             fmaf(xc[0] - xc[1], dinv, 4.0f) * s2;
-  hr = grey ? 0.0f : hr;
+  for (int c = 0; c < 3; ++c)  // colors.py:205.  IN_UNIT: caller guarantees 0 <= x <= 1
+    xc[c] = IN_UNIT ? vmax(x[c], T(k::HSV_LO)) : vmin(vmax(x[c], T(k::HSV_LO)), T(1.0f));
+  const T mx = vmax(xc[0], vmax(xc[1], xc[2]));                // colors.py:211
+  const T mn = vmin(xc[0], vmin(xc[1], xc[2]));                // colors.py:212
+  const T df = vsub(mx, mn);                                   // colors.py:214
+  const T dinv = vsel_eq(df, T(0.0f), T(0.0f), vrcp(df));      // colors.py:186-193,220
+  const T nz = vgate_ne(df, T(0.0f));
+  const T s0 = vgate_eq(xc[0], mx), s1 = vgate_eq(xc[1], mx), s2 = vgate_eq(xc[2], mx);
+  const T d12 = vsub(xc[1], xc[2]), d20 = vsub(xc[2], xc[0]), d01 = vsub(xc[0], xc[1]);
+  // colors.py:221-224 (grey pixels: `where` replaces the sum by 0)
+  T hr = vmul(vmul(d12, dinv), s0);
+  hr = vfma(vfma(d20, dinv, T(2.0f)), s1, hr);
+  hr = vfma(vfma(d01, dinv, T(4.0f)), s2, hr);
+  hr = vmul(hr, nz);
   // colors.py:225-231:  h = (60 hr (+360 if negative)) / 360
-  float h = hr * (float)(1.0 / 6.0);
-  h = (hr < 0.0f) ? h + 1.0f : h;
-  const float minv = M::rcp(mx);                               // colors.py:234 (mx >= 1e-9, never 0)
-  const float s = df * minv;                                   // colors.py:235-237
+  const T h = vfma(hr, T((float)(1.0 / 6.0)), vgate_lt(hr, T(0.0f)));
+  const T minv = vrcp(mx);                                     // colors.py:234 (mx >= 1e-9, never 0)
+  const T s = vmul(df, minv);                                  // colors.py:235-237
   // colors.py:240
-  hsv[0] = M::fmin_(M::fmax_(h, k::HSV_LO), 1.0f);
-  hsv[1] = M::fmin_(M::fmax_(s, k::HSV_LO), 1.0f);
+  hsv[0] = vmin(vmax(h, T(k::HSV_LO)), T(1.0f));
+  hsv[1] = vmin(vmax(s, T(k::HSV_LO)), T(1.0f));
   hsv[2] = mx;  // already inside [1e-9, 1]
-  if (WANT_JAC) {
-    jac->xc[0] = xc[0]; jac->xc[1] = xc[1]; jac->xc[2] = xc[2];
-    jac->dinv = dinv; jac->minv = minv; jac->df = df;
-    jac->sel[0] = s0; jac->sel[1] = s1; jac->sel[2] = s2;
-    jac->imax = (xc[0] == mx) ? 0 : ((xc[1] == mx) ? 1 : 2);
-    jac->imin = (xc[0] == mn) ? 0 : ((xc[1] == mn) ? 1 : 2);
-    jac->pass_h = (hsv[0] == h);
-    jac->pass_s = (hsv[1] == s);
+  if (JAC) {
+    const T pass_h6 = vmul(vgate_eq(hsv[0], h), T((float)(1.0 / 6.0)));   // d h / d hr = 60/360
+    const T pass_s = vgate_eq(hsv[1], s);
+    const T pin0 = vgate_eq(xc[0], x[0]), pin1 = vgate_eq(xc[1], x[1]), pin2 = vgate_eq(xc[2], x[2]);
+    const T A = vmul(pass_h6, dinv);      // dinv == 0 on grey pixels blocks the hue gradient
+    jac->hc[0] = vmul(vmul(A, vsub(s2, s1)), pin0);
+    jac->hc[1] = vmul(vmul(A, vsub(s0, s2)), pin1);
+    jac->hc[2] = vmul(vmul(A, vsub(s1, s0)), pin2);
+    const T num = vfma(s2, d01, vfma(s1, d20, vmul(s0, d12)));
+    jac->kdf_h = vneg(vmul(vmul(A, num), dinv));               // d(1/df) = -1/df^2
+    jac->kdf_s = vmul(pass_s, minv);                           // s = df / mx
+    jac->kmx_s = vneg(vmul(jac->kdf_s, s));
+    const T e0 = vgate_eq(xc[0], mn), e1 = vgate_eq(xc[1], mn);
+    const T ns0 = vsub(T(1.0f), s0), ne0 = vsub(T(1.0f), e0);
+    jac->amax[0] = vmul(s0, pin0);
+    jac->amax[1] = vmul(vmul(s1, ns0), pin1);
+    jac->amax[2] = vmul(vmul(ns0, vsub(T(1.0f), s1)), pin2);
+    jac->amin[0] = vmul(e0, pin0);
+    jac->amin[1] = vmul(vmul(e1, ne0), pin1);
+    jac->amin[2] = vmul(vmul(ne0, vsub(T(1.0f), e1)), pin2);
   }
 }
 
-CURL_HD void rgb2hsv_bwd(const HsvJac& j, const float ghsv[3], float gx[3]) {
-  const float gh = j.pass_h ? ghsv[0] * (float)(1.0 / 6.0) : 0.0f;  // d h / d hr = 60/360
-  const float gs = j.pass_s ? ghsv[1] : 0.0f;
-  const float gv = ghsv[2];
-  // hue terms (zero when df == 0 because dinv == 0 there and `where` blocks the gradient)
-  const float A = gh * j.dinv;
-  float g0 = A * (j.sel[2] - j.sel[1]);
-  float g1 = A * (j.sel[0] - j.sel[2]);
-  float g2 = A * (j.sel[1] - j.sel[0]);
-  const float num = j.sel[0] * (j.xc[1] - j.xc[2]) + j.sel[1] * (j.xc[2] - j.xc[0]) + j.sel[2] * (j.xc[0] - j.xc[1]);
-  float gdf = -(gh * num) * (j.dinv * j.dinv);   // d(1/df) = -1/df^2
-  gdf = fmaf(gs, j.minv, gdf);                    // s = df / mx
-  const float gmx = fmaf(-gs * j.df, j.minv * j.minv, gv) + gdf;
-  const float gmn = -gdf;
-  g0 += (j.imax == 0 ? gmx : 0.0f) + (j.imin == 0 ? gmn : 0.0f);
-  g1 += (j.imax == 1 ? gmx : 0.0f) + (j.imin == 1 ? gmn : 0.0f);
-  g2 += (j.imax == 2 ? gmx : 0.0f) + (j.imin == 2 ? gmn : 0.0f);
-  gx[0] = j.pass_in[0] ? g0 : 0.0f;
-  gx[1] = j.pass_in[1] ? g1 : 0.0f;
-  gx[2] = j.pass_in[2] ? g2 : 0.0f;
+template <class T>
+CURL_HD void rgb2hsv_bwd(const HsvJac<T>& j, const T ghsv[3], T gx[3]) {
+  const T gdf = vfma(ghsv[0], j.kdf_h, vmul(ghsv[1], j.kdf_s));
+  const T gmx = vadd(vfma(ghsv[1], j.kmx_s, ghsv[2]), gdf);
+#pragma unroll
+  for (int c = 0; c < 3; ++c)
+    gx[c] = vfma(ghsv[0], j.hc[c], vsub(vmul(gmx, j.amax[c]), vmul(gdf, j.amin[c])));
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -332,182 +286,192 @@ CURL_HD void rgb2hsv_bwd(const HsvJac& j, const float ghsv[3], float gx[3]) {
 //   p = v(1-s), w = v - p ;  ramp_k = clamp(360 h - k, 0, 60)/60 = sat(6h - k/60)
 //   r = v + w (ramp240 - ramp60) ; g = p + w (ramp0 - ramp180) ; b = p + w (ramp120 - ramp300)
 // ------------------------------------------------------------------------------------------------
+template <class T>
 struct Hsv2RgbJac {
-  float w, v, one_minus_s;
-  float dr, dg, db;          // ramp differences
-  float gate[6];             // ramp k unsaturated (inclusive ends), k = 0,60,120,180,240,300
-  bool pass_in[3];
-  bool pass_out[3];
+  T po[3];          // output clamp passes
+  T dr, dg, db;     // ramp differences
+  T hr, hg, hb;     // 6 w (gate differences) pass_in_h
+  T oms, vs;        // (1 - s) * pass_in_v ... see bwd ; v * pass_in_s
+  T pin_v;
 };
 
-template <class M, bool WANT_JAC, bool IN_UNIT>
-CURL_HD void hsv2rgb_fwd(const float hsv_in[3], float rgb[3], Hsv2RgbJac* jac) {
-  float q[3];
-#pragma unroll
-  for (int c = 0; c < 3; ++c) {
-    q[c] = IN_UNIT ? hsv_in[c] : M::sat(hsv_in[c]);           // colors.py:141
-    if (WANT_JAC) jac->pass_in[c] = IN_UNIT ? true : (q[c] == hsv_in[c]);
-  }
-  const float h = q[0], s = q[1], v = q[2];
-  const float oms = 1.0f - s;
-  const float p = v * oms;
-  const float w = v - p;
-  float t[6], u[6];
+template <class T, bool JAC, bool IN_UNIT>
+CURL_HD void hsv2rgb_fwd(const T in[3], T rgb[3], Hsv2RgbJac<T>* jac) {
+  const T h = IN_UNIT ? in[0] : vsat(in[0]);                    // colors.py:141
+  const T s = IN_UNIT ? in[1] : vsat(in[1]);
+  const T v = IN_UNIT ? in[2] : vsat(in[2]);
+  const T oms = vsub(T(1.0f), s);
+  const T p = vmul(v, oms);
+  const T w = vsub(v, p);
+  T t[6], u[6];
 #pragma unroll
   for (int i = 0; i < 6; ++i) {
-    t[i] = fmaf(h, 6.0f, -(float)i);
-    u[i] = M::sat(t[i]);
+    if (JAC) { t[i] = vfma(h, T(6.0f), T(-(float)i)); u[i] = vsat(t[i]); }
+    else u[i] = vfma_sat(h, T(6.0f), T(-(float)i));
   }
-  const float dr = u[4] - u[1], dg = u[0] - u[3], db = u[2] - u[5];
-  const float r = fmaf(w, dr, v);                               // colors.py:143-150
-  const float g = fmaf(w, dg, p);                               // colors.py:153-159
-  const float b = fmaf(w, db, p);                               // colors.py:162-168
-  rgb[0] = M::sat(r); rgb[1] = M::sat(g); rgb[2] = M::sat(b);   // colors.py:175
-  if (WANT_JAC) {
-    jac->w = w; jac->v = v; jac->one_minus_s = oms;
-    jac->dr = dr; jac->dg = dg; jac->db = db;
+  const T dr = vsub(u[4], u[1]), dg = vsub(u[0], u[3]), db = vsub(u[2], u[5]);
+  const T r = vfma(w, dr, v);                                   // colors.py:143-150
+  const T g = vfma(w, dg, p);                                   // colors.py:153-159
+  const T b = vfma(w, db, p);                                   // colors.py:162-168
+  rgb[0] = vsat(r); rgb[1] = vsat(g); rgb[2] = vsat(b);         // colors.py:175
+  if (JAC) {
+    T gate[6];
 #pragma unroll
-    for (int i = 0; i < 6; ++i) jac->gate[i] = (u[i] == t[i]) ? 1.0f : 0.0f;
-    jac->pass_out[0] = (rgb[0] == r); jac->pass_out[1] = (rgb[1] == g); jac->pass_out[2] = (rgb[2] == b);
+    for (int i = 0; i < 6; ++i) gate[i] = vgate_eq(u[i], t[i]);   // ramp unsaturated, inclusive ends
+    jac->po[0] = vgate_eq(rgb[0], r); jac->po[1] = vgate_eq(rgb[1], g); jac->po[2] = vgate_eq(rgb[2], b);
+    jac->dr = dr; jac->dg = dg; jac->db = db;
+    T w6 = vmul(w, T(6.0f));
+    if (!IN_UNIT) w6 = vmul(w6, vgate_eq(h, in[0]));
+    jac->hr = vmul(w6, vsub(gate[4], gate[1]));
+    jac->hg = vmul(w6, vsub(gate[0], gate[3]));
+    jac->hb = vmul(w6, vsub(gate[2], gate[5]));
+    jac->oms = oms;
+    jac->vs = IN_UNIT ? v : vmul(v, vgate_eq(s, in[1]));
+    jac->pin_v = IN_UNIT ? T(1.0f) : vgate_eq(v, in[2]);
   }
 }
 
-CURL_HD void hsv2rgb_bwd(const Hsv2RgbJac& j, const float grgb[3], float ghsv[3]) {
-  const float gr = j.pass_out[0] ? grgb[0] : 0.0f;
-  const float gg = j.pass_out[1] ? grgb[1] : 0.0f;
-  const float gb = j.pass_out[2] ? grgb[2] : 0.0f;
-  const float gw = fmaf(gr, j.dr, fmaf(gg, j.dg, gb * j.db));
-  // d/dh: each unsaturated ramp contributes 6 * (+-w) * g
-  const float hr = j.gate[4] - j.gate[1], hg = j.gate[0] - j.gate[3], hb = j.gate[2] - j.gate[5];
-  const float gh = 6.0f * j.w * fmaf(gr, hr, fmaf(gg, hg, gb * hb));
-  const float gp = gg + gb - gw;          // p enters g, b directly and w = v - p
-  const float gv = gr + gw + gp * j.one_minus_s;
-  const float gs = -gp * j.v;
-  ghsv[0] = j.pass_in[0] ? gh : 0.0f;
-  ghsv[1] = j.pass_in[1] ? gs : 0.0f;
-  ghsv[2] = j.pass_in[2] ? gv : 0.0f;
+template <class T, bool IN_UNIT>
+CURL_HD void hsv2rgb_bwd(const Hsv2RgbJac<T>& j, const T grgb[3], T ghsv[3]) {
+  const T gr = vmul(grgb[0], j.po[0]), gg = vmul(grgb[1], j.po[1]), gb = vmul(grgb[2], j.po[2]);
+  const T gw = vfma(gr, j.dr, vfma(gg, j.dg, vmul(gb, j.db)));
+  ghsv[0] = vfma(gr, j.hr, vfma(gg, j.hg, vmul(gb, j.hb)));
+  const T gp = vsub(vadd(gg, gb), gw);          // p enters g, b directly and w = v - p
+  const T gv = vfma(gp, j.oms, vadd(gr, gw));
+  ghsv[1] = vneg(vmul(gp, j.vs));
+  ghsv[2] = IN_UNIT ? gv : vmul(gv, j.pin_v);
 }
 
 // ------------------------------------------------------------------------------------------------
 // Stage: knot curves                            (reference curves.py:4-38)
 // One "self" curve: out = clamp(x * (alpha + beta x)); every apply_curve clamps all channels, so a
 // channel adjusted by the 2nd/3rd curve of a group sees its input clamped first (PRECLAMP).
+// Backward per curve: gs = go * a (d loss / d scale), moments S0 += gs, S1 += gs * xin, gx = go * d.
 // ------------------------------------------------------------------------------------------------
+template <class T>
 struct CurveJac {
-  float xin;       // (clamped) input
-  float dydx;      // alpha + 2 beta x
-  bool pass_in, pass_out;
+  T xin;   // (clamped) input
+  T a;     // pass_out * xin
+  T d;     // pass_out * pass_in * (alpha + 2 beta xin)
 };
 
-template <class M, bool WANT_JAC, bool PRECLAMP>
-CURL_HD float self_curve_fwd(float x, float alpha, float beta, CurveJac* jac) {
-  const float xin = PRECLAMP ? M::sat(x) : x;
-  const float s = fmaf(beta, xin, alpha);          // curves.py:31-32 (closed form)
-  const float y = xin * s;                         // curves.py:35
-  const float o = M::sat(y);                       // curves.py:36
-  if (WANT_JAC) {
-    jac->xin = xin;
-    jac->dydx = fmaf(beta, xin, s);
-    jac->pass_in = PRECLAMP ? (xin == x) : true;
-    jac->pass_out = (o == y);
-  }
+template <class T, bool JAC, bool PRECLAMP>
+CURL_HD T self_curve_fwd(T x, float alpha, float beta, CurveJac<T>* jac) {
+  const T xin = PRECLAMP ? vsat(x) : x;
+  const T s = vfma(T(beta), xin, T(alpha));        // curves.py:31-32 (closed form)
+  if (!JAC) return vmul_sat(xin, s);               // curves.py:35-36
+  const T y = vmul(xin, s);
+  const T o = vsat(y);
+  const T po = vgate_eq(o, y);
+  jac->xin = xin;
+  jac->a = vmul(po, xin);
+  T d = vmul(po, vfma(T(beta), xin, s));
+  if (PRECLAMP) d = vmul(d, vgate_eq(xin, x));
+  jac->d = d;
   return o;
 }
 
-// mom[0] += g, mom[1] += g * xin  with g = d loss / d scale
-CURL_HD float self_curve_bwd(const CurveJac& j, float go, float mom[2]) {
-  const float gy = j.pass_out ? go : 0.0f;
-  const float gs = gy * j.xin;
-  mom[0] += gs;
-  mom[1] = fmaf(gs, j.xin, mom[1]);
-  const float gx = gy * j.dydx;
-  return j.pass_in ? gx : 0.0f;
+template <class T>
+CURL_HD T self_curve_bwd(const CurveJac<T>& j, T go, T mom[2]) {
+  const T gs = vmul(go, j.a);
+  mom[0] = vadd(mom[0], gs);
+  mom[1] = vfma(gs, j.xin, mom[1]);
+  return vmul(go, j.d);
 }
 
 // One general curve cin -> cout on raw (unclamped) inputs, then the whole-pixel clamp: this is
 // curves.apply_curve itself (curves.py:4-38) for callers that use it directly.
-template <class M>
-CURL_HD void single_curve_fwd(const float x[3], int cin, int cout, float alpha, float beta, float y[3]) {
-  const float xi = cin == 0 ? x[0] : (cin == 1 ? x[1] : x[2]);
-  const float s = fmaf(beta, xi, alpha);
+template <class T>
+CURL_HD void single_curve_fwd(const T x[3], int cin, int cout, float alpha, float beta, T y[3]) {
+  const T xi = cin == 0 ? x[0] : (cin == 1 ? x[1] : x[2]);
+  const T s = vfma(T(beta), xi, T(alpha));
 #pragma unroll
-  for (int c = 0; c < 3; ++c) y[c] = M::sat(c == cout ? x[c] * s : x[c]);
+  for (int c = 0; c < 3; ++c) y[c] = vsat(c == cout ? vmul(x[c], s) : x[c]);
 }
 
-template <class M>
-CURL_HD void single_curve_bwd(const float x[3], int cin, int cout, float alpha, float beta, const float gy[3],
-                              float gx[3], float mom[2]) {
-  const float xi = cin == 0 ? x[0] : (cin == 1 ? x[1] : x[2]);
-  const float s = fmaf(beta, xi, alpha);
-  float gs = 0.0f;
+template <class T>
+CURL_HD void single_curve_bwd(const T x[3], int cin, int cout, float alpha, float beta, const T gy[3], T gx[3],
+                              T mom[2]) {
+  const T xi = cin == 0 ? x[0] : (cin == 1 ? x[1] : x[2]);
+  const T s = vfma(T(beta), xi, T(alpha));
+  T gs = T(0.0f);
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
-    const float pre = (c == cout) ? x[c] * s : x[c];
-    const float g = (M::sat(pre) == pre) ? gy[c] : 0.0f;
-    gx[c] = (c == cout) ? g * s : g;
-    if (c == cout) gs = g * x[c];
+    const T pre = (c == cout) ? vmul(x[c], s) : x[c];
+    const T g = vmul(gy[c], vgate_eq(vsat(pre), pre));
+    gx[c] = (c == cout) ? vmul(g, s) : g;
+    if (c == cout) gs = vmul(g, x[c]);
   }
-  mom[0] += gs;
-  mom[1] = fmaf(gs, xi, mom[1]);
+  mom[0] = vadd(mom[0], gs);
+  mom[1] = vfma(gs, xi, mom[1]);
 #pragma unroll
   for (int c = 0; c < 3; ++c)
-    if (c == cin) gx[c] = fmaf(gs, beta, gx[c]);
+    if (c == cin) gx[c] = vfma(gs, T(beta), gx[c]);
 }
 
 // adjust_lab / adjust_rgb: three self curves c -> c (curves.py:90-133, 136-180)
-struct Self3Jac { CurveJac c[3]; };
+template <class T>
+struct Self3Jac { CurveJac<T> c[3]; };
 
-template <class M, bool WANT_JAC>
-CURL_HD void adjust_self3_fwd(const float x[3], const float* ab, float y[3], Self3Jac* jac) {
-  y[0] = self_curve_fwd<M, WANT_JAC, false>(x[0], ab[0], ab[1], WANT_JAC ? &jac->c[0] : nullptr);
-  y[1] = self_curve_fwd<M, WANT_JAC, true>(x[1], ab[2], ab[3], WANT_JAC ? &jac->c[1] : nullptr);
-  y[2] = self_curve_fwd<M, WANT_JAC, true>(x[2], ab[4], ab[5], WANT_JAC ? &jac->c[2] : nullptr);
+template <class T, bool JAC>
+CURL_HD void adjust_self3_fwd(const T x[3], const float* ab, T y[3], Self3Jac<T>* jac) {
+  y[0] = self_curve_fwd<T, JAC, false>(x[0], ab[0], ab[1], JAC ? &jac->c[0] : nullptr);
+  y[1] = self_curve_fwd<T, JAC, true>(x[1], ab[2], ab[3], JAC ? &jac->c[1] : nullptr);
+  y[2] = self_curve_fwd<T, JAC, true>(x[2], ab[4], ab[5], JAC ? &jac->c[2] : nullptr);
 }
 
-CURL_HD void adjust_self3_bwd(const Self3Jac& j, const float gy[3], float gx[3], float* mom /*6*/) {
+template <class T>
+CURL_HD void adjust_self3_bwd(const Self3Jac<T>& j, const T gy[3], T gx[3], T* mom /*6*/) {
   gx[0] = self_curve_bwd(j.c[0], gy[0], mom + 0);
   gx[1] = self_curve_bwd(j.c[1], gy[1], mom + 2);
   gx[2] = self_curve_bwd(j.c[2], gy[2], mom + 4);
 }
 
 // adjust_hsv: hue<-f(hue); sat<-f(adjusted hue); sat<-f(sat); val<-f(val)   (curves.py:41-87)
+template <class T>
 struct HsvCurveJac {
-  CurveJac ch;        // curve 0 on hue
-  CurveJac cs;        // curve 2 on sat (self)
-  CurveJac cv;        // curve 3 on val
-  float s_c, h1, sc1; // clamped sat input, adjusted hue, scale of curve 1
-  bool pass_s_in, pass_y1;
+  CurveJac<T> ch;   // curve 0 on hue
+  CurveJac<T> cs;   // curve 2 on sat (self)
+  CurveJac<T> cv;   // curve 3 on val
+  T h1;             // adjusted hue = input of curve 1
+  T p;              // pass_y1 * (clamped sat)            : d loss/d scale1 = gs1 * p
+  T q;              // pass_y1 * scale1 * pass_sat_in     : d loss/d sat_in = gs1 * q
 };
 
-template <class M, bool WANT_JAC, bool IN_UNIT>
-CURL_HD void adjust_hsv_fwd(const float x[3], const float* ab, float y[3], HsvCurveJac* jac) {
-  const float h1 = self_curve_fwd<M, WANT_JAC, false>(x[0], ab[0], ab[1], WANT_JAC ? &jac->ch : nullptr);
+template <class T, bool JAC, bool IN_UNIT>
+CURL_HD void adjust_hsv_fwd(const T x[3], const float* ab, T y[3], HsvCurveJac<T>* jac) {
+  const T h1 = self_curve_fwd<T, JAC, false>(x[0], ab[0], ab[1], JAC ? &jac->ch : nullptr);
   // curve 1: sat * scale(h1); the first apply_curve already clamped sat and val (curves.py:36)
-  const float s_c = IN_UNIT ? x[1] : M::sat(x[1]);
-  const float sc1 = fmaf(ab[3], h1, ab[2]);
-  const float y1 = s_c * sc1;
-  const float s1 = M::sat(y1);
-  const float s2 = self_curve_fwd<M, WANT_JAC, false>(s1, ab[4], ab[5], WANT_JAC ? &jac->cs : nullptr);
-  const float v1 = IN_UNIT ? self_curve_fwd<M, WANT_JAC, false>(x[2], ab[6], ab[7], WANT_JAC ? &jac->cv : nullptr)
-                           : self_curve_fwd<M, WANT_JAC, true>(x[2], ab[6], ab[7], WANT_JAC ? &jac->cv : nullptr);
-  y[0] = h1; y[1] = s2; y[2] = v1;
-  if (WANT_JAC) {
-    jac->s_c = s_c; jac->h1 = h1; jac->sc1 = sc1;
-    jac->pass_s_in = IN_UNIT ? true : (s_c == x[1]);
-    jac->pass_y1 = (s1 == y1);
+  const T s_c = IN_UNIT ? x[1] : vsat(x[1]);
+  const T sc1 = vfma(T(ab[3]), h1, T(ab[2]));
+  T s1;
+  if (JAC) {
+    const T y1 = vmul(s_c, sc1);
+    s1 = vsat(y1);
+    const T py = vgate_eq(s1, y1);
+    jac->h1 = h1;
+    jac->p = vmul(py, s_c);
+    T q = vmul(py, sc1);
+    if (!IN_UNIT) q = vmul(q, vgate_eq(s_c, x[1]));
+    jac->q = q;
+  } else {
+    s1 = vmul_sat(s_c, sc1);
   }
+  y[0] = h1;
+  y[1] = self_curve_fwd<T, JAC, false>(s1, ab[4], ab[5], JAC ? &jac->cs : nullptr);
+  y[2] = IN_UNIT ? self_curve_fwd<T, JAC, false>(x[2], ab[6], ab[7], JAC ? &jac->cv : nullptr)
+                 : self_curve_fwd<T, JAC, true>(x[2], ab[6], ab[7], JAC ? &jac->cv : nullptr);
 }
 
-CURL_HD void adjust_hsv_bwd(const HsvCurveJac& j, const float* ab, const float gy[3], float gx[3], float* mom /*8*/) {
+template <class T>
+CURL_HD void adjust_hsv_bwd(const HsvCurveJac<T>& j, const float* ab, const T gy[3], T gx[3], T* mom /*8*/) {
   gx[2] = self_curve_bwd(j.cv, gy[2], mom + 6);
-  const float gs1 = self_curve_bwd(j.cs, gy[1], mom + 4);
-  const float gy1 = j.pass_y1 ? gs1 : 0.0f;
-  const float gsc = gy1 * j.s_c;                 // d loss / d scale of curve 1
-  mom[2] += gsc;
-  mom[3] = fmaf(gsc, j.h1, mom[3]);
-  const float gs_c = gy1 * j.sc1;
-  gx[1] = j.pass_s_in ? gs_c : 0.0f;
-  const float gh1 = fmaf(gsc, ab[3], gy[0]);     // hue feeds curve 1 through beta_1
+  const T gs1 = self_curve_bwd(j.cs, gy[1], mom + 4);
+  const T gsc = vmul(gs1, j.p);                    // d loss / d scale of curve 1
+  mom[2] = vadd(mom[2], gsc);
+  mom[3] = vfma(gsc, j.h1, mom[3]);
+  gx[1] = vmul(gs1, j.q);
+  const T gh1 = vfma(gsc, T(ab[3]), gy[0]);        // hue feeds curve 1 through beta_1
   gx[0] = self_curve_bwd(j.ch, gh1, mom + 0);
 }
 
@@ -522,68 +486,73 @@ CURL_HD void adjust_hsv_bwd(const HsvCurveJac& j, const float* ab, const float g
 // ------------------------------------------------------------------------------------------------
 constexpr int LAYER_CURVES = 10;
 
-template <class M, int MK>
-CURL_HD void layer_fwd(const float x[3], float m, const float* ab, float out[3]) {
-  float lab[3], lab2[3], rgb[3], rgb2[3], hsv[3], hsv2[3], res[3];
-  rgb2lab_fwd<M, false>(x, lab, nullptr);
-  adjust_self3_fwd<M, false>(lab, ab, lab2, nullptr);
-  if (MK == MASK_F32) { lab2[0] *= m; lab2[1] *= m; lab2[2] *= m; }
-  lab2rgb_fwd<M, false>(lab2, rgb, nullptr);
-  adjust_self3_fwd<M, false>(rgb, ab + 6, rgb2, nullptr);
-  if (MK == MASK_F32) { rgb2[0] *= m; rgb2[1] *= m; rgb2[2] *= m; }
-  rgb2hsv_fwd<M, false, MK != MASK_F32>(rgb2, hsv, nullptr);
-  adjust_hsv_fwd<M, false, true>(hsv, ab + 12, hsv2, nullptr);
+template <class T>
+CURL_HD void vscale3(T a[3], T m) { a[0] = vmul(a[0], m); a[1] = vmul(a[1], m); a[2] = vmul(a[2], m); }
+
+template <class T, int MK>
+CURL_HD void layer_fwd(const T x[3], T m, const float* ab, T out[3]) {
+  T lab[3], lab2[3], rgb[3], rgb2[3], hsv[3], hsv2[3], res[3];
+  rgb2lab_fwd<T, false>(x, lab, nullptr);
+  adjust_self3_fwd<T, false>(lab, ab, lab2, nullptr);
+  if (MK == MASK_F32) vscale3(lab2, m);
+  lab2rgb_fwd<T, false>(lab2, rgb, nullptr);
+  adjust_self3_fwd<T, false>(rgb, ab + 6, rgb2, nullptr);
+  if (MK == MASK_F32) vscale3(rgb2, m);
+  rgb2hsv_fwd<T, false, MK != MASK_F32>(rgb2, hsv, nullptr);
+  adjust_hsv_fwd<T, false, true>(hsv, ab + 12, hsv2, nullptr);
   if (MK == MASK_F32) {
-    hsv2[0] *= m; hsv2[1] *= m; hsv2[2] *= m;
-    hsv2rgb_fwd<M, false, false>(hsv2, res, nullptr);
+    vscale3(hsv2, m);
+    hsv2rgb_fwd<T, false, false>(hsv2, res, nullptr);
   } else {
-    hsv2rgb_fwd<M, false, true>(hsv2, res, nullptr);
+    hsv2rgb_fwd<T, false, true>(hsv2, res, nullptr);
   }
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
-    const float o = M::sat(x[c] + res[c]);           // model.py:170
-    out[c] = (MK == MASK_NONE) ? o : o * m;
+    const T o = vadd_sat(x[c], res[c]);              // model.py:170
+    out[c] = (MK == MASK_NONE) ? o : vmul(o, m);
   }
 }
 
 // Recompute-forward + reverse.  mom: 20 accumulators (S0,S1 per curve), accumulated in place.
-template <class M, int MK>
-CURL_HD void layer_bwd(const float x[3], float m, const float* ab, const float gout[3], float gx[3], float* mom) {
-  float lab[3], lab2[3], rgb[3], rgb2[3], hsv[3], hsv2[3], res[3];
-  LabJac j1; Self3Jac j2; RgbJac j3; Self3Jac j4; HsvJac j5; HsvCurveJac j6; Hsv2RgbJac j7;
-  rgb2lab_fwd<M, true>(x, lab, &j1);
-  adjust_self3_fwd<M, true>(lab, ab, lab2, &j2);
-  if (MK == MASK_F32) { lab2[0] *= m; lab2[1] *= m; lab2[2] *= m; }
-  lab2rgb_fwd<M, true>(lab2, rgb, &j3);
-  adjust_self3_fwd<M, true>(rgb, ab + 6, rgb2, &j4);
-  if (MK == MASK_F32) { rgb2[0] *= m; rgb2[1] *= m; rgb2[2] *= m; }
-  rgb2hsv_fwd<M, true, MK != MASK_F32>(rgb2, hsv, &j5);
-  adjust_hsv_fwd<M, true, true>(hsv, ab + 12, hsv2, &j6);
+template <class T, int MK, bool WANT_GX>
+CURL_HD void layer_bwd(const T x[3], T m, const float* ab, const T gout[3], T gx[3], T* mom) {
+  T lab[3], lab2[3], rgb[3], rgb2[3], hsv[3], hsv2[3], res[3];
+  LabJac<T> j1; Self3Jac<T> j2; RgbJac<T> j3; Self3Jac<T> j4; HsvJac<T> j5; HsvCurveJac<T> j6; Hsv2RgbJac<T> j7;
+  rgb2lab_fwd<T, WANT_GX>(x, lab, &j1);
+  adjust_self3_fwd<T, true>(lab, ab, lab2, &j2);
+  if (MK == MASK_F32) vscale3(lab2, m);
+  lab2rgb_fwd<T, true>(lab2, rgb, &j3);
+  adjust_self3_fwd<T, true>(rgb, ab + 6, rgb2, &j4);
+  if (MK == MASK_F32) vscale3(rgb2, m);
+  rgb2hsv_fwd<T, true, MK != MASK_F32>(rgb2, hsv, &j5);
+  adjust_hsv_fwd<T, true, true>(hsv, ab + 12, hsv2, &j6);
   if (MK == MASK_F32) {
-    hsv2[0] *= m; hsv2[1] *= m; hsv2[2] *= m;
-    hsv2rgb_fwd<M, true, false>(hsv2, res, &j7);
+    vscale3(hsv2, m);
+    hsv2rgb_fwd<T, true, false>(hsv2, res, &j7);
   } else {
-    hsv2rgb_fwd<M, true, true>(hsv2, res, &j7);
+    hsv2rgb_fwd<T, true, true>(hsv2, res, &j7);
   }
-  float g[3];
+  T g[3];
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
-    const float sum = x[c] + res[c];
-    const float go = (MK == MASK_NONE) ? gout[c] : gout[c] * m;
-    g[c] = (M::sat(sum) == sum) ? go : 0.0f;          // clamp passes on [0,1] inclusive
+    const T sum = vadd(x[c], res[c]);
+    const T pass = vgate_eq(vsat(sum), sum);         // clamp passes on [0,1] inclusive
+    g[c] = vmul(gout[c], (MK == MASK_NONE) ? pass : vmul(pass, m));
   }
-  float a[3], b[3];
-  hsv2rgb_bwd(j7, g, a);
-  if (MK == MASK_F32) { a[0] *= m; a[1] *= m; a[2] *= m; }
+  T a[3], b[3];
+  if (MK == MASK_F32) hsv2rgb_bwd<T, false>(j7, g, a); else hsv2rgb_bwd<T, true>(j7, g, a);
+  if (MK == MASK_F32) vscale3(a, m);
   adjust_hsv_bwd(j6, ab + 12, a, b, mom + 12);
   rgb2hsv_bwd(j5, b, a);
-  if (MK == MASK_F32) { a[0] *= m; a[1] *= m; a[2] *= m; }
+  if (MK == MASK_F32) vscale3(a, m);
   adjust_self3_bwd(j4, a, b, mom + 6);
   lab2rgb_bwd(j3, b, a);
-  if (MK == MASK_F32) { a[0] *= m; a[1] *= m; a[2] *= m; }
+  if (MK == MASK_F32) vscale3(a, m);
   adjust_self3_bwd(j2, a, b, mom + 0);
-  rgb2lab_bwd(j1, b, a);
-  gx[0] = g[0] + a[0]; gx[1] = g[1] + a[1]; gx[2] = g[2] + a[2];
+  if (WANT_GX) {
+    rgb2lab_bwd(j1, b, a);
+    gx[0] = vadd(g[0], a[0]); gx[1] = vadd(g[1], a[1]); gx[2] = vadd(g[2], a[2]);
+  }
 }
 
 }  // namespace curl

@@ -1,0 +1,131 @@
+// Lane types for the per-pixel arithmetic.
+//
+//   float : one pixel per value.  On the device the transcendental helpers are single MUFU ops
+//           (MUFU.LG2 / MUFU.EX2 / MUFU.RCP); on the host (tests/hostsim only -- never the product)
+//           they are double-precision libm rounded to fp32.
+//   F2    : two pixels per value in one 64-bit register pair (device only).  sm_100a has packed
+//           fp32 arithmetic (PTX fma/mul/add.rn.f32x2 -> SASS FFMA2/FMUL2/FADD2): one issue slot does
+//           the work of two scalar instructions, and a scalar register or an immediate is broadcast
+//           to both halves for free.  The layer kernels are issue-bound, not HBM-bound, so this is
+//           the main lever.  Operations with no packed form (MUFU, min/max, compare/select, .SAT)
+//           are done per half.
+//
+// Everything is written once as templates over the lane type T (curl_pixel.cuh) using the v*
+// helpers below; "gates" (clamp-pass indicators, branch selectors) are carried as 0/1 values of
+// type T so that applying them is a (packable) multiply.
+#pragma once
+
+#if defined(__CUDACC__)
+#define CURL_HD __host__ __device__ __forceinline__
+#define CURL_D __device__ __forceinline__
+#else
+#define CURL_HD inline
+#endif
+
+#include <math.h>
+
+namespace curl {
+
+// ------------------------------------------------------------------------------------------------
+// float lanes
+// ------------------------------------------------------------------------------------------------
+CURL_HD float vadd(float a, float b) { return a + b; }
+CURL_HD float vsub(float a, float b) { return a - b; }
+CURL_HD float vmul(float a, float b) { return a * b; }
+CURL_HD float vfma(float a, float b, float c) { return fmaf(a, b, c); }
+CURL_HD float vneg(float a) { return -a; }
+
+CURL_HD float vlg2(float x) {
+#if defined(__CUDA_ARCH__)
+  float y; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y;
+#else
+  return (float)log2((double)x);
+#endif
+}
+CURL_HD float vex2(float x) {
+#if defined(__CUDA_ARCH__)
+  float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y;
+#else
+  return (float)exp2((double)x);
+#endif
+}
+CURL_HD float vrcp(float x) {
+#if defined(__CUDA_ARCH__)
+  float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y;
+#else
+  return (float)(1.0 / (double)x);
+#endif
+}
+// clamp to [0,1]; NaN -> 0 (FADD.SAT semantics), mirrored on the host
+CURL_HD float vsat(float x) {
+#if defined(__CUDA_ARCH__)
+  return __saturatef(x);
+#else
+  return x < 0.f ? 0.f : (x > 1.f ? 1.f : (x == x ? x : 0.f));
+#endif
+}
+CURL_HD float vmul_sat(float a, float b) { return vsat(a * b); }
+CURL_HD float vadd_sat(float a, float b) { return vsat(a + b); }
+CURL_HD float vfma_sat(float a, float b, float c) { return vsat(fmaf(a, b, c)); }
+CURL_HD float vmax(float a, float b) {
+#if defined(__CUDA_ARCH__)
+  return fmaxf(a, b);
+#else
+  return a > b ? a : b;
+#endif
+}
+CURL_HD float vmin(float a, float b) {
+#if defined(__CUDA_ARCH__)
+  return fminf(a, b);
+#else
+  return a < b ? a : b;
+#endif
+}
+// 0/1 gates and selects
+CURL_HD float vgate_le(float a, float b) { return a <= b ? 1.0f : 0.0f; }
+CURL_HD float vgate_lt(float a, float b) { return a < b ? 1.0f : 0.0f; }
+CURL_HD float vgate_eq(float a, float b) { return a == b ? 1.0f : 0.0f; }
+CURL_HD float vgate_ne(float a, float b) { return a != b ? 1.0f : 0.0f; }
+CURL_HD float vsel_le(float a, float b, float t, float f) { return a <= b ? t : f; }   // a <= b ? t : f
+CURL_HD float vsel_lt(float a, float b, float t, float f) { return a < b ? t : f; }
+CURL_HD float vsel_eq(float a, float b, float t, float f) { return a == b ? t : f; }
+CURL_HD float vhsum(float a) { return a; }   // horizontal sum over the lanes of one value
+
+// ------------------------------------------------------------------------------------------------
+// F2 lanes (device only)
+// ------------------------------------------------------------------------------------------------
+#if defined(__CUDACC__)
+struct F2 {
+  unsigned long long u;
+  F2() = default;
+  CURL_D F2(float c) { asm("mov.b64 %0, {%1,%1};" : "=l"(u) : "f"(c)); }          // broadcast
+  CURL_D F2(float lo, float hi) { asm("mov.b64 %0, {%1,%2};" : "=l"(u) : "f"(lo), "f"(hi)); }
+  CURL_D float lo() const { float a, b; asm("mov.b64 {%0,%1}, %2;" : "=f"(a), "=f"(b) : "l"(u)); return a; }
+  CURL_D float hi() const { float a, b; asm("mov.b64 {%0,%1}, %2;" : "=f"(a), "=f"(b) : "l"(u)); return b; }
+};
+CURL_D F2 vadd(F2 a, F2 b) { F2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r.u) : "l"(a.u), "l"(b.u)); return r; }
+CURL_D F2 vmul(F2 a, F2 b) { F2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r.u) : "l"(a.u), "l"(b.u)); return r; }
+CURL_D F2 vfma(F2 a, F2 b, F2 c) {
+  F2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r.u) : "l"(a.u), "l"(b.u), "l"(c.u)); return r;
+}
+CURL_D F2 vsub(F2 a, F2 b) { return vfma(b, F2(-1.0f), a); }
+CURL_D F2 vneg(F2 a) { return vmul(a, F2(-1.0f)); }
+
+#define CURL_F2_MAP1(name)                                            \
+  CURL_D F2 name(F2 a) { return F2(name(a.lo()), name(a.hi())); }
+#define CURL_F2_MAP2(name)                                            \
+  CURL_D F2 name(F2 a, F2 b) { return F2(name(a.lo(), b.lo()), name(a.hi(), b.hi())); }
+#define CURL_F2_MAP3(name)                                            \
+  CURL_D F2 name(F2 a, F2 b, F2 c) { return F2(name(a.lo(), b.lo(), c.lo()), name(a.hi(), b.hi(), c.hi())); }
+#define CURL_F2_MAP4(name)                                            \
+  CURL_D F2 name(F2 a, F2 b, F2 c, F2 d) {                            \
+    return F2(name(a.lo(), b.lo(), c.lo(), d.lo()), name(a.hi(), b.hi(), c.hi(), d.hi())); }
+CURL_F2_MAP1(vlg2) CURL_F2_MAP1(vex2) CURL_F2_MAP1(vrcp) CURL_F2_MAP1(vsat)
+CURL_F2_MAP2(vmul_sat) CURL_F2_MAP2(vadd_sat) CURL_F2_MAP3(vfma_sat)
+CURL_F2_MAP2(vmax) CURL_F2_MAP2(vmin)
+CURL_F2_MAP2(vgate_le) CURL_F2_MAP2(vgate_lt) CURL_F2_MAP2(vgate_eq) CURL_F2_MAP2(vgate_ne)
+CURL_F2_MAP4(vsel_le) CURL_F2_MAP4(vsel_lt) CURL_F2_MAP4(vsel_eq)
+CURL_D float vhsum(F2 a) { return a.lo() + a.hi(); }
+#endif  // __CUDACC__
+
+}  // namespace curl

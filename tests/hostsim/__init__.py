@@ -9,6 +9,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(HERE, "pixel_sim.cpp")
 HDR = os.path.join(HERE, "..", "..", "curl_b200", "csrc", "curl_pixel.cuh")
+HDR2 = os.path.join(HERE, "..", "..", "curl_b200", "csrc", "curl_vec.cuh")
 OUT = os.path.join(HERE, "_build", "libpixel_sim.so")
 
 _lib = None
@@ -18,7 +19,7 @@ def lib():
     global _lib
     if _lib is not None:
         return _lib
-    newest = max(os.path.getmtime(SRC), os.path.getmtime(HDR))
+    newest = max(os.path.getmtime(SRC), os.path.getmtime(HDR), os.path.getmtime(HDR2))
     if not os.path.exists(OUT) or os.path.getmtime(OUT) < newest:
         os.makedirs(os.path.dirname(OUT), exist_ok=True)
         subprocess.check_call(["g++", "-O2", "-std=c++17", "-shared", "-fPIC", "-o", OUT, SRC])

@@ -1,8 +1,8 @@
 // TEST INFRASTRUCTURE ONLY -- host instantiation of curl_b200/csrc/curl_pixel.cuh.
 //
 // The per-pixel forward/backward functions the sm_100a kernels are built from are plain templates
-// over a math policy.  This file instantiates them with HostMath (double-precision libm rounded to
-// fp32 in place of MUFU.LG2/EX2/RCP) behind a small C interface so that the CPU-only test suite
+// over a math policy.  This file instantiates them with T = float on the host (double-precision libm
+// rounded to fp32 in place of MUFU.LG2/EX2/RCP) behind a small C interface so that the CPU-only test suite
 // can check the hand-derived reverse-mode code, the tie/clamp/branch semantics and the knot-gradient
 // moment expansion against the oracle without a GPU.  It is compiled by tests/ on demand into
 // tests/hostsim/_build/ and is never part of, linked into, or reachable from the product library.
@@ -61,10 +61,10 @@ float mask_at(const void* mask, int kind, size_t i) {
 }
 
 template <int MK>
-void layer_fwd_mk(const float x[3], float m, const float* ab, float y[3]) { layer_fwd<HostMath, MK>(x, m, ab, y); }
+void layer_fwd_mk(const float x[3], float m, const float* ab, float y[3]) { layer_fwd<float, MK>(x, m, ab, y); }
 template <int MK>
 void layer_bwd_mk(const float x[3], float m, const float* ab, const float gy[3], float gx[3], float* mom) {
-  layer_bwd<HostMath, MK>(x, m, ab, gy, gx, mom);
+  layer_bwd<float, MK, true>(x, m, ab, gy, gx, mom);
 }
 
 }  // namespace
@@ -117,10 +117,10 @@ int sim_color(int do_bwd, int conv, const float* in, const float* gout, float* o
       float gy[3] = {0, 0, 0};
       if (do_bwd) { gy[0] = gout[o]; gy[1] = gout[o + HW]; gy[2] = gout[o + 2 * (size_t)HW]; }
       switch (conv) {
-        case 0: { LabJac j; rgb2lab_fwd<HostMath, true>(x, y, &j); rgb2lab_bwd(j, gy, r); break; }
-        case 1: { RgbJac j; lab2rgb_fwd<HostMath, true>(x, y, &j); lab2rgb_bwd(j, gy, r); break; }
-        case 2: { HsvJac j; rgb2hsv_fwd<HostMath, true, false>(x, y, &j); rgb2hsv_bwd(j, gy, r); break; }
-        case 3: { Hsv2RgbJac j; hsv2rgb_fwd<HostMath, true, false>(x, y, &j); hsv2rgb_bwd(j, gy, r); break; }
+        case 0: { LabJac<float> j; rgb2lab_fwd<float, true>(x, y, &j); rgb2lab_bwd(j, gy, r); break; }
+        case 1: { RgbJac<float> j; lab2rgb_fwd<float, true>(x, y, &j); lab2rgb_bwd(j, gy, r); break; }
+        case 2: { HsvJac<float> j; rgb2hsv_fwd<float, true, false>(x, y, &j); rgb2hsv_bwd(j, gy, r); break; }
+        case 3: { Hsv2RgbJac<float> j; hsv2rgb_fwd<float, true, false>(x, y, &j); hsv2rgb_bwd<float, false>(j, gy, r); break; }
         default: return -1;
       }
       const float* w = do_bwd ? r : y;
@@ -146,12 +146,12 @@ int sim_adjust(int do_bwd, int group, const float* in, const float* P, int64_t l
       float mom[8] = {0, 0, 0, 0, 0, 0, 0, 0};
       if (do_bwd) { gy[0] = gout[o]; gy[1] = gout[o + HW]; gy[2] = gout[o + 2 * (size_t)HW]; }
       if (group == 2) {
-        HsvCurveJac j;
-        adjust_hsv_fwd<HostMath, true, false>(x, cv.ab.data(), y, &j);
+        HsvCurveJac<float> j;
+        adjust_hsv_fwd<float, true, false>(x, cv.ab.data(), y, &j);
         adjust_hsv_bwd(j, cv.ab.data(), gy, gx, mom);
       } else {
-        Self3Jac j;
-        adjust_self3_fwd<HostMath, true>(x, cv.ab.data(), y, &j);
+        Self3Jac<float> j;
+        adjust_self3_fwd<float, true>(x, cv.ab.data(), y, &j);
         adjust_self3_bwd(j, gy, gx, mom);
       }
       if (!do_bwd) { out[o] = y[0]; out[o + HW] = y[1]; out[o + 2 * (size_t)HW] = y[2]; }

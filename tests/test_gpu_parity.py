@@ -57,7 +57,7 @@ def test_layer_vs_golden(case, layer_golden):
     rep["out"] = parity.check_image(case, ours["out"], r32["out"], r64["out"])
     assert parity.rel_to_max(ours["reg"], r64["reg"]) <= 1e-5
     gscale = float(np.abs(r64["gimg"]).max())
-    rep["gimg"] = parity.check_image(case, ours["gimg"], r32["gimg"], r64["gimg"], scale=gscale)
+    rep["gimg"] = parity.check_image(case, ours["gimg"], r32["gimg"], r64["gimg"], scale=gscale, tol=parity.GRAD_TOL)
     for k in ("gL", "gR", "gH"):
         assert ours[k].shape == r32[k].shape
         if case == "identity":
@@ -166,7 +166,8 @@ def test_layer_vs_oracle_seeded(shape, maskdtype):
     n = lambda t: t.detach().cpu().numpy()
     rep = dict(out=parity.check_image("smooth", n(out), n(r32["out"]), n(r64["out"])))
     gscale = float(r64["gimg"].abs().max())
-    rep["gimg"] = parity.check_image("smooth", n(ig.grad), n(r32["gimg"]), n(r64["gimg"]), scale=gscale)
+    rep["gimg"] = parity.check_image("smooth", n(ig.grad), n(r32["gimg"]), n(r64["gimg"]), scale=gscale,
+                                     tol=parity.GRAD_TOL)
     for k, t in (("gL", Lg), ("gR", Rg), ("gH", Hg)):
         rep[k] = parity.check_knots("smooth", n(t.grad), n(r32[k]), n(r64[k]))
     REPORT[f"seeded.{shape}.{maskdtype}"] = rep
