@@ -15,6 +15,9 @@
 namespace curl {
 
 constexpr int THREADS = 256;
+#ifndef BWD_THREADS
+#define BWD_THREADS 256
+#endif
 #ifndef BWD_MIN_BLOCKS
 #define BWD_MIN_BLOCKS 1
 #endif
@@ -54,9 +57,13 @@ struct OpLayer {
   static __device__ __forceinline__ void fwd(const T x[3], T m, const float* ab, int, T y[3]) {
     layer_fwd<T, MK>(x, m, ab, y);
   }
-  template <int MK, bool WANT_GX, class T>
-  static __device__ __forceinline__ void bwd(const T x[3], T m, const float* ab, int, const T gy[3], T gx[3], T* mom) {
-    layer_bwd<T, MK, WANT_GX>(x, m, ab, gy, gx, mom);
+  // Measured on B200: parking the first four Jac records in shared memory (SPILL_SLOTS) does not lower
+  // ptxas' register allocation for this kernel and costs 30 extra LDS/STS per pixel, so it is off.
+  static constexpr int SPILL = 0;
+  template <int MK, bool WANT_GX, class T, class SP>
+  static __device__ __forceinline__ void bwd(const T x[3], T m, const float* ab, int, const T gy[3], T gx[3], T* mom,
+                                             const SP& sp) {
+    layer_bwd<T, MK, WANT_GX, SP>(x, m, ab, gy, gx, mom, sp);
   }
 };
 
@@ -70,8 +77,9 @@ struct OpColor {
     if (CONV == CURL_RGB2HSV) rgb2hsv_fwd<T, false, false>(x, y, nullptr);
     if (CONV == CURL_HSV2RGB) hsv2rgb_fwd<T, false, false>(x, y, nullptr);
   }
-  template <int MK, bool WANT_GX, class T>
-  static __device__ __forceinline__ void bwd(const T x[3], T, const float*, int, const T gy[3], T gx[3], T*) {
+  static constexpr int SPILL = 0;
+  template <int MK, bool WANT_GX, class T, class SP>
+  static __device__ __forceinline__ void bwd(const T x[3], T, const float*, int, const T gy[3], T gx[3], T*, const SP&) {
     T y[3];
     if (CONV == CURL_RGB2LAB) { LabJac<T> j; rgb2lab_fwd<T, true>(x, y, &j); rgb2lab_bwd(j, gy, gx); }
     if (CONV == CURL_LAB2RGB) { RgbJac<T> j; lab2rgb_fwd<T, true>(x, y, &j); lab2rgb_bwd(j, gy, gx); }
@@ -86,8 +94,10 @@ struct OpAdjustSelf3 {  // adjust_lab, adjust_rgb
   static __device__ __forceinline__ void fwd(const T x[3], T, const float* ab, int, T y[3]) {
     adjust_self3_fwd<T, false>(x, ab, y, nullptr);
   }
-  template <int MK, bool WANT_GX, class T>
-  static __device__ __forceinline__ void bwd(const T x[3], T, const float* ab, int, const T gy[3], T gx[3], T* mom) {
+  static constexpr int SPILL = 0;
+  template <int MK, bool WANT_GX, class T, class SP>
+  static __device__ __forceinline__ void bwd(const T x[3], T, const float* ab, int, const T gy[3], T gx[3], T* mom,
+                                             const SP&) {
     T y[3]; Self3Jac<T> j;
     adjust_self3_fwd<T, true>(x, ab, y, &j);
     adjust_self3_bwd(j, gy, gx, mom);
@@ -100,8 +110,10 @@ struct OpAdjustHsv {
   static __device__ __forceinline__ void fwd(const T x[3], T, const float* ab, int, T y[3]) {
     adjust_hsv_fwd<T, false, false>(x, ab, y, nullptr);
   }
-  template <int MK, bool WANT_GX, class T>
-  static __device__ __forceinline__ void bwd(const T x[3], T, const float* ab, int, const T gy[3], T gx[3], T* mom) {
+  static constexpr int SPILL = 0;
+  template <int MK, bool WANT_GX, class T, class SP>
+  static __device__ __forceinline__ void bwd(const T x[3], T, const float* ab, int, const T gy[3], T gx[3], T* mom,
+                                             const SP&) {
     T y[3]; HsvCurveJac<T> j;
     adjust_hsv_fwd<T, true, false>(x, ab, y, &j);
     adjust_hsv_bwd(j, ab, gy, gx, mom);
@@ -114,8 +126,10 @@ struct OpCurve1 {  // curves.apply_curve: one curve channel_in -> channel_out, k
   static __device__ __forceinline__ void fwd(const T x[3], T, const float* ab, int aux, T y[3]) {
     single_curve_fwd<T>(x, aux & 3, (aux >> 2) & 3, ab[0], ab[1], y);
   }
-  template <int MK, bool WANT_GX, class T>
-  static __device__ __forceinline__ void bwd(const T x[3], T, const float* ab, int aux, const T gy[3], T gx[3], T* mom) {
+  static constexpr int SPILL = 0;
+  template <int MK, bool WANT_GX, class T, class SP>
+  static __device__ __forceinline__ void bwd(const T x[3], T, const float* ab, int aux, const T gy[3], T gx[3], T* mom,
+                                             const SP&) {
     single_curve_bwd<T>(x, aux & 3, (aux >> 2) & 3, ab[0], ab[1], gy, gx, mom);
   }
 };
@@ -257,11 +271,11 @@ __global__ void __launch_bounds__(THREADS) fwd_kernel(const KParams p) {
 // image folds all partial rows in a fixed order (in double, bitwise deterministic) and expands the
 // 2 moments per curve into the knot gradients (curve_knot_grad).
 // ---------------------------------------------------------------------------------------------
-template <int NC, class T>
+template <int NC, class T, int NT>
 __device__ __forceinline__ void finish_knot_grads(const KParams& p, int b, const T* mom, const float* s_C,
                                                   double* s_mom, float* s_part, unsigned* s_ticket_p) {
   constexpr int NM = 2 * NC;
-  constexpr int NWARPS = THREADS / 32;
+  constexpr int NWARPS = NT / 32;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
   for (int k = 0; k < NM; ++k) {
@@ -299,7 +313,7 @@ __device__ __forceinline__ void finish_knot_grads(const KParams& p, int b, const
   for (int s = 0; s < p.nseg; ++s) {
     const int K = p.seg[s].K, n = p.seg[s].nc * K;
     float* g = p.seg[s].g + (size_t)b * n;
-    for (int i = threadIdx.x; i < n; i += THREADS) {
+    for (int i = threadIdx.x; i < n; i += NT) {
       const int c = i / K, kk = i - c * K;
       g[i] = curve_knot_grad(s_C + off + c * K, K, kk, s_mom[2 * (cbase + c)], s_mom[2 * (cbase + c) + 1], greg,
                              p.linear_knots == 0);
@@ -348,13 +362,13 @@ __global__ void __launch_bounds__(THREADS, BWD_MIN_BLOCKS) bwd_kernel(const KPar
       const T x[3] = {c0.v[v], c1.v[v], c2.v[v]};
       const T gy[3] = {g0.v[v], g1.v[v], g2.v[v]};
       T gx[3];
-      Op::template bwd<MK, WANT_GIN, T>(x, m.v[v], s_ab, p.aux, gy, gx, mom);
+      Op::template bwd<MK, WANT_GIN, T>(x, m.v[v], s_ab, p.aux, gy, gx, mom, KeepInRegisters());
       o0.v[v] = gx[0]; o1.v[v] = gx[1]; o2.v[v] = gx[2];
     }
     if (WANT_GIN) { o0.st(gin + i); o1.st(gin + HW + i); o2.st(gin + 2 * (size_t)HW + i); }
   }
 
-  if (NC > 0) finish_knot_grads<NC, T>(p, b, mom, s_C, s_mom, s_part, &s_ticket);
+  if (NC > 0) finish_knot_grads<NC, T, THREADS>(p, b, mom, s_C, s_mom, s_part, &s_ticket);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -390,17 +404,32 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned by
                : "memory");
 }
 
-constexpr int TMA_TILE = THREADS * 2;   // pixels per tile: one packed pair per thread
-constexpr int TMA_STAGES = 6;
+constexpr int TMA_TILE = BWD_THREADS * 2;   // pixels per tile: one packed pair per thread
+#ifndef TMA_STAGES_N
+#define TMA_STAGES_N 6
+#endif
+constexpr int TMA_STAGES = TMA_STAGES_N;
 constexpr int TMA_PLANES = 6;           // x0 x1 x2 g0 g1 g2
-constexpr size_t TMA_SMEM_BYTES = (size_t)TMA_STAGES * TMA_PLANES * TMA_TILE * sizeof(float);
+constexpr size_t TMA_RING_BYTES = (size_t)TMA_STAGES * TMA_PLANES * TMA_TILE * sizeof(float);
+template <class Op> constexpr size_t tma_smem_bytes() {
+  return TMA_RING_BYTES + (size_t)Op::SPILL * BWD_THREADS * sizeof(F2);
+}
+
+// Shared-memory parking space for Jac records (curl_pixel.cuh "Spill policies"): slot-major, one
+// 8-byte column per thread, so a warp's STS.64/LDS.64 touches 256 consecutive bytes.
+struct SmemSpill {
+  static constexpr bool kActive = true;
+  F2* base;   // already offset by threadIdx.x
+  __device__ __forceinline__ void put(int slot, F2 v) const { base[slot * BWD_THREADS] = v; }
+  __device__ __forceinline__ F2 get(int slot) const { return base[slot * BWD_THREADS]; }
+};
 
 // Backward, aligned path (HW % 4 == 0, 16-byte aligned bases).  Same math as bwd_kernel<.., 2, ..>.
 template <class Op, int MK, bool WANT_GIN>
-__global__ void __launch_bounds__(THREADS, BWD_MIN_BLOCKS) bwd_tma_kernel(const KParams p) {
+__global__ void __launch_bounds__(BWD_THREADS, BWD_MIN_BLOCKS) bwd_tma_kernel(const KParams p) {
   constexpr int NC = Op::NC;
   constexpr int NM = 2 * NC;
-  constexpr int NWARPS = THREADS / 32;
+  constexpr int NWARPS = BWD_THREADS / 32;
   extern __shared__ __align__(128) float s_ring[];   // [STAGES][PLANES][TILE]
   __shared__ __align__(8) unsigned long long s_full[TMA_STAGES];
   __shared__ float s_C[NC > 0 ? CURL_MAX_KNOTS : 1];
@@ -489,14 +518,19 @@ __global__ void __launch_bounds__(THREADS, BWD_MIN_BLOCKS) bwd_tma_kernel(const 
     if (threadIdx.x == 0 && it + TMA_STAGES < n_my) issue(it + TMA_STAGES);
     if (!valid) m = T(0.0f);
     T gx[3];
-    Op::template bwd<MK, WANT_GIN, T>(x, m, s_ab, p.aux, gy, gx, mom);
+    if constexpr (Op::SPILL > 0) {
+      const SmemSpill sp{reinterpret_cast<F2*>(reinterpret_cast<unsigned char*>(s_ring) + TMA_RING_BYTES) + threadIdx.x};
+      Op::template bwd<MK, WANT_GIN, T>(x, m, s_ab, p.aux, gy, gx, mom, sp);
+    } else {
+      Op::template bwd<MK, WANT_GIN, T>(x, m, s_ab, p.aux, gy, gx, mom, KeepInRegisters());
+    }
     if (WANT_GIN && valid) {
 #pragma unroll
       for (int c = 0; c < 3; ++c)
         __stcs(reinterpret_cast<float2*>(gin + (size_t)c * HW + px), make_float2(gx[c].lo(), gx[c].hi()));
     }
   }
-  if (NC > 0) finish_knot_grads<NC, T>(p, b, mom, s_C, s_mom, s_part, &s_ticket);
+  if (NC > 0) finish_knot_grads<NC, T, BWD_THREADS>(p, b, mom, s_C, s_mom, s_part, &s_ticket);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -561,12 +595,12 @@ static int launch_bwd(KParams& p, int B, bool vec4, void* ws, size_t ws_bytes, c
   if (vec4) {
     if (want) {
       if (cudaFuncSetAttribute(bwd_tma_kernel<Op, MK, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                               (int)TMA_SMEM_BYTES) != cudaSuccess) return CURL_ERR_LAUNCH;
-      bwd_tma_kernel<Op, MK, true><<<grid, THREADS, TMA_SMEM_BYTES, st>>>(p);
+                               (int)tma_smem_bytes<Op>()) != cudaSuccess) return CURL_ERR_LAUNCH;
+      bwd_tma_kernel<Op, MK, true><<<grid, BWD_THREADS, tma_smem_bytes<Op>(), st>>>(p);
     } else {
       if (cudaFuncSetAttribute(bwd_tma_kernel<Op, MK, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                               (int)TMA_SMEM_BYTES) != cudaSuccess) return CURL_ERR_LAUNCH;
-      bwd_tma_kernel<Op, MK, false><<<grid, THREADS, TMA_SMEM_BYTES, st>>>(p);
+                               (int)tma_smem_bytes<Op>()) != cudaSuccess) return CURL_ERR_LAUNCH;
+      bwd_tma_kernel<Op, MK, false><<<grid, BWD_THREADS, tma_smem_bytes<Op>(), st>>>(p);
     }
   } else {
     if (want) bwd_kernel<Op, MK, 1, true><<<grid, THREADS, 0, st>>>(p);

@@ -513,16 +513,58 @@ CURL_HD void layer_fwd(const T x[3], T m, const float* ab, T out[3]) {
   }
 }
 
+// Spill policies for the backward pass.  At the turning point of the reverse sweep every stage's
+// Jac record is live (66 values of T), which is what limits the kernel to 8 warps per SM.  The
+// records of the first four stages are not needed again until the very end, so the sm_100a kernel
+// parks them in shared memory (one 8-byte column per thread: conflict-free) and gets them back
+// when the reverse sweep reaches their stage.  KeepInRegisters is the no-op policy (host check,
+// scalar tail path).
+struct KeepInRegisters {
+  static constexpr bool kActive = false;
+};
+constexpr int SPILL_SLOTS = 30;   // LabJac 6 + Self3Jac 9 + RgbJac 6 + Self3Jac 9
+
+template <class T, class S> CURL_HD void spill_save(const S& sp, int o, const LabJac<T>& j) {
+#pragma unroll
+  for (int c = 0; c < 3; ++c) { sp.put(o + c, j.d_lin[c]); sp.put(o + 3 + c, j.d_f[c]); }
+}
+template <class T, class S> CURL_HD void spill_load(const S& sp, int o, LabJac<T>& j) {
+#pragma unroll
+  for (int c = 0; c < 3; ++c) { j.d_lin[c] = sp.get(o + c); j.d_f[c] = sp.get(o + 3 + c); }
+}
+template <class T, class S> CURL_HD void spill_save(const S& sp, int o, const RgbJac<T>& j) {
+#pragma unroll
+  for (int c = 0; c < 3; ++c) { sp.put(o + c, j.d_finv[c]); sp.put(o + 3 + c, j.d_gam[c]); }
+}
+template <class T, class S> CURL_HD void spill_load(const S& sp, int o, RgbJac<T>& j) {
+#pragma unroll
+  for (int c = 0; c < 3; ++c) { j.d_finv[c] = sp.get(o + c); j.d_gam[c] = sp.get(o + 3 + c); }
+}
+template <class T, class S> CURL_HD void spill_save(const S& sp, int o, const Self3Jac<T>& j) {
+#pragma unroll
+  for (int c = 0; c < 3; ++c) { sp.put(o + 3 * c, j.c[c].xin); sp.put(o + 3 * c + 1, j.c[c].a); sp.put(o + 3 * c + 2, j.c[c].d); }
+}
+template <class T, class S> CURL_HD void spill_load(const S& sp, int o, Self3Jac<T>& j) {
+#pragma unroll
+  for (int c = 0; c < 3; ++c) { j.c[c].xin = sp.get(o + 3 * c); j.c[c].a = sp.get(o + 3 * c + 1); j.c[c].d = sp.get(o + 3 * c + 2); }
+}
+
 // Recompute-forward + reverse.  mom: 20 accumulators (S0,S1 per curve), accumulated in place.
-template <class T, int MK, bool WANT_GX>
-CURL_HD void layer_bwd(const T x[3], T m, const float* ab, const T gout[3], T gx[3], T* mom) {
+// SPILL: a policy with put(slot, T) / get(slot) (see above) or KeepInRegisters.
+template <class T, int MK, bool WANT_GX, class SPILL>
+CURL_HD void layer_bwd(const T x[3], T m, const float* ab, const T gout[3], T gx[3], T* mom, const SPILL& sp) {
+  constexpr bool kSpill = SPILL::kActive;
   T lab[3], lab2[3], rgb[3], rgb2[3], hsv[3], hsv2[3], res[3];
   LabJac<T> j1; Self3Jac<T> j2; RgbJac<T> j3; Self3Jac<T> j4; HsvJac<T> j5; HsvCurveJac<T> j6; Hsv2RgbJac<T> j7;
   rgb2lab_fwd<T, WANT_GX>(x, lab, &j1);
+  if constexpr (kSpill && WANT_GX) spill_save<T>(sp, 0, j1);
   adjust_self3_fwd<T, true>(lab, ab, lab2, &j2);
+  if constexpr (kSpill) spill_save<T>(sp, 6, j2);
   if (MK == MASK_F32) vscale3(lab2, m);
   lab2rgb_fwd<T, true>(lab2, rgb, &j3);
+  if constexpr (kSpill) spill_save<T>(sp, 15, j3);
   adjust_self3_fwd<T, true>(rgb, ab + 6, rgb2, &j4);
+  if constexpr (kSpill) spill_save<T>(sp, 21, j4);
   if (MK == MASK_F32) vscale3(rgb2, m);
   rgb2hsv_fwd<T, true, MK != MASK_F32>(rgb2, hsv, &j5);
   adjust_hsv_fwd<T, true, true>(hsv, ab + 12, hsv2, &j6);
@@ -545,11 +587,15 @@ CURL_HD void layer_bwd(const T x[3], T m, const float* ab, const T gout[3], T gx
   adjust_hsv_bwd(j6, ab + 12, a, b, mom + 12);
   rgb2hsv_bwd(j5, b, a);
   if (MK == MASK_F32) vscale3(a, m);
+  if constexpr (kSpill) spill_load<T>(sp, 21, j4);
   adjust_self3_bwd(j4, a, b, mom + 6);
+  if constexpr (kSpill) spill_load<T>(sp, 15, j3);
   lab2rgb_bwd(j3, b, a);
   if (MK == MASK_F32) vscale3(a, m);
+  if constexpr (kSpill) spill_load<T>(sp, 6, j2);
   adjust_self3_bwd(j2, a, b, mom + 0);
   if (WANT_GX) {
+    if constexpr (kSpill) spill_load<T>(sp, 0, j1);
     rgb2lab_bwd(j1, b, a);
     gx[0] = vadd(g[0], a[0]); gx[1] = vadd(g[1], a[1]); gx[2] = vadd(g[2], a[2]);
   }

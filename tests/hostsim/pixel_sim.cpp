@@ -64,7 +64,7 @@ template <int MK>
 void layer_fwd_mk(const float x[3], float m, const float* ab, float y[3]) { layer_fwd<float, MK>(x, m, ab, y); }
 template <int MK>
 void layer_bwd_mk(const float x[3], float m, const float* ab, const float gy[3], float gx[3], float* mom) {
-  layer_bwd<float, MK, true>(x, m, ab, gy, gx, mom);
+  layer_bwd<float, MK, true>(x, m, ab, gy, gx, mom, KeepInRegisters());
 }
 
 }  // namespace

@@ -1,0 +1,77 @@
+"""CPU: the kernel's per-pixel templates (curl_b200/csrc/curl_pixel.cuh), instantiated on the host
+with T = float by tests/hostsim, against the golden fixtures.  This checks the hand-derived
+reverse-mode code, the clamp/tie/branch semantics and the moment -> knot-gradient expansion without
+a GPU; the GPU tests then only have to establish that the MUFU approximations and the packed
+arithmetic stay inside the same bounds."""
+import numpy as np
+import pytest
+
+import hostsim
+import parity
+from conftest import LAYER_CASES, STAGE_CASES
+
+
+@pytest.mark.parametrize("case", LAYER_CASES)
+def test_hostsim_layer_vs_golden(case, layer_golden):
+    g = layer_golden
+    pts = tuple(int(v) for v in g[f"{case}.pts"])
+    args = [g[f"{case}.{k}"] for k in ("img", "mask", "L", "R", "H")]
+    fwd = hostsim.layer(*args, pts)
+    bwd = hostsim.layer(*args, pts, gout=g[f"{case}.gout"], greg=g[f"{case}.greg"])
+    r32 = {k: g[f"{case}.f32.{k}"] for k in ("out", "reg", "gimg", "gL", "gR", "gH")}
+    r64 = {k: g[f"{case}.f64.{k}"] for k in ("out", "reg", "gimg", "gL", "gR", "gH")}
+    parity.check_image(case, fwd["out"], r32["out"], r64["out"])
+    assert parity.rel_to_max(fwd["reg"], r64["reg"]) <= 1e-5
+    gscale = float(np.abs(r64["gimg"]).max())
+    if np.isfinite(gscale) and gscale > 0:
+        parity.check_image(case, bwd["gimg"], r32["gimg"], r64["gimg"], scale=gscale, tol=parity.GRAD_TOL)
+    for k, n in (("gL", pts[0]), ("gR", pts[1]), ("gH", pts[2])):
+        assert bwd[k].shape[1] == n
+        if case == "identity":
+            continue
+        parity.check_knots(case, bwd[k], r32[k][:, :n], r64[k][:, :n])
+        # columns beyond num_*_points are sliced away by the layer: the reference gradient is zero there
+        assert np.all(r64[k][:, n:] == 0)
+
+
+@pytest.mark.parametrize("case", STAGE_CASES)
+@pytest.mark.parametrize("conv,name", [(0, "rgb2lab"), (1, "lab2rgb"), (2, "rgb2hsv"), (3, "hsv2rgb")])
+def test_hostsim_colors_vs_golden(case, conv, name, stage_golden):
+    g = stage_golden
+    x, gy = g[f"{case}.x"], g[f"{case}.gy"]
+    y = hostsim.color(conv, x)
+    gx = hostsim.color(conv, x, gy)
+    y64 = g[f"{case}.{name}.f64.y"]
+    scale = max(1.0, float(np.abs(y64).max()))
+    kind = "smooth" if case == "unit" and name != "rgb2hsv" else "edges"
+    parity.check_image(kind, y, g[f"{case}.{name}.f32.y"], y64, scale=scale)
+    gx64 = g[f"{case}.{name}.f64.gx"]
+    parity.check_image("edges", gx, g[f"{case}.{name}.f32.gx"], gx64, scale=float(np.abs(gx64).max()), tol=2e-5)
+
+
+@pytest.mark.parametrize("case", STAGE_CASES)
+@pytest.mark.parametrize("group,name,K", [(0, "adjust_lab", 16), (1, "adjust_rgb", 16), (2, "adjust_hsv", 16)])
+def test_hostsim_adjust_vs_golden(case, group, name, K, stage_golden):
+    g = stage_golden
+    x, gy, P = g[f"{case}.x"], g[f"{case}.gy"], g[f"{case}.{name}.P"]
+    f = hostsim.adjust(group, x, P, K)
+    b = hostsim.adjust(group, x, P, K, gy=gy, greg=np.ones(x.shape[0], np.float32))
+    pre = f"{case}.{name}"
+    kind = "smooth" if case == "unit" else "edges"
+    parity.check_image(kind, f["y"], g[f"{pre}.f32.y"], g[f"{pre}.f64.y"])
+    assert parity.rel_to_max(f["reg"], g[f"{pre}.f64.reg"]) <= 1e-5
+    gx64 = g[f"{pre}.f64.gx"]
+    parity.check_image(kind, b["gx"], g[f"{pre}.f32.gx"], gx64, scale=float(np.abs(gx64).max()), tol=parity.GRAD_TOL)
+    parity.check_knots(kind, b["gP"], g[f"{pre}.f32.gP"], g[f"{pre}.f64.gP"])
+
+
+def test_hostsim_tie_semantics():
+    """Hue selectors add on ties; grey pixels give h = s = 1e-9; max/min route to the first index."""
+    px = lambda r, g, b: np.array([r, g, b], np.float32).reshape(1, 3, 1, 1)
+    assert abs(hostsim.color(2, px(0.5, 0.5, 0.2))[0, 0, 0, 0] - 1 / 3) < 1e-6
+    assert abs(hostsim.color(2, px(0.2, 0.5, 0.5))[0, 0, 0, 0] - 1.0) < 1e-6
+    assert abs(hostsim.color(2, px(0.5, 0.2, 0.5))[0, 0, 0, 0] - 2 / 3) < 1e-6
+    grey = hostsim.color(2, px(0.3, 0.3, 0.3))[0, :, 0, 0]
+    assert grey[0] == np.float32(1e-9) and grey[1] == np.float32(1e-9) and grey[2] == np.float32(0.3)
+    gx = hostsim.color(2, px(0.3, 0.3, 0.3), np.array([0, 0, 1], np.float32).reshape(1, 3, 1, 1))[0, :, 0, 0]
+    assert gx.tolist() == [1.0, 0.0, 0.0]      # d v / d rgb goes to channel 0 on a three-way tie

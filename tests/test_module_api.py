@@ -1,0 +1,90 @@
+"""CPU: the reference-facing module API (names, constructor arguments, state-dict keys/shapes,
+error behaviour).  Compute needs a GPU and is covered by tests/test_gpu_parity.py."""
+import pytest
+import torch
+
+import curl_b200
+from curl_b200 import colors, curves
+from oracle import curl_oracle as O
+from oracle import ref_loader
+
+
+def test_state_dict_matches_reference_layout():
+    layer = curl_b200.CURLLayer()
+    sd = layer.state_dict()
+    ref = O.constants()          # names/shapes/values of the reference's CURLLayer().state_dict()
+    assert list(sd) == ["rgb2lab.rgb_to_xyz", "rgb2lab.fxfyfz_to_lab", "rgb2lab.xyz_to_rgb_mult",
+                        "rgb2lab.lab_to_fxfyfz_offset", "lab2rgb.xyz_to_rgb", "lab2rgb.lab_to_fxfyfz",
+                        "lab2rgb.xyz_to_rgb_mult", "lab2rgb.lab_to_fxfyfz_offset", "rgb2hsv.comparison_zero"]
+    for k, v in sd.items():
+        assert v.shape == ref[k].shape and torch.equal(v, ref[k]), k
+    assert all(not p.requires_grad for p in layer.parameters())
+    assert (layer.num_lab_points, layer.num_rgb_points, layer.num_hsv_points) == (48, 48, 64)
+    assert curl_b200.CURLLayer(30, 18, 40).num_hsv_points == 40
+
+
+def test_strict_load_and_legacy_matrix_conversion():
+    """Strict load_state_dict (main.py:184,246; infer.py:29) and convert_state.py:11-13, which reshapes
+    legacy 2-D colour matrices to [1,1,3,3] by key name, keep working."""
+    layer = curl_b200.CURLLayer()
+    sd = {("module." + k): v.clone() for k, v in O.constants().items()}
+    for k in list(sd):
+        if sd[k].dim() == 4 and sd[k].shape[-2:] == (3, 3):
+            sd[k] = sd[k].reshape(3, 3)                      # a legacy checkpoint
+    conv = {}
+    for k, v in sd.items():                                  # what convert_state.py does
+        k = k[len("module."):] if k.startswith("module.") else k
+        if k.split(".")[-1] in ("rgb_to_xyz", "fxfyfz_to_lab", "xyz_to_rgb", "lab_to_fxfyfz") and v.dim() == 2:
+            v = v.reshape(1, 1, 3, 3)
+        conv[k] = v
+    assert layer.load_state_dict(conv, strict=True).missing_keys == []
+
+
+@pytest.mark.skipif(not ref_loader.available(), reason="reference tree not present on this box")
+def test_load_reference_state_dict_directly():
+    _, _, RefLayer = ref_loader.load()
+    layer = curl_b200.CURLLayer()
+    res = layer.load_state_dict(RefLayer().state_dict(), strict=True)
+    assert not res.missing_keys and not res.unexpected_keys
+
+
+def test_constructor_validation():
+    with pytest.raises(ValueError):
+        curl_b200.CURLLayer(47, 48, 64)
+    with pytest.raises(ValueError):
+        curl_b200.CURLLayer(48, 48, 8)
+
+
+def test_no_cpu_fallback():
+    layer = curl_b200.CURLLayer()
+    img = torch.rand(1, 3, 4, 4)
+    z = lambda n: torch.zeros(1, n)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        layer(img, None, z(48), z(48), z(64))
+    for M in (colors.RGB2LAB, colors.LAB2RGB, colors.RGB2HSV, colors.HSV2RGB):
+        with pytest.raises(RuntimeError, match="CUDA"):
+            M()(img)
+    for fn, n in ((curves.adjust_lab, 48), (curves.adjust_rgb, 48), (curves.adjust_hsv, 64)):
+        with pytest.raises(RuntimeError, match="CUDA"):
+            fn(img, z(n))
+    with pytest.raises(RuntimeError, match="CUDA"):
+        curves.apply_curve(img, torch.ones(1, 16), None, 0, 0)
+
+
+def test_changed_constants_are_rejected():
+    m = colors.RGB2LAB()
+    with torch.no_grad():
+        m.rgb_to_xyz[0, 0, 0, 0] += 0.01
+    with pytest.raises(RuntimeError, match="frozen colour constant"):
+        m(torch.rand(1, 3, 4, 4))
+
+
+def test_product_code_does_not_import_the_oracle():
+    import os
+    from conftest import ROOT
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "curl_b200")):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert "import oracle" not in src and "from oracle" not in src, f
+                assert "import hostsim" not in src and "pixel_sim" not in src, f
