@@ -350,8 +350,7 @@ CURL_HD void hsv2rgb_bwd(const Hsv2RgbJac<T>& j, const T grgb[3], T ghsv[3]) {
 // ------------------------------------------------------------------------------------------------
 template <class T>
 struct CurveJac {
-  T xin;   // (clamped) input
-  T a;     // pass_out * xin
+  T a;     // pass_out * xin   (xin = the clamped input; pass_out is 0/1, so a * a == pass_out * xin^2)
   T d;     // pass_out * pass_in * (alpha + 2 beta xin)
 };
 
@@ -363,7 +362,6 @@ CURL_HD T self_curve_fwd(T x, float alpha, float beta, CurveJac<T>* jac) {
   const T y = vmul(xin, s);
   const T o = vsat(y);
   const T po = vgate_eq(o, y);
-  jac->xin = xin;
   jac->a = vmul(po, xin);
   T d = vmul(po, vfma(T(beta), xin, s));
   if (PRECLAMP) d = vmul(d, vgate_eq(xin, x));
@@ -375,7 +373,7 @@ template <class T>
 CURL_HD T self_curve_bwd(const CurveJac<T>& j, T go, T mom[2]) {
   const T gs = vmul(go, j.a);
   mom[0] = vadd(mom[0], gs);
-  mom[1] = vfma(gs, j.xin, mom[1]);
+  mom[1] = vfma(gs, j.a, mom[1]);     // gs * xin: gs already carries pass_out, so gs * a == gs * xin
   return vmul(go, j.d);
 }
 
@@ -522,7 +520,7 @@ CURL_HD void layer_fwd(const T x[3], T m, const float* ab, T out[3]) {
 struct KeepInRegisters {
   static constexpr bool kActive = false;
 };
-constexpr int SPILL_SLOTS = 30;   // LabJac 6 + Self3Jac 9 + RgbJac 6 + Self3Jac 9
+constexpr int SPILL_SLOTS = 24;   // LabJac 6 + Self3Jac 6 + RgbJac 6 + Self3Jac 6
 
 template <class T, class S> CURL_HD void spill_save(const S& sp, int o, const LabJac<T>& j) {
 #pragma unroll
@@ -542,11 +540,11 @@ template <class T, class S> CURL_HD void spill_load(const S& sp, int o, RgbJac<T
 }
 template <class T, class S> CURL_HD void spill_save(const S& sp, int o, const Self3Jac<T>& j) {
 #pragma unroll
-  for (int c = 0; c < 3; ++c) { sp.put(o + 3 * c, j.c[c].xin); sp.put(o + 3 * c + 1, j.c[c].a); sp.put(o + 3 * c + 2, j.c[c].d); }
+  for (int c = 0; c < 3; ++c) { sp.put(o + 2 * c, j.c[c].a); sp.put(o + 2 * c + 1, j.c[c].d); }
 }
 template <class T, class S> CURL_HD void spill_load(const S& sp, int o, Self3Jac<T>& j) {
 #pragma unroll
-  for (int c = 0; c < 3; ++c) { j.c[c].xin = sp.get(o + 3 * c); j.c[c].a = sp.get(o + 3 * c + 1); j.c[c].d = sp.get(o + 3 * c + 2); }
+  for (int c = 0; c < 3; ++c) { j.c[c].a = sp.get(o + 2 * c); j.c[c].d = sp.get(o + 2 * c + 1); }
 }
 
 // Recompute-forward + reverse.  mom: 20 accumulators (S0,S1 per curve), accumulated in place.
@@ -562,9 +560,9 @@ CURL_HD void layer_bwd(const T x[3], T m, const float* ab, const T gout[3], T gx
   if constexpr (kSpill) spill_save<T>(sp, 6, j2);
   if (MK == MASK_F32) vscale3(lab2, m);
   lab2rgb_fwd<T, true>(lab2, rgb, &j3);
-  if constexpr (kSpill) spill_save<T>(sp, 15, j3);
+  if constexpr (kSpill) spill_save<T>(sp, 12, j3);
   adjust_self3_fwd<T, true>(rgb, ab + 6, rgb2, &j4);
-  if constexpr (kSpill) spill_save<T>(sp, 21, j4);
+  if constexpr (kSpill) spill_save<T>(sp, 18, j4);
   if (MK == MASK_F32) vscale3(rgb2, m);
   rgb2hsv_fwd<T, true, MK != MASK_F32>(rgb2, hsv, &j5);
   adjust_hsv_fwd<T, true, true>(hsv, ab + 12, hsv2, &j6);
@@ -587,9 +585,9 @@ CURL_HD void layer_bwd(const T x[3], T m, const float* ab, const T gout[3], T gx
   adjust_hsv_bwd(j6, ab + 12, a, b, mom + 12);
   rgb2hsv_bwd(j5, b, a);
   if (MK == MASK_F32) vscale3(a, m);
-  if constexpr (kSpill) spill_load<T>(sp, 21, j4);
+  if constexpr (kSpill) spill_load<T>(sp, 18, j4);
   adjust_self3_bwd(j4, a, b, mom + 6);
-  if constexpr (kSpill) spill_load<T>(sp, 15, j3);
+  if constexpr (kSpill) spill_load<T>(sp, 12, j3);
   lab2rgb_bwd(j3, b, a);
   if (MK == MASK_F32) vscale3(a, m);
   if constexpr (kSpill) spill_load<T>(sp, 6, j2);
