@@ -185,6 +185,7 @@ def run_ours(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=dev)
     _lib.load()
 
@@ -247,31 +248,48 @@ def run_ours(args):
     value = world * n_px / 1e6 / (ms_step / 1e3)
 
     # ---- e2e: pinned host buffers -> H2D -> fwd+bwd -> D2H of the step's results -------------------
+    # The public module API is driven from HOST data the way the reference's training loop does
+    # (main.py:279-283: batch.to(device, non_blocking=True) then net(...)): the batch is fed in
+    # chunks of images, chunk i+1's copy (copy stream) overlapping chunk i's kernels (compute stream).
     for t in (img, L, R, Hk):
         t.grad = None
     h_img = torch.empty(img.shape, dtype=torch.float32, pin_memory=True)
     h_mask = torch.empty(mask.shape, dtype=torch.bool, pin_memory=True)
     h_img.copy_(img.detach()); h_mask.copy_(mask)
-    h_res = torch.empty(B * (1 + 160), dtype=torch.float32, pin_memory=True)
+    h_res = torch.empty(B, 1 + 160, dtype=torch.float32, pin_memory=True)
     d_img = img.detach()          # reuse the resident buffers as the H2D destination
     d_mask = mask
+    Ld, Rd, Hd = L.detach(), R.detach(), Hk.detach()
     e2e_steps = max(1, min(args.steps, 5))
+    chunk = max(1, min(B, args.e2e_chunk))
+    spans = [(lo, min(B, lo + chunk)) for lo in range(0, B, chunk)]
+    copy_stream = torch.cuda.Stream(device=dev)
+    main_stream = torch.cuda.current_stream(dev)
+    d_res = torch.empty(B, 1 + 160, dtype=torch.float32, device=dev)
 
     def e2e_step():
-        d_img.copy_(h_img, non_blocking=True)
-        d_mask.copy_(h_mask, non_blocking=True)
-        x = d_img.requires_grad_(True)
-        for t in (L, R, Hk):
-            t.grad = None
-        o, r = layer(x, d_mask, L, R, Hk)
-        torch.autograd.backward([o, r], [gout, greg])
-        res = torch.cat([r.detach().reshape(-1), L.grad.reshape(-1), R.grad.reshape(-1), Hk.grad.reshape(-1)])
-        h_res.copy_(res, non_blocking=True)
-        x.grad = None
-        d_img.requires_grad_(False)
+        ready = []
+        copy_stream.wait_stream(main_stream)          # previous step's kernels are done with the buffers
+        with torch.cuda.stream(copy_stream):
+            for lo, hi in spans:
+                d_img[lo:hi].copy_(h_img[lo:hi], non_blocking=True)
+                d_mask[lo:hi].copy_(h_mask[lo:hi], non_blocking=True)
+                ev_c = torch.cuda.Event()
+                ev_c.record(copy_stream)
+                ready.append(ev_c)
+        for (lo, hi), ev_c in zip(spans, ready):
+            main_stream.wait_event(ev_c)
+            x = d_img[lo:hi].requires_grad_(True)
+            l, r, h = (t[lo:hi].clone().requires_grad_(True) for t in (Ld, Rd, Hd))
+            o, rg = layer(x, d_mask[lo:hi], l, r, h)
+            torch.autograd.backward([o, rg], [gout[lo:hi], greg[lo:hi]])
+            d_res[lo:hi, 0] = rg.detach()
+            d_res[lo:hi, 1:49] = l.grad; d_res[lo:hi, 49:97] = r.grad; d_res[lo:hi, 97:161] = h.grad
+        h_res.copy_(d_res, non_blocking=True)
 
     e2e_step()
     barrier()
+    launches_e0 = _lib.launches
     s2 = torch.cuda.Event(enable_timing=True); e2 = torch.cuda.Event(enable_timing=True)
     s2.record()
     for _ in range(e2e_steps):
@@ -288,6 +306,11 @@ def run_ours(args):
 
     if rank == 0:
         peak, peak_src = measured_peak()
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tpath):       # DRAM bytes per pixel measured by ncu (committed), scaled to this launch
+            with open(tpath) as f:
+                traffic = json.load(f)["bwd_bytes_per_px"] * n_px / 1e9
         bwd_gbs = n_px * BWD_BYTES_PER_PX / (bwd_ms / 1e3) / 1e9
         fwd_gbs = n_px * FWD_BYTES_PER_PX / (fwd_ms / 1e3) / 1e9
         step_gbs = n_px * (FWD_BYTES_PER_PX + BWD_BYTES_PER_PX) / ((fwd_ms + bwd_ms) / 1e3) / 1e9
@@ -302,12 +325,15 @@ def run_ours(args):
                        "l2": "inputs exceed L2 (%.1f GB per tensor), no flush needed" % (n_px * 12 / 1e9),
                        "parallelism": "batch-sharded, no collective" if world > 1 else "single GPU"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": e2e_ms, "steps": e2e_steps},
+                    "ms_per_step": e2e_ms, "steps": e2e_steps, "chunk_images": chunk,
+                    "what": "pinned host img+mask -> H2D (copy stream, chunked) -> CURLLayer fwd+bwd -> D2H reg + knot grads"},
             "gpu_launches": launches,
             "clocks": clocks,
-            "roofline": {"bound": "hbm", "kernel": "bwd_kernel<OpLayer> (fused recompute backward, 37 B/px)",
+            "roofline": {"bound": "hbm", "kernel": "bwd_tma_kernel<OpLayer> (fused recompute backward, 37 B/px)",
                          "achieved": bwd_gbs, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
-                         "frac": bwd_gbs / peak, "frac_of_8TBps": bwd_gbs / 8000.0, "traffic": None,
+                         "frac": bwd_gbs / peak, "frac_of_8TBps": bwd_gbs / 8000.0, "traffic": traffic,
+                         "traffic_unit": "GB per launch (ncu dram read+write, profiles/traffic.json)",
+                         "algorithmic_gb_per_launch": n_px * BWD_BYTES_PER_PX / 1e9,
                          "ms_per_launch": bwd_ms},
             "roofline_fwd": {"kernel": "fwd_kernel<OpLayer> (fused forward, 25 B/px)", "achieved": fwd_gbs,
                              "frac": fwd_gbs / peak, "ms_per_launch": fwd_ms},
@@ -333,6 +359,7 @@ def main():
     ap.add_argument("--height", type=int, default=H4K)
     ap.add_argument("--width", type=int, default=W4K)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--e2e-chunk", type=int, default=8, help="images per host->device chunk in the e2e leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
