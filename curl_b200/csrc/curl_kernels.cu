@@ -16,7 +16,10 @@ namespace curl {
 
 constexpr int THREADS = 256;
 #ifndef BWD_THREADS
-#define BWD_THREADS 256
+#define BWD_THREADS 384
+#endif
+#ifndef BWD_SPILL
+#define BWD_SPILL 24
 #endif
 #ifndef BWD_MIN_BLOCKS
 #define BWD_MIN_BLOCKS 1
@@ -57,9 +60,9 @@ struct OpLayer {
   static __device__ __forceinline__ void fwd(const T x[3], T m, const float* ab, int, T y[3]) {
     layer_fwd<T, MK>(x, m, ab, y);
   }
-  // Measured on B200: parking the first four Jac records in shared memory (SPILL_SLOTS) does not lower
-  // ptxas' register allocation for this kernel and costs 30 extra LDS/STS per pixel, so it is off.
-  static constexpr int SPILL = 0;
+  // The Jac records of the first four stages (24 packed values) are parked in shared memory during
+  // the turn of the reverse sweep: 192 -> 148 registers, which lets 12 warps share an SM.
+  static constexpr int SPILL = BWD_SPILL;
   template <int MK, bool WANT_GX, class T, class SP>
   static __device__ __forceinline__ void bwd(const T x[3], T m, const float* ab, int, const T gy[3], T gx[3], T* mom,
                                              const SP& sp) {
@@ -406,7 +409,7 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned by
 
 constexpr int TMA_TILE = BWD_THREADS * 2;   // pixels per tile: one packed pair per thread
 #ifndef TMA_STAGES_N
-#define TMA_STAGES_N 6
+#define TMA_STAGES_N 4
 #endif
 constexpr int TMA_STAGES = TMA_STAGES_N;
 constexpr int TMA_PLANES = 6;           // x0 x1 x2 g0 g1 g2
@@ -419,9 +422,15 @@ template <class Op> constexpr size_t tma_smem_bytes() {
 // 8-byte column per thread, so a warp's STS.64/LDS.64 touches 256 consecutive bytes.
 struct SmemSpill {
   static constexpr bool kActive = true;
-  F2* base;   // already offset by threadIdx.x
-  __device__ __forceinline__ void put(int slot, F2 v) const { base[slot * BWD_THREADS] = v; }
-  __device__ __forceinline__ F2 get(int slot) const { return base[slot * BWD_THREADS]; }
+  unsigned base;   // shared-space byte address, already offset by threadIdx.x
+  // asm volatile: the compiler must not forward the stored value to the later load (that would keep
+  // the value live in a register, which is exactly what parking is meant to avoid)
+  __device__ __forceinline__ void put(int slot, F2 v) const {
+    asm volatile("st.shared.b64 [%0], %1;" ::"r"(base + slot * (BWD_THREADS * 8)), "l"(v.u) : "memory");
+  }
+  __device__ __forceinline__ F2 get(int slot) const {
+    F2 r; asm volatile("ld.shared.b64 %0, [%1];" : "=l"(r.u) : "r"(base + slot * (BWD_THREADS * 8)) : "memory"); return r;
+  }
 };
 
 // Backward, aligned path (HW % 4 == 0, 16-byte aligned bases).  Same math as bwd_kernel<.., 2, ..>.
@@ -464,6 +473,11 @@ __global__ void __launch_bounds__(BWD_THREADS, BWD_MIN_BLOCKS) bwd_tma_kernel(co
     for (int s = 0; s < TMA_STAGES; ++s) mbar_init(&s_full[s], 1);
     mbar_fence_init();
   }
+  // The last tile of an image may be partial; its tail pairs read whatever the stage holds.  Zero the
+  // ring once so that this is always finite pixel data (their gradients are gated off below).
+  for (int i = threadIdx.x; i < (int)(TMA_RING_BYTES / sizeof(float4)); i += BWD_THREADS)
+    reinterpret_cast<float4*>(s_ring)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   __syncthreads();
   if (threadIdx.x == 0)
     for (int it = 0; it < TMA_STAGES && it < n_my; ++it) issue(it);
@@ -511,15 +525,16 @@ __global__ void __launch_bounds__(BWD_THREADS, BWD_MIN_BLOCKS) bwd_tma_kernel(co
     for (int c = 0; c < 3; ++c) {
       const float2 a = *reinterpret_cast<const float2*>(src + c * TMA_TILE);
       const float2 g = *reinterpret_cast<const float2*>(src + (3 + c) * TMA_TILE);
-      x[c] = valid ? F2(a.x, a.y) : F2(0.5f);
-      gy[c] = valid ? F2(g.x, g.y) : F2(0.0f);
+      x[c] = F2(a.x, a.y);
+      // a tail pair's gradient is switched off through m (= 0) where a mask multiplies it anyway
+      gy[c] = (MK == MASK_NONE && !valid) ? F2(0.0f) : F2(g.x, g.y);
     }
     __syncthreads();                                    // every thread has read stage s
     if (threadIdx.x == 0 && it + TMA_STAGES < n_my) issue(it + TMA_STAGES);
     if (!valid) m = T(0.0f);
     T gx[3];
     if constexpr (Op::SPILL > 0) {
-      const SmemSpill sp{reinterpret_cast<F2*>(reinterpret_cast<unsigned char*>(s_ring) + TMA_RING_BYTES) + threadIdx.x};
+      const SmemSpill sp{smem_u32(reinterpret_cast<unsigned char*>(s_ring) + TMA_RING_BYTES) + threadIdx.x * 8u};
       Op::template bwd<MK, WANT_GIN, T>(x, m, s_ab, p.aux, gy, gx, mom, sp);
     } else {
       Op::template bwd<MK, WANT_GIN, T>(x, m, s_ab, p.aux, gy, gx, mom, KeepInRegisters());
@@ -559,9 +574,15 @@ static int blocks_per_image(int B, int HW, int vec, int blocks_per_sm) {
   return (int)n;
 }
 
-constexpr int BWD_GRID_BLOCKS_PER_SM = 8;
+#ifndef BWD_GRID_BPS
+#define BWD_GRID_BPS 8
+#endif
+constexpr int BWD_GRID_BLOCKS_PER_SM = BWD_GRID_BPS;
 constexpr int BWD_VEC = 2;   // pixels per thread per iteration on the aligned backward path
-constexpr int FWD_GRID_BLOCKS_PER_SM = 16;
+#ifndef FWD_GRID_BPS
+#define FWD_GRID_BPS 16
+#endif
+constexpr int FWD_GRID_BLOCKS_PER_SM = FWD_GRID_BPS;
 
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 static bool aligned4(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 3u) == 0; }
@@ -577,7 +598,21 @@ static int launch_fwd(const KParams& p, int B, bool vec4, cudaStream_t st) {
   return check_launch();
 }
 
-static int bwd_grid_x(int B, int HW, int vec) { return blocks_per_image(B, HW, vec, BWD_GRID_BLOCKS_PER_SM); }
+// Backward grid: one block is resident per SM, so the grid is sized to a whole number of waves
+// (B * grid.x a multiple of the SM count) whenever some wave count in [W, 2W] allows it; a partial
+// last wave costs up to one full wave of time.
+static int bwd_grid_x(int B, int HW, int vec) {
+  const int px_per_tile = (vec == 1 ? THREADS : BWD_THREADS * vec);
+  const long long tiles = ((long long)HW + px_per_tile - 1) / px_per_tile;
+  const int sms = sm_count();
+  for (int w = BWD_GRID_BLOCKS_PER_SM; w <= 2 * BWD_GRID_BLOCKS_PER_SM; ++w) {
+    const long long total = (long long)sms * w;
+    if (total % B == 0 && total / B <= tiles) return (int)(total / B);
+  }
+  long long cap = ((long long)sms * BWD_GRID_BLOCKS_PER_SM + B - 1) / B;
+  long long n = tiles < cap ? tiles : cap;
+  return (int)(n < 1 ? 1 : n);
+}
 
 template <class Op, int MK>
 static int launch_bwd(KParams& p, int B, bool vec4, void* ws, size_t ws_bytes, cudaStream_t st) {
@@ -713,6 +748,9 @@ int curl_layer_bwd_f32(const float* img, const void* mask, int mask_kind, const 
 }
 
 int curl_color_fwd_f32(int conversion, const float* in, float* out, int B, int H, int W, void* stream) {
+#ifdef CURL_DEV_LAYER_ONLY   /* quick experiment builds: only the layer kernels are instantiated */
+  return CURL_ERR_BAD_ARG;
+#else
   int rc = check_shape(B, H, W);
   if (rc != CURL_OK) return rc;
   if (!in || !out) return CURL_ERR_BAD_ARG;
@@ -728,10 +766,14 @@ int curl_color_fwd_f32(int conversion, const float* in, float* out, int B, int H
     case CURL_HSV2RGB: return launch_fwd<OpColor<CURL_HSV2RGB>, MASK_NONE>(p, B, v4, st);
     default: return CURL_ERR_BAD_ARG;
   }
+#endif
 }
 
 int curl_color_bwd_f32(int conversion, const float* in, const float* gout, float* gin, int B, int H, int W,
                        void* stream) {
+#ifdef CURL_DEV_LAYER_ONLY   /* quick experiment builds: only the layer kernels are instantiated */
+  return CURL_ERR_BAD_ARG;
+#else
   int rc = check_shape(B, H, W);
   if (rc != CURL_OK) return rc;
   if (!in || !gout || !gin) return CURL_ERR_BAD_ARG;
@@ -747,6 +789,7 @@ int curl_color_bwd_f32(int conversion, const float* in, const float* gout, float
     case CURL_HSV2RGB: return launch_bwd<OpColor<CURL_HSV2RGB>, MASK_NONE>(p, B, v4, nullptr, 0, st);
     default: return CURL_ERR_BAD_ARG;
   }
+#endif
 }
 
 static int adjust_params(KParams& p, int group, const float* in, const float* P, int64_t ldP, int B, int H, int W,
@@ -767,6 +810,9 @@ static int adjust_params(KParams& p, int group, const float* in, const float* P,
 
 int curl_adjust_fwd_f32(int group, const float* in, const float* P, int64_t ldP, float* out, float* reg, int B,
                         int H, int W, int K, void* stream) {
+#ifdef CURL_DEV_LAYER_ONLY   /* quick experiment builds: only the layer kernels are instantiated */
+  return CURL_ERR_BAD_ARG;
+#else
   KParams p;
   int rc = adjust_params(p, group, in, P, ldP, B, H, W, K);
   if (rc != CURL_OK) return rc;
@@ -777,11 +823,15 @@ int curl_adjust_fwd_f32(int group, const float* in, const float* P, int64_t ldP,
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (group == CURL_ADJUST_HSV) return launch_fwd<OpAdjustHsv, MASK_NONE>(p, B, v4, st);
   return launch_fwd<OpAdjustSelf3, MASK_NONE>(p, B, v4, st);
+#endif
 }
 
 int curl_adjust_bwd_f32(int group, const float* in, const float* P, int64_t ldP, const float* gout,
                         const float* greg, float* gin, float* gP, void* workspace, size_t workspace_bytes, int B,
                         int H, int W, int K, void* stream) {
+#ifdef CURL_DEV_LAYER_ONLY   /* quick experiment builds: only the layer kernels are instantiated */
+  return CURL_ERR_BAD_ARG;
+#else
   KParams p;
   int rc = adjust_params(p, group, in, P, ldP, B, H, W, K);
   if (rc != CURL_OK) return rc;
@@ -792,10 +842,14 @@ int curl_adjust_bwd_f32(int group, const float* in, const float* P, int64_t ldP,
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (group == CURL_ADJUST_HSV) return launch_bwd<OpAdjustHsv, MASK_NONE>(p, B, v4, workspace, workspace_bytes, st);
   return launch_bwd<OpAdjustSelf3, MASK_NONE>(p, B, v4, workspace, workspace_bytes, st);
+#endif
 }
 
 int curl_apply_curve_fwd_f32(const float* in, const float* C, int64_t ldC, int channel_in, int channel_out,
                              float* out, float* reg, int B, int H, int W, int K, void* stream) {
+#ifdef CURL_DEV_LAYER_ONLY   /* quick experiment builds: only the layer kernels are instantiated */
+  return CURL_ERR_BAD_ARG;
+#else
   int rc = check_shape(B, H, W);
   if (rc != CURL_OK) return rc;
   if (!in || !C || !out || !reg || K < 3 || ldC < K) return CURL_ERR_BAD_ARG;
@@ -807,11 +861,15 @@ int curl_apply_curve_fwd_f32(const float* in, const float* C, int64_t ldC, int c
   p.aux = channel_in | (channel_out << 2);
   p.seg[0] = KnotSeg{C, nullptr, (long long)ldC, 1, K};
   return launch_fwd<OpCurve1, MASK_NONE>(p, B, can_vec4(p, CURL_MASK_NONE), reinterpret_cast<cudaStream_t>(stream));
+#endif
 }
 
 int curl_apply_curve_bwd_f32(const float* in, const float* C, int64_t ldC, int channel_in, int channel_out,
                              const float* gout, const float* greg, float* gin, float* gC, void* workspace,
                              size_t workspace_bytes, int B, int H, int W, int K, void* stream) {
+#ifdef CURL_DEV_LAYER_ONLY   /* quick experiment builds: only the layer kernels are instantiated */
+  return CURL_ERR_BAD_ARG;
+#else
   int rc = check_shape(B, H, W);
   if (rc != CURL_OK) return rc;
   if (!in || !C || !gout || !gC || K < 3 || ldC < K) return CURL_ERR_BAD_ARG;
@@ -824,6 +882,7 @@ int curl_apply_curve_bwd_f32(const float* in, const float* C, int64_t ldC, int c
   p.seg[0] = KnotSeg{C, gC, (long long)ldC, 1, K};
   return launch_bwd<OpCurve1, MASK_NONE>(p, B, can_vec4(p, CURL_MASK_NONE), workspace, workspace_bytes,
                                          reinterpret_cast<cudaStream_t>(stream));
+#endif
 }
 
 }  // extern "C"

@@ -59,6 +59,22 @@ constexpr float N00 = (float)(3.2404542 * WX), N10 = (float)(-1.5371385 * WY), N
 constexpr float N01 = (float)(-0.9692660 * WX), N11 = (float)(1.8760108 * WY), N21 = (float)(0.0415560 * WZ);
 constexpr float N02 = (float)(0.0556434 * WX), N12 = (float)(-0.2040259 * WY), N22 = (float)(1.0572252 * WZ);
 constexpr float HSV_LO = 1e-9f;                          // colors.py:205,240
+// Reverse-sweep constants with the factors of the slimmed Jac records folded in (in double):
+//   LabJac.d_lin holds (d lin/d x)/SRGB_DK, LabJac.d_f holds 3 (d f/d t);
+//   RgbJac.d_finv holds (d finv/d f)/3, RgbJac.d_gam holds (d rgb/d v)/GAM_DK.
+constexpr double DK_D = 2.4 / 1.055, GDK_D = 1.055 / 2.4;
+constexpr float SRGB_INV_SLOPE_BY_DK = (float)((1.0 / 12.92) / DK_D);
+constexpr float F_SLOPE_X3 = (float)(1.0 / (EPS * EPS));
+constexpr float FINV_SLOPE_BY3 = (float)(EPS * EPS);
+constexpr float LIN_SLOPE_BY_DK = (float)(12.92 / GDK_D);
+constexpr float LN_S3 = (float)(1.16 / 3.0), AN_S3 = (float)(500.0 / 220.0 / 3.0), BN_S3 = (float)(200.0 / 220.0 / 3.0);
+constexpr float MB00 = (float)(0.412453 / WX * DK_D), MB10 = (float)(0.357580 / WX * DK_D), MB20 = (float)(0.180423 / WX * DK_D);
+constexpr float MB01 = (float)(0.212671 / WY * DK_D), MB11 = (float)(0.715160 / WY * DK_D), MB21 = (float)(0.072169 / WY * DK_D);
+constexpr float MB02 = (float)(0.019334 / WZ * DK_D), MB12 = (float)(0.119193 / WZ * DK_D), MB22 = (float)(0.950227 / WZ * DK_D);
+constexpr float NB00 = (float)(3.2404542 * WX * GDK_D), NB10 = (float)(-1.5371385 * WY * GDK_D), NB20 = (float)(-0.4985314 * WZ * GDK_D);
+constexpr float NB01 = (float)(-0.9692660 * WX * GDK_D), NB11 = (float)(1.8760108 * WY * GDK_D), NB21 = (float)(0.0415560 * WZ * GDK_D);
+constexpr float NB02 = (float)(0.0556434 * WX * GDK_D), NB12 = (float)(-0.2040259 * WY * GDK_D), NB22 = (float)(1.0572252 * WZ * GDK_D);
+constexpr float FY_S3 = (float)(300.0 / 116.0), FX_S3 = (float)(660.0 / 500.0), FZ_S3 = (float)(-660.0 / 200.0);
 }  // namespace k
 
 enum MaskKind { MASK_NONE = 0, MASK_U8 = 1, MASK_F32 = 2 };
@@ -114,8 +130,8 @@ CURL_HD float curve_knot_grad(const float* C, int K, int i, double S0, double S1
 // ------------------------------------------------------------------------------------------------
 template <class T>
 struct LabJac {
-  T d_lin[3];  // d lin_c / d x_c
-  T d_f[3];    // d f_k / d t_k
+  T d_lin[3];  // (d lin_c / d x_c) / SRGB_DK   -- the constant factors are folded into rgb2lab_bwd
+  T d_f[3];    // 3 (d f_k / d t_k)
 };
 
 template <class T, bool JAC>
@@ -128,7 +144,7 @@ CURL_HD void rgb2lab_fwd(const T x[3], T lab[3], LabJac<T>* jac) {
     const T u14 = vmul(u, vex2(vmul(vlg2(u), T(0.4f))));
     const T hi = vmul(u, u14);
     lin[c] = vsel_le(x[c], T(k::SRGB_T), vmul(x[c], T(k::SRGB_INV_SLOPE)), hi);
-    if (JAC) jac->d_lin[c] = vsel_le(x[c], T(k::SRGB_T), T(k::SRGB_INV_SLOPE), vmul(u14, T(k::SRGB_DK)));
+    if (JAC) jac->d_lin[c] = vsel_le(x[c], T(k::SRGB_T), T(k::SRGB_INV_SLOPE_BY_DK), u14);   // (d lin / d x) / SRGB_DK
   }
   T t[3];
   t[0] = vfma(lin[2], T(k::M20), vfma(lin[1], T(k::M10), vmul(lin[0], T(k::M00))));  // colors.py:40-41
@@ -141,7 +157,7 @@ CURL_HD void rgb2lab_fwd(const T x[3], T lab[3], LabJac<T>* jac) {
     const T e = vex2(vmul(vlg2(t[c]), T((float)(-2.0 / 3.0))));   // t^(-2/3)
     const T cr = vmul(t[c], e);
     f[c] = vsel_le(t[c], T(k::F_T), vfma(t[c], T(k::F_SLOPE), T(k::F_OFF)), cr);
-    if (JAC) jac->d_f[c] = vsel_le(t[c], T(k::F_T), T(k::F_SLOPE), vmul(e, T((float)(1.0 / 3.0))));
+    if (JAC) jac->d_f[c] = vsel_le(t[c], T(k::F_T), T(k::F_SLOPE_X3), e);                      // 3 (d f / d t)
   }
   lab[0] = vfma(f[1], T(k::LN_S), T(k::LN_O));               // colors.py:50,57
   lab[1] = vfma(vsub(f[0], f[1]), T(k::AN_S), T(0.5f));      // colors.py:50,58
@@ -150,14 +166,15 @@ CURL_HD void rgb2lab_fwd(const T x[3], T lab[3], LabJac<T>* jac) {
 
 template <class T>
 CURL_HD void rgb2lab_bwd(const LabJac<T>& jac, const T glab[3], T gx[3]) {
-  const T ga = vmul(glab[1], T(k::AN_S)), gb = vmul(glab[2], T(k::BN_S));
+  // constants carry the 1/3 of d_f and the SRGB_DK of d_lin; the sign of d f_z is in the MB?2 column
+  const T ga = vmul(glab[1], T(k::AN_S3)), gb = vmul(glab[2], T(k::BN_S3));
   T gt[3];
   gt[0] = vmul(ga, jac.d_f[0]);
-  gt[1] = vmul(vsub(vfma(glab[0], T(k::LN_S), gb), ga), jac.d_f[1]);
-  gt[2] = vneg(vmul(gb, jac.d_f[2]));
-  gx[0] = vmul(vfma(gt[2], T(k::M02), vfma(gt[1], T(k::M01), vmul(gt[0], T(k::M00)))), jac.d_lin[0]);
-  gx[1] = vmul(vfma(gt[2], T(k::M12), vfma(gt[1], T(k::M11), vmul(gt[0], T(k::M10)))), jac.d_lin[1]);
-  gx[2] = vmul(vfma(gt[2], T(k::M22), vfma(gt[1], T(k::M21), vmul(gt[0], T(k::M20)))), jac.d_lin[2]);
+  gt[1] = vmul(vsub(vfma(glab[0], T(k::LN_S3), gb), ga), jac.d_f[1]);
+  gt[2] = vmul(gb, jac.d_f[2]);
+  gx[0] = vmul(vfma(gt[2], T(-k::MB02), vfma(gt[1], T(k::MB01), vmul(gt[0], T(k::MB00)))), jac.d_lin[0]);
+  gx[1] = vmul(vfma(gt[2], T(-k::MB12), vfma(gt[1], T(k::MB11), vmul(gt[0], T(k::MB10)))), jac.d_lin[1]);
+  gx[2] = vmul(vfma(gt[2], T(-k::MB22), vfma(gt[1], T(k::MB21), vmul(gt[0], T(k::MB20)))), jac.d_lin[2]);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -165,8 +182,8 @@ CURL_HD void rgb2lab_bwd(const LabJac<T>& jac, const T glab[3], T gx[3]) {
 // ------------------------------------------------------------------------------------------------
 template <class T>
 struct RgbJac {
-  T d_finv[3];  // d finv_k / d f_k
-  T d_gam[3];   // d rgb_c / d v_c
+  T d_finv[3];  // (d finv_k / d f_k) / 3          -- the constant factors are folded into lab2rgb_bwd
+  T d_gam[3];   // (d rgb_c / d v_c) / GAM_DK
 };
 
 template <class T, bool JAC>
@@ -181,7 +198,7 @@ CURL_HD void lab2rgb_fwd(const T lab[3], T rgb[3], RgbJac<T>* jac) {
     // colors.py:110-111.  In the cube branch f > eps > 1e-4 so the clamp is inert.
     const T sq = vmul(f[c], f[c]);
     xyz[c] = vsel_le(f[c], T(k::FINV_T), vfma(f[c], T(k::FINV_SLOPE), T(k::FINV_OFF)), vmul(sq, f[c]));
-    if (JAC) jac->d_finv[c] = vsel_le(f[c], T(k::FINV_T), T(k::FINV_SLOPE), vmul(sq, T(3.0f)));
+    if (JAC) jac->d_finv[c] = vsel_le(f[c], T(k::FINV_T), T(k::FINV_SLOPE_BY3), sq);             // (d finv / d f) / 3
   }
   T v[3];
   v[0] = vfma(xyz[2], T(k::N20), vfma(xyz[1], T(k::N10), vmul(xyz[0], T(k::N00))));  // colors.py:114,117
@@ -193,19 +210,19 @@ CURL_HD void lab2rgb_fwd(const T lab[3], T rgb[3], RgbJac<T>* jac) {
     const T e = vex2(vmul(vlg2(v[c]), T(k::GAM_E)));               // v^(1/2.4 - 1)
     const T hi = vfma(vmul(v[c], e), T(1.055f), T(-0.055f));
     rgb[c] = vsel_le(v[c], T(k::LIN_T), vmul(v[c], T(k::LIN_SLOPE)), hi);
-    if (JAC) jac->d_gam[c] = vsel_le(v[c], T(k::LIN_T), T(k::LIN_SLOPE), vmul(e, T(k::GAM_DK)));
+    if (JAC) jac->d_gam[c] = vsel_le(v[c], T(k::LIN_T), T(k::LIN_SLOPE_BY_DK), e);               // (d rgb / d v) / GAM_DK
   }
 }
 
 template <class T>
 CURL_HD void lab2rgb_bwd(const RgbJac<T>& jac, const T grgb[3], T glab[3]) {
   const T gv0 = vmul(grgb[0], jac.d_gam[0]), gv1 = vmul(grgb[1], jac.d_gam[1]), gv2 = vmul(grgb[2], jac.d_gam[2]);
-  const T gf0 = vmul(vfma(gv2, T(k::N02), vfma(gv1, T(k::N01), vmul(gv0, T(k::N00)))), jac.d_finv[0]);
-  const T gf1 = vmul(vfma(gv2, T(k::N12), vfma(gv1, T(k::N11), vmul(gv0, T(k::N10)))), jac.d_finv[1]);
-  const T gf2 = vmul(vfma(gv2, T(k::N22), vfma(gv1, T(k::N21), vmul(gv0, T(k::N20)))), jac.d_finv[2]);
-  glab[0] = vmul(vadd(vadd(gf0, gf1), gf2), T(k::FY_S));
-  glab[1] = vmul(gf0, T(k::FX_S));
-  glab[2] = vmul(gf2, T(k::FZ_S));
+  const T gf0 = vmul(vfma(gv2, T(k::NB02), vfma(gv1, T(k::NB01), vmul(gv0, T(k::NB00)))), jac.d_finv[0]);
+  const T gf1 = vmul(vfma(gv2, T(k::NB12), vfma(gv1, T(k::NB11), vmul(gv0, T(k::NB10)))), jac.d_finv[1]);
+  const T gf2 = vmul(vfma(gv2, T(k::NB22), vfma(gv1, T(k::NB21), vmul(gv0, T(k::NB20)))), jac.d_finv[2]);
+  glab[0] = vmul(vadd(vadd(gf0, gf1), gf2), T(k::FY_S3));
+  glab[1] = vmul(gf0, T(k::FX_S3));
+  glab[2] = vmul(gf2, T(k::FZ_S3));
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -103,11 +103,17 @@ struct F2 {
   CURL_D float lo() const { float a, b; asm("mov.b64 {%0,%1}, %2;" : "=f"(a), "=f"(b) : "l"(u)); return a; }
   CURL_D float hi() const { float a, b; asm("mov.b64 {%0,%1}, %2;" : "=f"(a), "=f"(b) : "l"(u)); return b; }
 };
+#ifdef ABL_SCALAR
+CURL_D F2 vadd(F2 a, F2 b) { return F2(a.lo() + b.lo(), a.hi() + b.hi()); }
+CURL_D F2 vmul(F2 a, F2 b) { return F2(a.lo() * b.lo(), a.hi() * b.hi()); }
+CURL_D F2 vfma(F2 a, F2 b, F2 c) { return F2(fmaf(a.lo(), b.lo(), c.lo()), fmaf(a.hi(), b.hi(), c.hi())); }
+#else
 CURL_D F2 vadd(F2 a, F2 b) { F2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r.u) : "l"(a.u), "l"(b.u)); return r; }
 CURL_D F2 vmul(F2 a, F2 b) { F2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r.u) : "l"(a.u), "l"(b.u)); return r; }
 CURL_D F2 vfma(F2 a, F2 b, F2 c) {
   F2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r.u) : "l"(a.u), "l"(b.u), "l"(c.u)); return r;
 }
+#endif
 CURL_D F2 vsub(F2 a, F2 b) { return vfma(b, F2(-1.0f), a); }
 CURL_D F2 vneg(F2 a) { return vmul(a, F2(-1.0f)); }
 
@@ -120,10 +126,28 @@ CURL_D F2 vneg(F2 a) { return vmul(a, F2(-1.0f)); }
 #define CURL_F2_MAP4(name)                                            \
   CURL_D F2 name(F2 a, F2 b, F2 c, F2 d) {                            \
     return F2(name(a.lo(), b.lo(), c.lo(), d.lo()), name(a.hi(), b.hi(), c.hi(), d.hi())); }
-CURL_F2_MAP1(vlg2) CURL_F2_MAP1(vex2) CURL_F2_MAP1(vrcp) CURL_F2_MAP1(vsat)
+#ifdef ABL_NOMUFU
+CURL_D F2 vlg2(F2 a) { return a; }
+CURL_D F2 vex2(F2 a) { return a; }
+CURL_D F2 vrcp(F2 a) { return a; }
+#else
+CURL_F2_MAP1(vlg2) CURL_F2_MAP1(vex2) CURL_F2_MAP1(vrcp)
+#endif
+#ifdef ABL_NOSAT
+CURL_D F2 vsat(F2 a) { return a; }
+#else
+CURL_F2_MAP1(vsat)
+#endif
 CURL_F2_MAP2(vmul_sat) CURL_F2_MAP2(vadd_sat) CURL_F2_MAP3(vfma_sat)
 CURL_F2_MAP2(vmax) CURL_F2_MAP2(vmin)
+#ifdef ABL_NOGATE
+CURL_D F2 vgate_le(F2 a, F2 b) { return F2(1.0f); }
+CURL_D F2 vgate_lt(F2 a, F2 b) { return F2(1.0f); }
+CURL_D F2 vgate_eq(F2 a, F2 b) { return F2(1.0f); }
+CURL_D F2 vgate_ne(F2 a, F2 b) { return F2(1.0f); }
+#else
 CURL_F2_MAP2(vgate_le) CURL_F2_MAP2(vgate_lt) CURL_F2_MAP2(vgate_eq) CURL_F2_MAP2(vgate_ne)
+#endif
 CURL_F2_MAP4(vsel_le) CURL_F2_MAP4(vsel_lt) CURL_F2_MAP4(vsel_eq)
 CURL_D float vhsum(F2 a) { return a.lo() + a.hi(); }
 #endif  // __CUDACC__
