@@ -4,10 +4,11 @@ Mirrors the reference's module API for this path:
     curl_b200.colors  : RGB2LAB, LAB2RGB, RGB2HSV, HSV2RGB        (reference colors.py)
     curl_b200.curves  : apply_curve, adjust_lab, adjust_rgb, adjust_hsv   (reference curves.py)
     curl_b200.model   : CURLLayer                                 (reference model.py:121-176)
+                        GCURLNet (backbone -> knots -> layer)     (reference model.py:179-203)
 All of them run hand-written CUDA kernels through the C ABI in include/curl_b200.h; there is no
 CPU or PyTorch fallback.
 """
 from . import colors, curves, model  # noqa: F401
-from .model import CURLLayer  # noqa: F401
+from .model import CURLLayer, GCURLNet  # noqa: F401
 
-__all__ = ["colors", "curves", "model", "CURLLayer"]
+__all__ = ["colors", "curves", "model", "CURLLayer", "GCURLNet"]

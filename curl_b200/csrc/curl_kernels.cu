@@ -48,6 +48,8 @@ struct KParams {
   int HW;
   int linear_knots;    // 1: seg[].p holds C itself (apply_curve), 0: log-domain (C = exp(p))
   int aux;             // op-specific: apply_curve packs channel_in | channel_out << 2
+  const unsigned char* in8;   // 8-bit forward: image in, CHW or HWC
+  unsigned char* out8;        //                image out
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -231,8 +233,13 @@ __device__ __forceinline__ void stage_curves(const KParams& p, int b, float* s_C
 // ---------------------------------------------------------------------------------------------
 // Forward
 // ---------------------------------------------------------------------------------------------
+#ifdef FWD_MIN_BLOCKS
+#define FWD_BOUNDS __launch_bounds__(THREADS, FWD_MIN_BLOCKS)
+#else
+#define FWD_BOUNDS __launch_bounds__(THREADS)
+#endif
 template <class Op, int MK, int VEC>
-__global__ void __launch_bounds__(THREADS) fwd_kernel(const KParams p) {
+__global__ void FWD_BOUNDS fwd_kernel(const KParams p) {
   constexpr int NC = Op::NC;
   __shared__ float s_C[NC > 0 ? CURL_MAX_KNOTS : 1];
   __shared__ float s_ab[NC > 0 ? 2 * NC : 1];
@@ -265,6 +272,92 @@ __global__ void __launch_bounds__(THREADS) fwd_kernel(const KParams p) {
       o0.v[v] = y[0]; o1.v[v] = y[1]; o2.v[v] = y[2];
     }
     o0.st(out + i); o1.st(out + HW + i); o2.st(out + 2 * (size_t)HW + i);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Forward on 8-bit images (curl_layer_fwd_u8): u8 -> x/255 -> layer_fwd -> trunc(out*255) -> u8.
+// 3 B/px in, 3 B/px out (+ the mask).  VEC == 4: four consecutive pixels per thread (32-bit
+// accesses per plane, or three 32-bit words of an interleaved row); VEC == 1: any size/alignment.
+// ---------------------------------------------------------------------------------------------
+// byte k of w as the float 2^23 + byte (one PRMT; I2F would go through the MUFU pipe, which is the
+// forward kernel's bottleneck); the caller subtracts 2^23, which is exact.
+__device__ __forceinline__ float byte_of(unsigned w, int k) {
+  return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7650u + k));
+}
+constexpr float TWO23 = 8388608.0f;
+
+template <int MK, bool IN_HWC, bool OUT_HWC, int VEC>
+__global__ void __launch_bounds__(THREADS) fwd_u8_kernel(const KParams p) {
+  constexpr int NC = LAYER_CURVES;
+  __shared__ float s_C[CURL_MAX_KNOTS];
+  __shared__ float s_ab[2 * NC];
+  __shared__ double s_reg[NC];
+  const int b = blockIdx.y;
+  {
+    const bool owner = (blockIdx.x == 0) && (p.reg != nullptr);
+    stage_curves<NC>(p, b, s_C, s_ab, s_reg, owner);
+    if (owner && threadIdx.x == 0) {
+      double r = 0.0;
+      for (int j = 0; j < NC; ++j) r += s_reg[j];
+      p.reg[b] = (float)r;
+    }
+  }
+  const int HW = p.HW;
+  const unsigned char* in = p.in8 + (size_t)b * 3 * HW;
+  unsigned char* out = p.out8 + (size_t)b * 3 * HW;
+  const int stride = gridDim.x * THREADS * VEC;
+  for (int i = (blockIdx.x * THREADS + threadIdx.x) * VEC; i < HW; i += stride) {
+    if constexpr (VEC == 4) {
+      float ch[3][4];
+      if (IN_HWC) {
+        const unsigned* w = reinterpret_cast<const unsigned*>(in + 3 * (size_t)i);
+        const unsigned w0 = __ldcs(w), w1 = __ldcs(w + 1), w2 = __ldcs(w + 2);   // r0 g0 b0 r1 | g1 b1 r2 g2 | b2 r3 g3 b3
+        ch[0][0] = byte_of(w0, 0); ch[1][0] = byte_of(w0, 1); ch[2][0] = byte_of(w0, 2);
+        ch[0][1] = byte_of(w0, 3); ch[1][1] = byte_of(w1, 0); ch[2][1] = byte_of(w1, 1);
+        ch[0][2] = byte_of(w1, 2); ch[1][2] = byte_of(w1, 3); ch[2][2] = byte_of(w2, 0);
+        ch[0][3] = byte_of(w2, 1); ch[1][3] = byte_of(w2, 2); ch[2][3] = byte_of(w2, 3);
+      } else {
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          const unsigned w = __ldcs(reinterpret_cast<const unsigned*>(in + (size_t)c * HW + i));
+#pragma unroll
+          for (int k = 0; k < 4; ++k) ch[c][k] = byte_of(w, k);
+        }
+      }
+      const Group<4> m = load_mask<MK, 4>(p.mask, (size_t)b * HW + i);
+      unsigned o[3][4];
+#pragma unroll
+      for (int v = 0; v < 2; ++v) {
+        F2 x[3], y[3];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) x[c] = u8_to_unit(vadd(F2(ch[c][2 * v], ch[c][2 * v + 1]), F2(-TWO23)));
+        layer_fwd<F2, MK>(x, m.v[v], s_ab, y);
+#pragma unroll
+        for (int c = 0; c < 3; ++c) { o[c][2 * v] = unit_to_u8(y[c].lo()); o[c][2 * v + 1] = unit_to_u8(y[c].hi()); }
+      }
+      if (OUT_HWC) {
+        unsigned* w = reinterpret_cast<unsigned*>(out + 3 * (size_t)i);
+        __stcs(w, o[0][0] | (o[1][0] << 8) | (o[2][0] << 16) | (o[0][1] << 24));
+        __stcs(w + 1, o[1][1] | (o[2][1] << 8) | (o[0][2] << 16) | (o[1][2] << 24));
+        __stcs(w + 2, o[2][2] | (o[0][3] << 8) | (o[1][3] << 16) | (o[2][3] << 24));
+      } else {
+#pragma unroll
+        for (int c = 0; c < 3; ++c)
+          __stcs(reinterpret_cast<unsigned*>(out + (size_t)c * HW + i),
+                 o[c][0] | (o[c][1] << 8) | (o[c][2] << 16) | (o[c][3] << 24));
+      }
+    } else {
+      float x[3], y[3];
+#pragma unroll
+      for (int c = 0; c < 3; ++c)
+        x[c] = u8_to_unit((float)__ldcs(in + (IN_HWC ? 3 * (size_t)i + c : (size_t)c * HW + i)));
+      const Group<1> m = load_mask<MK, 1>(p.mask, (size_t)b * HW + i);
+      layer_fwd<float, MK>(x, m.v[0], s_ab, y);
+#pragma unroll
+      for (int c = 0; c < 3; ++c)
+        __stcs(out + (OUT_HWC ? 3 * (size_t)i + c : (size_t)c * HW + i), (unsigned char)unit_to_u8(y[c]));
+    }
   }
 }
 
@@ -724,6 +817,54 @@ int curl_layer_fwd_f32(const float* img, const void* mask, int mask_kind, const 
     case CURL_MASK_NONE: return launch_fwd<OpLayer, MASK_NONE>(p, B, v4, st);
     case CURL_MASK_U8: return launch_fwd<OpLayer, MASK_U8>(p, B, v4, st);
     default: return launch_fwd<OpLayer, MASK_F32>(p, B, v4, st);
+  }
+}
+
+}  // extern "C"
+
+template <int MK>
+static int launch_fwd_u8(const KParams& p, int B, bool vec4, int in_layout, int out_layout, cudaStream_t st) {
+  const int vec = vec4 ? 4 : 1;
+  dim3 grid(blocks_per_image(B, p.HW, vec, FWD_GRID_BLOCKS_PER_SM), B);
+  const int sel = (in_layout == CURL_LAYOUT_HWC ? 2 : 0) | (out_layout == CURL_LAYOUT_HWC ? 1 : 0);
+#define CURL_U8_LAUNCH(IH, OH)                                                     \
+  do {                                                                             \
+    if (vec4) fwd_u8_kernel<MK, IH, OH, 4><<<grid, THREADS, 0, st>>>(p);            \
+    else fwd_u8_kernel<MK, IH, OH, 1><<<grid, THREADS, 0, st>>>(p);                 \
+  } while (0)
+  switch (sel) {
+    case 0: CURL_U8_LAUNCH(false, false); break;
+    case 1: CURL_U8_LAUNCH(false, true); break;
+    case 2: CURL_U8_LAUNCH(true, false); break;
+    default: CURL_U8_LAUNCH(true, true); break;
+  }
+#undef CURL_U8_LAUNCH
+  return check_launch();
+}
+
+extern "C" {
+
+int curl_layer_fwd_u8(const uint8_t* img, int in_layout, const void* mask, int mask_kind, const float* L,
+                      int64_t ldL, const float* R, int64_t ldR, const float* Hk, int64_t ldH, uint8_t* out,
+                      int out_layout, float* reg, int B, int H, int W, int K_lab, int K_rgb, int K_hsv,
+                      void* stream) {
+  KParams p;
+  // layer_params validates everything but the image pointers (its float* img is only null-checked here)
+  int rc = layer_params(p, reinterpret_cast<const float*>(L), mask, mask_kind, L, ldL, R, ldR, Hk, ldH, B, H, W, K_lab,
+                        K_rgb, K_hsv);
+  if (rc != CURL_OK) return rc;
+  if (!img || !out || !reg) return CURL_ERR_BAD_ARG;
+  if (in_layout < CURL_LAYOUT_CHW || in_layout > CURL_LAYOUT_HWC) return CURL_ERR_BAD_ARG;
+  if (out_layout < CURL_LAYOUT_CHW || out_layout > CURL_LAYOUT_HWC) return CURL_ERR_BAD_ARG;
+  p.in = nullptr; p.in8 = img; p.out8 = out; p.reg = reg;
+  bool v4 = (p.HW % 4 == 0) && aligned4(img) && aligned4(out);
+  if (mask_kind == CURL_MASK_U8 && !aligned4(mask)) v4 = false;
+  if (mask_kind == CURL_MASK_F32 && !aligned16(mask)) v4 = false;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  switch (mask_kind) {
+    case CURL_MASK_NONE: return launch_fwd_u8<MASK_NONE>(p, B, v4, in_layout, out_layout, st);
+    case CURL_MASK_U8: return launch_fwd_u8<MASK_U8>(p, B, v4, in_layout, out_layout, st);
+    default: return launch_fwd_u8<MASK_F32>(p, B, v4, in_layout, out_layout, st);
   }
 }
 

@@ -91,6 +91,26 @@ CURL_HD float vsel_lt(float a, float b, float t, float f) { return a < b ? t : f
 CURL_HD float vsel_eq(float a, float b, float t, float f) { return a == b ? t : f; }
 CURL_HD float vhsum(float a) { return a; }   // horizontal sum over the lanes of one value
 
+// 8-bit image I/O (reference: torchvision TF.to_tensor = u8 / 255 in fp32; (x * 255) truncated to u8
+// on the way out, evaluate.py:63).  u8_to_unit returns the correctly rounded quotient without a
+// division: one Newton step on the residual, verified against f / 255.0f for all 256 inputs
+// (tests/test_hostsim.py).  unit_to_u8 expects 0 <= y <= 1.
+template <class T>
+CURL_HD T u8_to_unit(T f) {   // f: an exact integer 0..255 held as a float
+  const T r = T((float)(1.0 / 255.0));
+  const T q = vmul(f, r);
+  const T rem = vfma(q, T(-255.0f), f);
+  return vfma(rem, r, q);
+}
+CURL_HD unsigned unit_to_u8(float y) {
+  const float v = y * 255.0f;             // rounded to nearest like torch's mul, then truncated
+#if defined(__CUDA_ARCH__)
+  return __float_as_uint(__fadd_rd(v, 8388608.0f)) & 0xffu;   // floor via the 2^23 trick: no F2I
+#else
+  return (unsigned)v;
+#endif
+}
+
 // ------------------------------------------------------------------------------------------------
 // F2 lanes (device only)
 // ------------------------------------------------------------------------------------------------

@@ -262,3 +262,54 @@ class ApplyCurveFn(torch.autograd.Function):
         _lib.check(rc, "curl_apply_curve_bwd_f32")
         _lib.count_launch()
         return gin, gC, None, None
+
+
+def curl_layer_u8(img, mask, L, R, H, k_lab, k_rgb, k_hsv, layout="CHW", out_layout=None):
+    """Inference on 8-bit images (curl_layer_fwd_u8): img is uint8 [B,3,H,W] (layout "CHW", what
+    TF.to_tensor starts from after its permute) or [B,H,W,3] ("HWC", what PIL / plt.imsave hold);
+    returns (uint8 image in `out_layout` (default: same as the input), reg[B]).  x = u8/255 on the way
+    in (data.py:152-158), trunc(out*255) on the way out (evaluate.py:63).  No autograd."""
+    lib = _lib.load()
+    layouts = {"CHW": _lib.LAYOUT_CHW, "HWC": _lib.LAYOUT_HWC}
+    if layout not in layouts or (out_layout is not None and out_layout not in layouts):
+        raise ValueError("curl_b200: layout must be 'CHW' or 'HWC'")
+    out_layout = layout if out_layout is None else out_layout
+    if not isinstance(img, torch.Tensor) or not img.is_cuda:
+        raise RuntimeError("curl_b200: img must be a CUDA tensor (this path has no CPU implementation)")
+    if img.dtype != torch.uint8:
+        raise TypeError("curl_b200: forward_u8 takes a uint8 image, got %s" % img.dtype)
+    cdim = 1 if layout == "CHW" else 3
+    if img.dim() != 4 or img.shape[cdim] != 3 or img.numel() == 0:
+        raise ValueError("curl_b200: img must have shape %s, got %s"
+                         % ("[B,3,H,W]" if layout == "CHW" else "[B,H,W,3]", tuple(img.shape)))
+    img = img.contiguous()
+    dev = img.device
+    B = img.shape[0]
+    h, w = (img.shape[2], img.shape[3]) if layout == "CHW" else (img.shape[1], img.shape[2])
+    L, ldL = _knots(L, 3 * k_lab, "L", dev)
+    R, ldR = _knots(R, 3 * k_rgb, "R", dev)
+    H, ldH = _knots(H, 4 * k_hsv, "H", dev)
+    for P, nm in ((L, "L"), (R, "R"), (H, "H")):
+        if P.shape[0] != B:
+            raise ValueError("curl_b200: %s has batch %d, image has %d" % (nm, P.shape[0], B))
+    if any(t.requires_grad for t in (L, R, H)) and torch.is_grad_enabled():
+        raise RuntimeError("curl_b200: forward_u8 is inference only; call it under torch.no_grad()")
+    shape_like = torch.empty(B, 3, h, w, device="meta")
+    mask, kind = _mask(mask, _MetaShape(shape_like, dev))
+    out = torch.empty((B, 3, h, w) if out_layout == "CHW" else (B, h, w, 3), dtype=torch.uint8, device=dev)
+    reg = torch.empty(B, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        rc = lib.curl_layer_fwd_u8(_ptr(img), layouts[layout], _ptr(mask), kind, _ptr(L), ldL, _ptr(R), ldR,
+                                   _ptr(H), ldH, _ptr(out), layouts[out_layout], _ptr(reg), B, h, w,
+                                   k_lab, k_rgb, k_hsv, _stream(dev))
+    _lib.check(rc, "curl_layer_fwd_u8")
+    _lib.count_launch()
+    return out, reg
+
+
+class _MetaShape:
+    """What _mask() needs to know about the image: its NCHW shape and device."""
+
+    def __init__(self, t, dev):
+        self.shape = t.shape
+        self.device = dev

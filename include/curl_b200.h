@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define CURL_ABI_VERSION 1
+#define CURL_ABI_VERSION 2
 
 /* error codes */
 #define CURL_OK 0
@@ -88,6 +88,25 @@ int curl_layer_bwd_f32(const float* img, const void* mask, int mask_kind,
                        float* gimg, float* gL, float* gR, float* gH,
                        void* workspace, size_t workspace_bytes,
                        int B, int H, int W, int K_lab, int K_rgb, int K_hsv, void* stream);
+
+/*
+ * Inference on 8-bit images: u8 in -> fp32 arithmetic -> u8 out, 7 bytes per pixel over HBM/PCIe
+ * instead of 25.  Replaces the data-format steps the reference wraps around the layer:
+ *   in : torchvision TF.to_tensor on a uint8 image (data.py:152-158, infer.py:38-41): x = u8 / 255
+ *        in fp32, correctly rounded;
+ *   out: (out * 255) truncated to uint8 (evaluate.py:63 `.astype('uint8')`, TF.to_pil_image's
+ *        `.mul(255).byte()`, infer.py:47).
+ * in_layout / out_layout: CURL_LAYOUT_CHW = planar [B][3][H][W] (what to_tensor produces),
+ * CURL_LAYOUT_HWC = interleaved [B][H][W][3] (what PIL / plt.imsave hold, transpose.py).
+ * Everything between the two conversions is curl_layer_fwd_f32, bit for bit.  Forward only.
+ */
+#define CURL_LAYOUT_CHW 0
+#define CURL_LAYOUT_HWC 1
+int curl_layer_fwd_u8(const uint8_t* img, int in_layout, const void* mask, int mask_kind,
+                      const float* L, int64_t ldL, const float* R, int64_t ldR,
+                      const float* Hk, int64_t ldH,
+                      uint8_t* out, int out_layout, float* reg,
+                      int B, int H, int W, int K_lab, int K_rgb, int K_hsv, void* stream);
 
 /* Bytes of device workspace the two *_bwd_f32 entry points need for this shape (host-only call). */
 size_t curl_bwd_workspace_bytes(int B, int H, int W);

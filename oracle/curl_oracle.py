@@ -248,3 +248,25 @@ def curl_layer_fwd_bwd(img, mask, L, R, H, gout, greg, **kw):
     loss = (out * gout).sum() + (reg * greg).sum()
     gimg, gL, gR, gH = torch.autograd.grad(loss, (img, L, R, H))
     return {"out": out.detach(), "reg": reg.detach(), "gimg": gimg, "gL": gL, "gR": gR, "gH": gH}
+
+
+# ---------------------------------------------------------------------------------------------
+# 8-bit I/O around the layer: what the reference's data path does on either side of it
+# ---------------------------------------------------------------------------------------------
+
+def u8_to_unit(img_u8):
+    """torchvision TF.to_tensor on a uint8 image (data.py:152-158, infer.py:38-41), minus its HWC->CHW
+    permute: `img.to(float32).div(255)`.  Pinned against torchvision in tests/test_oracle_pins.py."""
+    return img_u8.to(torch.float32).div(255)
+
+
+def unit_to_u8(img):
+    """evaluate.py:63 `(numpy_batch[i] * 255).astype('uint8')` == TF.to_pil_image's `.mul(255).byte()`
+    (infer.py:47): multiply in fp32, truncate."""
+    return img.mul(255).to(torch.uint8)
+
+
+def curl_layer_u8(img_u8, mask, L, R, H, **kw):
+    """uint8 CHW image in, uint8 CHW image out; returns (out_u8, reg, out_fp32)."""
+    out, reg = curl_layer(u8_to_unit(img_u8), mask, L, R, H, **kw)
+    return unit_to_u8(out), reg, out

@@ -90,3 +90,16 @@ def adjust(group, x, P, K, gy=None, greg=None):
     rc = lib().sim_adjust(1, group, _f(x), _f(P), i64(P.shape[1]), None, None, _f(gy), _f(greg), _f(gx), _f(gP), B, h * w, K)
     assert rc == 0
     return dict(gx=gx, gP=gP)
+
+
+def u8_to_unit_table():
+    out = np.empty(256, np.float32)
+    lib().sim_u8_to_unit_table(_f(out))
+    return out
+
+
+def unit_to_u8(y):
+    y = _c(y)
+    out = np.empty(y.shape, np.uint8)
+    lib().sim_unit_to_u8(_f(y), _f(out), ctypes.c_longlong(y.size))
+    return out

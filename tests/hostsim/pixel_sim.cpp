@@ -165,4 +165,13 @@ int sim_adjust(int do_bwd, int group, const float* in, const float* P, int64_t l
   return 0;
 }
 
+// 8-bit I/O conversions of curl_layer_fwd_u8 (curl_vec.cuh), host instantiation: out[i] = u8_to_unit(i)
+// for i = 0..255, and unit_to_u8 over an arbitrary array.
+void sim_u8_to_unit_table(float* out) {
+  for (int i = 0; i < 256; ++i) out[i] = curl::u8_to_unit<float>((float)i);
+}
+void sim_unit_to_u8(const float* y, unsigned char* out, long long n) {
+  for (long long i = 0; i < n; ++i) out[i] = (unsigned char)curl::unit_to_u8(y[i]);
+}
+
 }  // extern "C"

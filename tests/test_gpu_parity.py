@@ -9,7 +9,7 @@ import pytest
 import torch
 
 import parity
-from conftest import LAYER_CASES, STAGE_CASES, ROOT
+from conftest import LAYER_CASES, STAGE_CASES, ROOT, frac_over, rel_to_max
 
 pytestmark = pytest.mark.gpu
 
@@ -297,3 +297,102 @@ def test_errors():
         bad.rgb2lab.rgb_to_xyz.mul_(1.01)
     with pytest.raises(RuntimeError):
         bad(img, None, z(48), z(48), z(64))
+
+
+def _standin_backbone(seed):
+    """timm is not in the image: a small conv net with the GCURLNet head width (160 knots).  The
+    final layer is scaled down so that the predicted curves stay near identity (|param| ~ 0.1)."""
+    import torch.nn as nn
+    torch.manual_seed(seed)
+    net = nn.Sequential(nn.Conv2d(3, 8, 3, stride=2, padding=1), nn.SiLU(), nn.Conv2d(8, 16, 3, stride=2, padding=1),
+                        nn.SiLU(), nn.AdaptiveAvgPool2d(4), nn.Flatten(), nn.Linear(256, 160))
+    with torch.no_grad():
+        net[-1].weight.mul_(0.3)
+        net[-1].bias.normal_(0.0, 0.1)
+    return net
+
+
+@pytest.mark.gpu
+def test_gcurlnet_training_step_vs_oracle():
+    """BASELINE config 3 in miniature: backbone (PyTorch/cuDNN) -> knots -> fused layer -> L1 loss +
+    regulariser, one optimiser-free training step; every backbone gradient against the CPU oracle
+    driven by the same backbone weights (reference model.py:194-203, main.py:254-262)."""
+    import copy
+    import curl_b200
+    from oracle import curl_oracle as O
+    dev = _dev()
+    gen = torch.Generator().manual_seed(77)
+    B, H, W = 4, 64, 64
+    img = torch.rand(B, 3, H, W, generator=gen)
+    tgt = torch.rand(B, 3, H, W, generator=gen)
+    mask = torch.rand(B, 1, H, W, generator=gen) > 0.1
+
+    cpu_bb = _standin_backbone(5)
+    gpu_net = curl_b200.GCURLNet(backbone=copy.deepcopy(cpu_bb)).to(dev)
+
+    def loss_of(out, reg, target, m):
+        return ((out - target).abs() * m).sum() / (3 * m.sum()) + 1e-6 * reg.mean()
+
+    curves = cpu_bb(img)
+    o_out, o_reg = O.curl_layer(img, mask, curves[:, :48], curves[:, 48:96], curves[:, 96:160])
+    loss_of(o_out, o_reg, tgt, mask).backward()
+
+    g_out, g_reg = gpu_net(img.to(dev), mask.to(dev))
+    loss = loss_of(g_out, g_reg, tgt.to(dev), mask.to(dev))
+    loss.backward()
+    assert frac_over(g_out.detach().cpu().numpy(), o_out.detach().numpy(), 1e-5) <= 1e-3
+    for (name, pc), pg in zip(cpu_bb.named_parameters(), gpu_net.backbone.parameters()):
+        assert pg.grad is not None, name
+        assert rel_to_max(pg.grad.cpu().numpy(), pc.grad.numpy()) <= 2e-4, name
+
+
+@pytest.mark.parametrize("layout,out_layout", [("CHW", None), ("HWC", None), ("HWC", "CHW"), ("CHW", "HWC")])
+@pytest.mark.parametrize("shape,masked", [((3, 64, 96), True), ((2, 37, 53), True), ((1, 128, 128), False)])
+def test_layer_u8_vs_oracle(layout, out_layout, shape, masked):
+    """curl_layer_fwd_u8 (8-bit in/out, reference data path folded into the kernel) against the
+    oracle: the fp32 core is the same device code as curl_layer_fwd_f32, so the only differences
+    allowed are the +-1 steps where the fp32 result times 255 sits within 1e-5*255 of an integer
+    (the image tolerance of north_star, carried through the truncation)."""
+    import curl_b200
+    from oracle import curl_oracle as O
+    dev = _dev()
+    B, H, W = shape
+    gen = torch.Generator().manual_seed(4321 + H)
+    img8 = torch.randint(0, 256, (B, 3, H, W), generator=gen, dtype=torch.uint8)
+    mask = (torch.rand(B, 1, H, W, generator=gen) > 0.1) if masked else None
+    L, R, Hk = (0.1 * torch.randn(B, n, generator=gen) for n in (48, 48, 64))
+    omask = mask if masked else torch.ones(B, 1, H, W, dtype=torch.bool)
+    ref8, ref_reg, ref32 = O.curl_layer_u8(img8, omask, L, R, Hk)
+    layer = curl_b200.CURLLayer().to(dev)
+    src = img8 if layout == "CHW" else img8.permute(0, 2, 3, 1).contiguous()
+    with torch.no_grad():
+        out8, reg = layer.forward_u8(src.to(dev), None if mask is None else mask.to(dev), L.to(dev), R.to(dev),
+                                     Hk.to(dev), layout=layout, out_layout=out_layout)
+        # the fp32 entry point on the same pixels: the u8 kernel must agree with it exactly
+        f32, _ = layer(O.u8_to_unit(img8).to(dev), None if mask is None else mask.to(dev), L.to(dev), R.to(dev), Hk.to(dev))
+    eff = out_layout or layout
+    assert out8.dtype == torch.uint8 and out8.shape == ((B, 3, H, W) if eff == "CHW" else (B, H, W, 3))
+    got = out8.cpu() if eff == "CHW" else out8.cpu().permute(0, 3, 1, 2)
+    assert torch.equal(got, O.unit_to_u8(f32.cpu())), "u8 kernel differs from quantised fp32 kernel"
+    diff = (got.to(torch.int16) - ref8.to(torch.int16)).abs()
+    assert int(diff.max()) <= 1
+    v = ref32 * 255
+    near = (v - v.round()).abs() <= 255 * 3e-5           # within the image tolerance of a truncation step
+    assert bool(((diff == 0) | near).all()), "u8 output differs away from a quantisation boundary"
+    assert float((diff != 0).float().mean()) <= 2e-3
+    assert rel_to_max(reg.cpu().numpy(), ref_reg.numpy()) <= 1e-5
+
+
+def test_layer_u8_errors():
+    import curl_b200
+    dev = _dev()
+    layer = curl_b200.CURLLayer().to(dev)
+    z = lambda n: torch.zeros(1, n, device=dev)
+    with pytest.raises(TypeError, match="uint8"):
+        layer.forward_u8(torch.zeros(1, 3, 8, 8, device=dev), None, z(48), z(48), z(64))
+    with pytest.raises(ValueError, match="shape"):
+        layer.forward_u8(torch.zeros(1, 8, 8, 3, dtype=torch.uint8, device=dev), None, z(48), z(48), z(64))
+    with pytest.raises(ValueError, match="layout"):
+        layer.forward_u8(torch.zeros(1, 3, 8, 8, dtype=torch.uint8, device=dev), None, z(48), z(48), z(64), layout="NHWC")
+    with pytest.raises(RuntimeError, match="inference only"):
+        layer.forward_u8(torch.zeros(1, 3, 8, 8, dtype=torch.uint8, device=dev), None, z(48).requires_grad_(True), z(48), z(64))

@@ -75,3 +75,21 @@ def test_hostsim_tie_semantics():
     assert grey[0] == np.float32(1e-9) and grey[1] == np.float32(1e-9) and grey[2] == np.float32(0.3)
     gx = hostsim.color(2, px(0.3, 0.3, 0.3), np.array([0, 0, 1], np.float32).reshape(1, 3, 1, 1))[0, :, 0, 0]
     assert gx.tolist() == [1.0, 0.0, 0.0]      # d v / d rgb goes to channel 0 on a three-way tie
+
+
+def test_u8_conversions_are_exact():
+    """curl_layer_fwd_u8's conversions: u8 -> x/255 must be the correctly rounded quotient for all 256
+    inputs (the kernel uses a multiply + one Newton step, not a division), and the way out must be
+    trunc(rn(y*255)) like numpy's astype('uint8') (evaluate.py:63)."""
+    import torch
+    from oracle import curl_oracle as O
+    tab = hostsim.u8_to_unit_table()
+    want = O.u8_to_unit(torch.arange(256, dtype=torch.uint8)).numpy()
+    assert np.array_equal(tab.view(np.uint32), want.view(np.uint32))
+    rng = np.random.default_rng(3)
+    y = np.concatenate([rng.random(200000, dtype=np.float32), np.arange(256, dtype=np.float32) / np.float32(255),
+                        np.nextafter(np.arange(256, dtype=np.float32) / np.float32(255), np.float32(0)),
+                        np.array([0.0, 1.0, 0.999999, 1e-9], np.float32)]).astype(np.float32)
+    got = hostsim.unit_to_u8(y)
+    assert np.array_equal(got, O.unit_to_u8(torch.from_numpy(y)).numpy())
+    assert np.array_equal(got, (y * np.float32(255)).astype("uint8"))

@@ -88,3 +88,22 @@ def test_product_code_does_not_import_the_oracle():
                 src = open(os.path.join(dirpath, f)).read()
                 assert "import oracle" not in src and "from oracle" not in src, f
                 assert "import hostsim" not in src and "pixel_sim" not in src, f
+
+
+def test_gcurlnet_api():
+    """GCURLNet (reference model.py:179-203): attribute names, knot split, explicit backbone."""
+    import torch.nn as nn
+    net = curl_b200.GCURLNet(backbone=nn.Sequential(nn.AdaptiveAvgPool2d(1), nn.Flatten(), nn.Linear(3, 160)))
+    assert (net.curve_break_1, net.curve_break_2, net.num_curve_params) == (48, 96, 160)
+    assert isinstance(net.curllayer, curl_b200.CURLLayer)
+    assert [k for k in net.state_dict() if k.startswith("curllayer.")][0] == "curllayer.rgb2lab.rgb_to_xyz"
+    with pytest.raises(RuntimeError, match="CUDA"):           # the layer has no CPU path
+        net(torch.rand(1, 3, 8, 8), None)
+    narrow = curl_b200.GCURLNet(backbone=nn.Sequential(nn.AdaptiveAvgPool2d(1), nn.Flatten(), nn.Linear(3, 100)))
+    with pytest.raises(ValueError, match="backbone must return"):
+        narrow(torch.rand(1, 3, 8, 8), None)
+    try:
+        import timm  # noqa: F401
+    except ImportError:
+        with pytest.raises(ImportError, match="backbone="):
+            curl_b200.GCURLNet()
