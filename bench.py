@@ -14,6 +14,9 @@ Printed JSON (rank 0, one line):
             image + mask are copied host->device, forward+backward run, and the regulariser and knot
             gradients are read back device->host
   roofline  the dominant kernel (fused backward, 37 algorithmic B/px) against the measured HBM peak
+  gpu_eager_baseline  the same op sequence run eagerly by PyTorch on this GPU (the reference's own
+            way of using a GPU), one 1080p tile
+  extras    non-headline measurements: BASELINE configs[1] (1080p x16 forward) and the 8-bit inference path
   cpu_baseline  the CPU oracle (the reference's ATen op sequence, restated; kind "port") on this
             box's host cores over a bounded sample of the same workload
 `--impl reference` times only that CPU path (the reference has no native code and /root/reference
@@ -145,6 +148,29 @@ def time_cpu(steps, warmup, h=1080, w=1920):
             "sample": "one %dx%d tile of a 4K image, batch 1, fwd+bwd with image gradient, fp32 (%.2f Mpx/step, "
                       "%d steps, %.2f s/step); oracle/curl_oracle.py = the reference's ATen op sequence "
                       "(bit-identical to the patched reference on CPU)" % (h, w, mpx, steps, dt)}, dt
+
+
+def time_gpu_eager(dev, steps=3, warmup=2, h=1080, w=1920):
+    """The reference's own way of running this path on a GPU: the same ATen op sequence, eagerly, on
+    the B200.  ~650 launches per forward and every intermediate kept for autograd
+    (~3.6 kB/px), which is why the sample is one 1080p tile: 4K x 64 would need ~1.9 TB."""
+    sample = tuple(t.to(dev) for t in cpu_sample(h, w))
+    for _ in range(warmup):
+        cpu_reference_step(sample)
+    torch.cuda.synchronize(dev)
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        cpu_reference_step(sample)
+    e1.record()
+    torch.cuda.synchronize(dev)
+    dt = e0.elapsed_time(e1) / 1e3 / steps
+    mpx = h * w / 1e6
+    peak_gb = torch.cuda.max_memory_allocated(dev) / 1e9
+    return {"value": mpx / dt, "unit": UNIT, "kind": "port, eager PyTorch on this GPU",
+            "sample": "one %dx%d tile, batch 1, fwd+bwd with image gradient, fp32 (%.2f Mpx/step, %d steps, "
+                      "%.1f ms/step); oracle/curl_oracle.py on cuda" % (h, w, mpx, steps, dt * 1e3),
+            "peak_mem_gb": peak_gb}
 
 
 def run_reference(args):
@@ -304,6 +330,46 @@ def run_ours(args):
     h2d = h_img.numel() * 4 + h_mask.numel()
     d2h = h_res.numel() * 4
 
+    # ---- extras (reported beside the headline, never part of it) -----------------------------------
+    def timed(fn, reps=10):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize(dev)
+        a = torch.cuda.Event(enable_timing=True); b_ = torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(reps):
+            fn()
+        b_.record()
+        torch.cuda.synchronize(dev)
+        return a.elapsed_time(b_) / reps
+
+    extras = {}
+    if rank == 0 and not args.no_extras:
+        with torch.no_grad():
+            # BASELINE.json configs[1]: forward only, 1080p, batch 16 (398 MB per tensor > L2)
+            gi, gm, gl, gr, gh = make_inputs(16, 1080, 1920, dev, 4321)
+            ms = timed(lambda: layer(gi, gm, gl, gr, gh), 20)
+            extras["config1_fwd_1080p_b16"] = {"ms": ms, "mpx_per_s": 16 * 1080 * 1920 / 1e6 / (ms / 1e3),
+                                               "gbs": 16 * 1080 * 1920 * FWD_BYTES_PER_PX / (ms / 1e3) / 1e9}
+            del gi, gm, gl, gr, gh
+            # 8-bit inference (curl_layer_fwd_u8): 3 B/px in + 1 mask + 3 B/px out
+            i8 = (img.detach() * 255).to(torch.uint8)
+            ms = timed(lambda: layer.forward_u8(i8, mask, Ld, Rd, Hd), 5)
+            extras["fwd_u8_4k_b%d" % B] = {"ms": ms, "mpx_per_s": n_px / 1e6 / (ms / 1e3), "bytes_per_px": 7,
+                                           "gbs": n_px * 7 / (ms / 1e3) / 1e9}
+            h_i8 = torch.empty(i8.shape, dtype=torch.uint8, pin_memory=True); h_i8.copy_(i8)
+            h_o8 = torch.empty(i8.shape, dtype=torch.uint8, pin_memory=True)
+
+            def u8_e2e():
+                i8.copy_(h_i8, non_blocking=True); d_mask.copy_(h_mask, non_blocking=True)
+                o8, _ = layer.forward_u8(i8, d_mask, Ld, Rd, Hd)
+                h_o8.copy_(o8, non_blocking=True)
+            ms = timed(u8_e2e, 3)
+            extras["fwd_u8_4k_b%d" % B]["e2e_ms"] = ms
+            extras["fwd_u8_4k_b%d" % B]["e2e_mpx_per_s"] = n_px / 1e6 / (ms / 1e3)
+            extras["fwd_u8_4k_b%d" % B]["e2e_what"] = "pinned host u8 image + bool mask -> H2D -> kernel -> D2H u8 image (7 B/px over PCIe)"
+            del i8, h_i8, h_o8
+
     if rank == 0:
         peak, peak_src = measured_peak()
         traffic = None
@@ -340,9 +406,18 @@ def run_ours(args):
             "roofline_step": {"bytes_per_px": FWD_BYTES_PER_PX + BWD_BYTES_PER_PX, "achieved": step_gbs,
                               "frac": step_gbs / peak, "frac_of_8TBps": step_gbs / 8000.0},
         }
+        if extras:
+            line["extras"] = extras
         if world == 1 and not args.no_cpu:
             base, _ = time_cpu(3, 1)
             line["cpu_baseline"] = base
+            try:
+                del img, gout, h_img, d_img
+                torch.cuda.empty_cache()
+                torch.cuda.reset_peak_memory_stats(dev)
+                line["gpu_eager_baseline"] = time_gpu_eager(dev)
+            except Exception as e:   # reported baseline only: never fail the bench line for it
+                line["gpu_eager_baseline"] = {"unavailable": "%s: %s" % (type(e).__name__, str(e)[:200])}
         print(json.dumps(line))
     if world > 1:
         dist.barrier()
@@ -358,7 +433,8 @@ def main():
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--height", type=int, default=H4K)
     ap.add_argument("--width", type=int, default=W4K)
-    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline and gpu_eager_baseline legs")
+    ap.add_argument("--no-extras", action="store_true", help="skip the extra (non-headline) measurements")
     ap.add_argument("--e2e-chunk", type=int, default=8, help="images per host->device chunk in the e2e leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

@@ -66,10 +66,12 @@ def constants(dtype=torch.float32):
 _CONST_CACHE = {}
 
 
-def _c(dtype):
-    if dtype not in _CONST_CACHE:
-        _CONST_CACHE[dtype] = constants(dtype)
-    return _CONST_CACHE[dtype]
+def _c(dtype, device=None):
+    key = (dtype, str(device))
+    if key not in _CONST_CACHE:
+        k = constants(dtype)
+        _CONST_CACHE[key] = k if device is None else {n: v.to(device) for n, v in k.items()}
+    return _CONST_CACHE[key]
 
 
 def _mix(img, m):
@@ -83,7 +85,7 @@ def _mix(img, m):
 
 def rgb2lab(img):
     """colors.py:27-62.  sRGB -> linear -> XYZ/white -> f(t) -> Lab, normalised to about [0,1]."""
-    k = _c(img.dtype)
+    k = _c(img.dtype, img.device)
     x = img.contiguous()
     lo = (x / 12.92) * x.le(0.04045).float()                                       # colors.py:37
     hi = (((torch.clamp(x, min=0.0001) + 0.055) / 1.055) ** 2.4) * x.gt(0.04045).float()  # :37-38
@@ -102,7 +104,7 @@ def rgb2lab(img):
 
 def lab2rgb(img):
     """colors.py:88-123.  Inverse of rgb2lab; no clamp on the output."""
-    k = _c(img.dtype)
+    k = _c(img.dtype, img.device)
     x = img.contiguous()
     c0 = torch.unsqueeze(x[:, 0, :, :] * 100, dim=1)                               # colors.py:97
     c1 = torch.unsqueeze(((x[:, 1, :, :] * 2) - 1) * 110, dim=1)                   # colors.py:98
@@ -129,7 +131,7 @@ def _inv_or_zero(t):
 
 def rgb2hsv(img):
     """colors.py:195-242.  Note the ADDITIVE hue selectors (ties add), colors.py:221-224."""
-    k = _c(img.dtype)
+    k = _c(img.dtype, img.device)
     x = torch.clamp(img, 10 ** (-9), 1.0).contiguous()                              # colors.py:205-208
     mx = torch.max(x, 1)[0]                                                        # colors.py:211
     mn = torch.min(x, 1)[0]                                                        # colors.py:212
