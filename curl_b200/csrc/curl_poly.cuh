@@ -1,0 +1,205 @@
+// Per-pixel arithmetic of the reference's polynomial colour regression ("TriSpace" residual):
+//   ChannelPolyLayer.forward              (reference model.py:319-333)
+//   TriSpaceRegNet.generate_residual      (reference model.py:486-503)
+//   TriSpaceRegNet.generate_image         (reference model.py:505-508)
+// written, like curl_pixel.cuh, as templates over the lane type T (F2 on the device, float in the
+// host-side derivation check).
+//
+// A degree-D polynomial in NV variables has NC = C(NV + D, D) coefficients per output channel.  The
+// reference orders them the way ChannelPolyLayer.generate_powers (model.py:221-243) enumerates the
+// exponent tuples: by total degree, and inside one degree lexicographically DESCENDING in
+// (e0, e1, ...): 1, x0, x1, .., x0^2, x0 x1, .., x1^2, ...  mono_rank() is that position, computed at
+// compile time; mono_visit() walks all monomials depth-first (each is its parent times one
+// variable, so one multiply per monomial and at most D partial products alive) and hands every
+// (rank, value) to a visitor.  Nothing is tabulated at run time and no [.., NC, H, W] tensor exists.
+#pragma once
+
+#include "curl_pixel.cuh"
+
+namespace curl {
+
+// ------------------------------------------------------------------------------------------------
+// Compile-time combinatorics
+// ------------------------------------------------------------------------------------------------
+#if defined(__CUDACC__)
+#define CURL_CX __host__ __device__ constexpr
+#else
+#define CURL_CX constexpr
+#endif
+CURL_CX int binom(int n, int r) {
+  if (r < 0 || r > n) return 0;
+  long long v = 1;
+  for (int i = 1; i <= r; ++i) v = v * (n - r + i) / i;
+  return (int)v;
+}
+// number of m-tuples of non-negative integers with sum s
+CURL_CX int ncomp(int s, int m) { return m == 0 ? (s == 0 ? 1 : 0) : binom(s + m - 1, m - 1); }
+CURL_CX int poly_num_coeffs(int nv, int deg) { return binom(nv + deg, deg); }
+
+// position of the exponent tuple e[0..nv) in the reference's coefficient order
+CURL_CX int mono_rank(int nv, int e0, int e1, int e2, int e3, int e4) {
+  const int e[5] = {e0, e1, e2, e3, e4};
+  int d = 0;
+  for (int i = 0; i < nv; ++i) d += e[i];
+  int r = 0;
+  for (int j = 0; j < d; ++j) r += ncomp(j, nv);             // all monomials of lower degree
+  int rem = d;
+  for (int i = 0; i + 1 < nv; ++i) {                         // tuples of the same degree that come first
+    for (int f = e[i] + 1; f <= rem; ++f) r += ncomp(rem - f, nv - 1 - i);
+    rem -= e[i];
+  }
+  return r;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Depth-first walk over the monomials of degree 1..DEG (the constant term, rank 0, is the caller's).
+// Visitor: template <int RANK> void operator()(T value).
+// ------------------------------------------------------------------------------------------------
+template <class T, int NV, int LEFT, int V, int E0, int E1, int E2, int E3, int E4>
+struct MonoWalk {
+  template <int v, class Vis>
+  static CURL_HD void from(const T* x, T prod, Vis& vis) {
+    if constexpr (v < NV) {
+      constexpr int F0 = E0 + (v == 0), F1 = E1 + (v == 1), F2_ = E2 + (v == 2), F3 = E3 + (v == 3), F4 = E4 + (v == 4);
+      const T p = vmul(prod, x[v]);
+      vis.template operator()<mono_rank(NV, F0, F1, F2_, F3, F4)>(p);
+      if constexpr (LEFT > 1) MonoWalk<T, NV, LEFT - 1, v, F0, F1, F2_, F3, F4>::template from<v>(x, p, vis);
+      from<v + 1>(x, prod, vis);
+    }
+  }
+};
+
+template <class T, int NV, int DEG, class Vis>
+CURL_HD void mono_visit(const T* x, Vis& vis) {
+  // degree-1 monomials are the variables themselves: start the walk from prod = 1 without the multiply
+  MonoWalk<T, NV, DEG, 0, 0, 0, 0, 0, 0>::template from<0>(x, T(1.0f), vis);
+}
+
+// out_c = sum_k coef[c][k] * monomial_k   (model.py:331-333).  coef: [3][NC] floats (shared memory on
+// the device: every lane reads the same address, a broadcast).
+template <class T, int NC>
+struct PolyEval {
+  const float* coef;
+  T acc[3];
+  template <int RANK>
+  CURL_HD void operator()(T m) {
+    acc[0] = vfma(T(coef[RANK]), m, acc[0]);
+    acc[1] = vfma(T(coef[NC + RANK]), m, acc[1]);
+    acc[2] = vfma(T(coef[2 * NC + RANK]), m, acc[2]);
+  }
+};
+
+template <class T, int NV, int DEG>
+CURL_HD void poly_eval(const T* x, const float* coef, T out[3]) {
+  constexpr int NC = poly_num_coeffs(NV, DEG);
+  PolyEval<T, NC> ev{coef, {T(coef[0]), T(coef[NC]), T(coef[2 * NC])}};     // the constant term
+  mono_visit<T, NV, DEG>(x, ev);
+  out[0] = ev.acc[0]; out[1] = ev.acc[1]; out[2] = ev.acc[2];
+}
+
+// sigmoid and its derivative from the value
+template <class T>
+CURL_HD T vsigmoid(T p) {
+  const T e = vex2(vmul(p, T(-1.4426950408889634f)));        // exp(-p)
+  return vrcp(vadd(e, T(1.0f)));
+}
+
+// ------------------------------------------------------------------------------------------------
+// TriSpaceRegNet.generate_residual (+ generate_image when clamp)      (model.py:486-508)
+//   rgb_res = sigmoid(poly(rgb | x, y ; R))
+//   lab_res = lab2rgb(sigmoid(poly(rgb2lab(rgb) | x, y ; L)))
+//   hsv_res = hsv2rgb(sigmoid(poly(rgb2hsv(rgb) | x, y ; H)))
+//   residual = 2 (rgb_res - 0.5) + 2 (lab_res - 0.5) + 2 (hsv_res - 0.5)
+//   out = clamp ? clamp(rgb + residual, 0, 1) : residual
+// NV = 3 (spatial=False) or 5 (spatial=True: x = column / width, y = row / height appended, model.py:472-484).
+// coef: [space R, L, H][channel][NC].
+// ------------------------------------------------------------------------------------------------
+template <class T, int NV, int DEG>
+CURL_HD void trispace_fwd(const T rgb[3], T xs, T ys, const float* coef, bool clamp, T out[3]) {
+  constexpr int NC = poly_num_coeffs(NV, DEG);
+  T v[5], p[3], s[3], r[3], res[3];
+  v[3] = xs; v[4] = ys;
+  v[0] = rgb[0]; v[1] = rgb[1]; v[2] = rgb[2];
+  poly_eval<T, NV, DEG>(v, coef, p);
+#pragma unroll
+  for (int k = 0; k < 3; ++k) res[k] = vfma(vsigmoid(p[k]), T(2.0f), T(-1.0f));           // model.py:490,497
+  rgb2lab_fwd<T, false>(rgb, v, nullptr);
+  poly_eval<T, NV, DEG>(v, coef + 3 * NC, p);
+#pragma unroll
+  for (int k = 0; k < 3; ++k) s[k] = vsigmoid(p[k]);
+  lab2rgb_fwd<T, false>(s, r, nullptr);                                                    // model.py:491
+#pragma unroll
+  for (int k = 0; k < 3; ++k) res[k] = vadd(res[k], vfma(r[k], T(2.0f), T(-1.0f)));        // model.py:498,501
+  rgb2hsv_fwd<T, false, false>(rgb, v, nullptr);
+  poly_eval<T, NV, DEG>(v, coef + 6 * NC, p);
+#pragma unroll
+  for (int k = 0; k < 3; ++k) s[k] = vsigmoid(p[k]);
+  hsv2rgb_fwd<T, false, false>(s, r, nullptr);                                             // model.py:492
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    res[k] = vadd(res[k], vfma(r[k], T(2.0f), T(-1.0f)));                                  // model.py:499,501
+    out[k] = clamp ? vadd_sat(rgb[k], res[k]) : res[k];                                    // model.py:508
+  }
+}
+
+// Backward, per-pixel part (the image is data -- TriSpaceRegNet.forward feeds the input or target
+// image, model.py:517-519 -- so only coefficient gradients exist).  Recomputes the forward and
+// returns, per space s, the three colour variables the polynomial saw (vars[s]) and the gradient
+// arriving at the polynomial's three outputs (gp[s]).  The coefficient gradient is then
+//   d coef[s][c][k] = sum over pixels of gp[s][c] * monomial_k(vars[s] | x, y),
+// a reduction the caller organises (curl_trispace.cu).
+template <class T, int NV, int DEG>
+CURL_HD void trispace_gpoly(const T rgb[3], T xs, T ys, const float* coef, bool clamp, const T gout[3],
+                            T vars[3][3], T gp[3][3]) {
+  constexpr int NC = poly_num_coeffs(NV, DEG);
+  T v[5], p[3], s[3][3], r_lab[3], r_hsv[3];
+  RgbJac<T> jl; Hsv2RgbJac<T> jh;
+  v[3] = xs; v[4] = ys;
+  v[0] = vars[0][0] = rgb[0]; v[1] = vars[0][1] = rgb[1]; v[2] = vars[0][2] = rgb[2];
+  poly_eval<T, NV, DEG>(v, coef, p);
+#pragma unroll
+  for (int k = 0; k < 3; ++k) s[0][k] = vsigmoid(p[k]);
+  rgb2lab_fwd<T, false>(rgb, vars[1], nullptr);
+  v[0] = vars[1][0]; v[1] = vars[1][1]; v[2] = vars[1][2];
+  poly_eval<T, NV, DEG>(v, coef + 3 * NC, p);
+#pragma unroll
+  for (int k = 0; k < 3; ++k) s[1][k] = vsigmoid(p[k]);
+  lab2rgb_fwd<T, true>(s[1], r_lab, &jl);
+  rgb2hsv_fwd<T, false, false>(rgb, vars[2], nullptr);
+  v[0] = vars[2][0]; v[1] = vars[2][1]; v[2] = vars[2][2];
+  poly_eval<T, NV, DEG>(v, coef + 6 * NC, p);
+#pragma unroll
+  for (int k = 0; k < 3; ++k) s[2][k] = vsigmoid(p[k]);
+  hsv2rgb_fwd<T, true, false>(s[2], r_hsv, &jh);
+  T g2[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    T g = gout[k];
+    if (clamp) {
+      const T res = vadd(vadd(vfma(s[0][k], T(2.0f), T(-1.0f)), vfma(r_lab[k], T(2.0f), T(-1.0f))),
+                         vfma(r_hsv[k], T(2.0f), T(-1.0f)));
+      const T sum = vadd(rgb[k], res);
+      g = vmul(g, vgate_eq(vsat(sum), sum));       // clamp passes gradient on [0,1] inclusive
+    }
+    g2[k] = vmul(g, T(2.0f));
+  }
+  T ga[3][3];
+  ga[0][0] = g2[0]; ga[0][1] = g2[1]; ga[0][2] = g2[2];
+  lab2rgb_bwd(jl, g2, ga[1]);
+  hsv2rgb_bwd<T, false>(jh, g2, ga[2]);
+#pragma unroll
+  for (int sp = 0; sp < 3; ++sp)
+#pragma unroll
+    for (int k = 0; k < 3; ++k) gp[sp][k] = vmul(ga[sp][k], vmul(s[sp][k], vsub(T(1.0f), s[sp][k])));   // d sigmoid
+}
+
+// visitor that writes monomial k to dst[k * pitch]
+template <class T>
+struct MonoStore {
+  T* dst;
+  int pitch;
+  template <int RANK>
+  CURL_HD void operator()(T m) { dst[RANK * pitch] = m; }
+};
+
+}  // namespace curl

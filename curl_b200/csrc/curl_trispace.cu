@@ -1,0 +1,297 @@
+// sm_100a kernels + C ABI of the polynomial colour regression ("TriSpace" residual), the per-pixel
+// path the reference's main.py / infer.py run through TriSpaceRegNet (model.py:411-520):
+//   curl_trispace_fwd_f32 : generate_residual (+ generate_image), one pass per pixel, no
+//                           [B, NC, H, W] monomial tensor (the reference materialises 126 floats per
+//                           pixel and space)
+//   curl_trispace_bwd_f32 : gradient w.r.t. the 3 x 3 x NC coefficients per image (recompute)
+// Per-pixel math: curl_poly.cuh.  Layout: planar NCHW fp32 like the curve layer; blockIdx.y = image,
+// whose 9 * NC coefficients live in shared memory.
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/curl_b200.h"
+#include "curl_poly.cuh"
+
+namespace curl {
+namespace tri {
+
+constexpr int THREADS = 256;
+constexpr int DEG = 4;                       // the reference's polynomial_order default (model.py:413)
+constexpr int MAX_NC = poly_num_coeffs(5, DEG);
+
+struct TParams {
+  const float* img;      // [B][3][HW]
+  const float* coef[3];  // R, L, H: [B][3][NC]
+  const float* gout;     // backward: [B][3][HW]
+  float* out;            // forward: [B][3][HW]
+  float* gcoef[3];       // backward: [B][3][NC]
+  float* partials;       // backward: [B][gridDim.x][9*NC]
+  unsigned* tickets;     // backward: [B], zero on entry
+  int HW, W, H;
+  int clamp;             // apply generate_image: clamp(img + residual, 0, 1)
+};
+
+static int sm_count() {
+  int dev = 0, n = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+  if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) return 148;
+  return n;
+}
+
+template <int NC>
+__device__ __forceinline__ void stage_coef(const TParams& p, int b, float* s_coef) {
+  for (int i = threadIdx.x; i < 9 * NC; i += blockDim.x) {
+    const int s = i / (3 * NC), j = i - s * 3 * NC;
+    s_coef[i] = p.coef[s][(size_t)b * 3 * NC + j];
+  }
+  __syncthreads();
+}
+
+// normalised pixel coordinates of linear index idx (model.py:480-483): column / width, row / height
+__device__ __forceinline__ void coords(int idx, int W, float fW, float fH, float* xs, float* ys) {
+  const int row = idx / W, col = idx - row * W;
+  *xs = __fdiv_rn((float)col, fW);
+  *ys = __fdiv_rn((float)row, fH);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Forward.  VEC = 2: one packed pixel pair (F2) per thread and iteration, 64-bit accesses -- the
+// kernel is FMA-bound (about 1500 multiply-adds per pixel), not HBM-bound, and the fully unrolled
+// monomial walk wants its registers; VEC = 1: scalar path for odd HW or unaligned bases.
+// ---------------------------------------------------------------------------------------------
+template <int NV, int VEC>
+__global__ void __launch_bounds__(THREADS, 2) trispace_fwd_kernel(const TParams p) {
+  constexpr int NC = poly_num_coeffs(NV, DEG);
+  __shared__ float s_coef[9 * NC];
+  const int b = blockIdx.y;
+  stage_coef<NC>(p, b, s_coef);
+  const int HW = p.HW;
+  const float* in = p.img + (size_t)b * 3 * HW;
+  float* out = p.out + (size_t)b * 3 * HW;
+  const float fW = (float)p.W, fH = (float)p.H;
+  const bool clamp = p.clamp != 0;
+  const int stride = gridDim.x * THREADS * VEC;
+  for (int i = (blockIdx.x * THREADS + threadIdx.x) * VEC; i < HW; i += stride) {
+    if constexpr (VEC == 2) {
+      const float2 c0 = __ldcs(reinterpret_cast<const float2*>(in + i));
+      const float2 c1 = __ldcs(reinterpret_cast<const float2*>(in + HW + i));
+      const float2 c2 = __ldcs(reinterpret_cast<const float2*>(in + 2 * (size_t)HW + i));
+      float xs[2] = {0.f, 0.f}, ys[2] = {0.f, 0.f};
+      if (NV == 5) { coords(i, p.W, fW, fH, &xs[0], &ys[0]); coords(i + 1, p.W, fW, fH, &xs[1], &ys[1]); }
+      const F2 x[3] = {F2(c0.x, c0.y), F2(c1.x, c1.y), F2(c2.x, c2.y)};
+      F2 y[3];
+      trispace_fwd<F2, NV, DEG>(x, F2(xs[0], xs[1]), F2(ys[0], ys[1]), s_coef, clamp, y);
+#pragma unroll
+      for (int c = 0; c < 3; ++c)
+        __stcs(reinterpret_cast<float2*>(out + (size_t)c * HW + i), make_float2(y[c].lo(), y[c].hi()));
+    } else {
+      const float x[3] = {__ldcs(in + i), __ldcs(in + HW + i), __ldcs(in + 2 * (size_t)HW + i)};
+      float xs = 0.f, ys = 0.f, y[3];
+      if (NV == 5) coords(i, p.W, fW, fH, &xs, &ys);
+      trispace_fwd<float, NV, DEG>(x, xs, ys, s_coef, clamp, y);
+#pragma unroll
+      for (int c = 0; c < 3; ++c) __stcs(out + (size_t)c * HW + i, y[c]);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Backward: coefficient gradients  g[s][c][k] = sum_px gp_s_c(px) * monomial_s_k(px), per image a
+// [3 x N] . [N x NC] product for each of the three spaces.  Tiles of 128 pixels:
+//   phase A (thread = pixel):   recompute the forward, get gp (trispace_gpoly), write the tile's
+//            monomials to shared memory T[k][px] (conflict-free: consecutive threads, consecutive px)
+//            and gp to G[px];
+//   phase B (thread = monomial k): acc[c] += G[px][c] * T[k][px] over the tile's pixels (row pitch
+//            132 words: a quarter-warp's 128-bit loads fall in 32 distinct banks).
+// Nine accumulators per thread live across the whole image share; at the end one partial row per
+// block goes to global memory, one atomic ticket per block, and the last block of the image folds
+// the rows in a fixed order in double (bitwise deterministic, no float atomics).
+// ---------------------------------------------------------------------------------------------
+constexpr int BT = 128;              // threads per block = pixels per tile
+constexpr int T_PITCH = BT + 4;
+
+template <int NV>
+constexpr size_t bwd_smem_bytes() {
+  return ((size_t)9 * poly_num_coeffs(NV, DEG) + (size_t)poly_num_coeffs(NV, DEG) * T_PITCH + (size_t)BT * 4) * sizeof(float);
+}
+
+template <int NV>
+__global__ void __launch_bounds__(BT) trispace_bwd_kernel(const TParams p) {
+  constexpr int NC = poly_num_coeffs(NV, DEG);
+  constexpr int NG = 9 * NC;
+  extern __shared__ __align__(16) float smem[];
+  float* s_G = smem;                        // [BT][4]   (16-byte aligned)
+  float* s_T = smem + BT * 4;               // [NC][T_PITCH]
+  float* s_coef = s_T + NC * T_PITCH;       // [9 * NC]
+  __shared__ unsigned s_ticket;
+  const int b = blockIdx.y;
+  const int t = threadIdx.x;
+  stage_coef<NC>(p, b, s_coef);
+  const int HW = p.HW;
+  const float* in = p.img + (size_t)b * 3 * HW;
+  const float* go = p.gout + (size_t)b * 3 * HW;
+  const float fW = (float)p.W, fH = (float)p.H;
+  const bool clamp = p.clamp != 0;
+  float acc[3][3];
+#pragma unroll
+  for (int sp = 0; sp < 3; ++sp) acc[sp][0] = acc[sp][1] = acc[sp][2] = 0.0f;
+  const int n_tiles = (HW + BT - 1) / BT;
+  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const int i = tile * BT + t;
+    const bool valid = i < HW;
+    float x[3], g[3], xs = 0.f, ys = 0.f;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      x[c] = valid ? __ldcs(in + (size_t)c * HW + i) : 0.5f;
+      g[c] = valid ? __ldcs(go + (size_t)c * HW + i) : 0.0f;
+    }
+    if (NV == 5) coords(valid ? i : 0, p.W, fW, fH, &xs, &ys);
+    float vars[3][3], gp[3][3];
+    trispace_gpoly<float, NV, DEG>(x, xs, ys, s_coef, clamp, g, vars, gp);
+#pragma unroll
+    for (int sp = 0; sp < 3; ++sp) {
+      __syncthreads();                               // phase B of the previous space is done with T, G
+      const float v[5] = {vars[sp][0], vars[sp][1], vars[sp][2], xs, ys};
+      s_T[t] = 1.0f;                                 // the constant term
+      MonoStore<float> st{s_T + t, T_PITCH};
+      mono_visit<float, NV, DEG>(v, st);
+      reinterpret_cast<float4*>(s_G)[t] = make_float4(gp[sp][0], gp[sp][1], gp[sp][2], 0.0f);
+      __syncthreads();
+      if (t < NC) {
+        const float4* row = reinterpret_cast<const float4*>(s_T + t * T_PITCH);
+        float a0 = acc[sp][0], a1 = acc[sp][1], a2 = acc[sp][2];
+#pragma unroll 4
+        for (int q = 0; q < BT / 4; ++q) {
+          const float4 m = row[q];
+          const float4 g0 = reinterpret_cast<const float4*>(s_G)[4 * q + 0];
+          const float4 g1 = reinterpret_cast<const float4*>(s_G)[4 * q + 1];
+          const float4 g2 = reinterpret_cast<const float4*>(s_G)[4 * q + 2];
+          const float4 g3 = reinterpret_cast<const float4*>(s_G)[4 * q + 3];
+          a0 = fmaf(g0.x, m.x, a0); a1 = fmaf(g0.y, m.x, a1); a2 = fmaf(g0.z, m.x, a2);
+          a0 = fmaf(g1.x, m.y, a0); a1 = fmaf(g1.y, m.y, a1); a2 = fmaf(g1.z, m.y, a2);
+          a0 = fmaf(g2.x, m.z, a0); a1 = fmaf(g2.y, m.z, a1); a2 = fmaf(g2.z, m.z, a2);
+          a0 = fmaf(g3.x, m.w, a0); a1 = fmaf(g3.y, m.w, a1); a2 = fmaf(g3.z, m.w, a2);
+        }
+        acc[sp][0] = a0; acc[sp][1] = a1; acc[sp][2] = a2;
+      }
+    }
+  }
+  float* row = p.partials + ((size_t)b * gridDim.x + blockIdx.x) * NG;
+  if (t < NC) {
+#pragma unroll
+    for (int sp = 0; sp < 3; ++sp)
+#pragma unroll
+      for (int c = 0; c < 3; ++c) row[(sp * 3 + c) * NC + t] = acc[sp][c];
+  }
+  __threadfence();
+  __syncthreads();
+  if (t == 0) s_ticket = atomicAdd(&p.tickets[b], 1u);
+  __syncthreads();
+  if (s_ticket != gridDim.x - 1) return;
+  __threadfence();
+  const float* rows = p.partials + (size_t)b * gridDim.x * NG;
+  for (int k = t; k < NG; k += BT) {
+    double a = 0.0;
+    for (unsigned r = 0; r < gridDim.x; ++r) a += (double)__ldcg(rows + (size_t)r * NG + k);
+    const int s = k / (3 * NC), j = k - s * 3 * NC;
+    p.gcoef[s][(size_t)b * 3 * NC + j] = (float)a;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Host side
+// ---------------------------------------------------------------------------------------------
+static bool aligned16(const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15u) == 0; }
+static bool aligned4(const void* q) { return (reinterpret_cast<uintptr_t>(q) & 3u) == 0; }
+
+static int grid_x(int B, int HW, int px_per_block, int blocks_per_sm) {
+  const long long tiles = ((long long)HW + px_per_block - 1) / px_per_block;
+  long long cap = ((long long)sm_count() * blocks_per_sm + B - 1) / B;
+  long long n = tiles < cap ? tiles : cap;
+  return (int)(n < 1 ? 1 : n);
+}
+constexpr int FWD_BLOCKS_PER_SM = 16;
+constexpr int BWD_BLOCKS_PER_SM = 12;   // 3 resident blocks per SM (73 KB of shared memory each) x 4 waves
+static int bwd_grid_x(int B, int HW) { return grid_x(B, HW, BT, BWD_BLOCKS_PER_SM); }
+
+static int check_args(const float* img, const float* R, const float* L, const float* Hc, int degree, int spatial,
+                      int B, int H, int W) {
+  if (B <= 0 || H <= 0 || W <= 0 || (long long)H * W > 0x3fffffffLL || B > 65535) return CURL_ERR_BAD_ARG;
+  if (!img || !R || !L || !Hc) return CURL_ERR_BAD_ARG;
+  if (degree != DEG || (spatial != 0 && spatial != 1)) return CURL_ERR_BAD_ARG;
+  if (!aligned4(img) || !aligned4(R) || !aligned4(L) || !aligned4(Hc)) return CURL_ERR_MISALIGNED;
+  return CURL_OK;
+}
+
+template <int NV>
+static int launch_fwd(const TParams& p, int B, bool vec2, cudaStream_t st) {
+  dim3 grid(grid_x(B, p.HW, THREADS * (vec2 ? 2 : 1), FWD_BLOCKS_PER_SM), B);
+  if (vec2) trispace_fwd_kernel<NV, 2><<<grid, THREADS, 0, st>>>(p);
+  else trispace_fwd_kernel<NV, 1><<<grid, THREADS, 0, st>>>(p);
+  return cudaGetLastError() == cudaSuccess ? CURL_OK : CURL_ERR_LAUNCH;
+}
+
+template <int NV>
+static int launch_bwd(const TParams& p, int B, cudaStream_t st) {
+  if (cudaFuncSetAttribute(trispace_bwd_kernel<NV>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           (int)bwd_smem_bytes<NV>()) != cudaSuccess) return CURL_ERR_LAUNCH;
+  dim3 grid(bwd_grid_x(B, p.HW), B);
+  trispace_bwd_kernel<NV><<<grid, BT, bwd_smem_bytes<NV>(), st>>>(p);
+  return cudaGetLastError() == cudaSuccess ? CURL_OK : CURL_ERR_LAUNCH;
+}
+
+}  // namespace tri
+}  // namespace curl
+
+using namespace curl;
+using namespace curl::tri;
+
+extern "C" {
+
+int curl_trispace_num_coeffs(int degree, int spatial) {
+  if (degree < 0 || degree > 8 || (spatial != 0 && spatial != 1)) return 0;
+  return poly_num_coeffs(spatial ? 5 : 3, degree);
+}
+
+int curl_trispace_fwd_f32(const float* img, const float* R, const float* L, const float* Hc, int degree,
+                          int spatial, int final_clamp, float* out, int B, int H, int W, void* stream) {
+  int rc = check_args(img, R, L, Hc, degree, spatial, B, H, W);
+  if (rc != CURL_OK) return rc;
+  if (!out) return CURL_ERR_BAD_ARG;
+  if (!aligned4(out)) return CURL_ERR_MISALIGNED;
+  TParams p{};
+  p.img = img; p.coef[0] = R; p.coef[1] = L; p.coef[2] = Hc; p.out = out;
+  p.HW = H * W; p.W = W; p.H = H; p.clamp = final_clamp ? 1 : 0;
+  const bool v2 = (p.HW % 2 == 0) && ((reinterpret_cast<uintptr_t>(img) | reinterpret_cast<uintptr_t>(out)) & 7u) == 0;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  return spatial ? launch_fwd<5>(p, B, v2, st) : launch_fwd<3>(p, B, v2, st);
+}
+
+size_t curl_trispace_bwd_workspace_bytes(int B, int H, int W, int degree, int spatial) {
+  if (B <= 0 || H <= 0 || W <= 0 || degree != DEG) return 0;
+  const size_t tick_bytes = ((size_t)B * sizeof(unsigned) + 255) / 256 * 256;
+  return tick_bytes + (size_t)B * bwd_grid_x(B, H * W) * 9 * poly_num_coeffs(spatial ? 5 : 3, DEG) * sizeof(float);
+}
+
+int curl_trispace_bwd_f32(const float* img, const float* R, const float* L, const float* Hc, int degree,
+                          int spatial, int final_clamp, const float* gout, float* gR, float* gL, float* gH,
+                          void* workspace, size_t workspace_bytes, int B, int H, int W, void* stream) {
+  int rc = check_args(img, R, L, Hc, degree, spatial, B, H, W);
+  if (rc != CURL_OK) return rc;
+  if (!gout || !gR || !gL || !gH) return CURL_ERR_BAD_ARG;
+  if (!aligned4(gout)) return CURL_ERR_MISALIGNED;
+  const size_t need = curl_trispace_bwd_workspace_bytes(B, H, W, degree, spatial);
+  if (!workspace || workspace_bytes < need || !aligned16(workspace)) return CURL_ERR_WORKSPACE;
+  const size_t tick_bytes = ((size_t)B * sizeof(unsigned) + 255) / 256 * 256;
+  TParams p{};
+  p.img = img; p.coef[0] = R; p.coef[1] = L; p.coef[2] = Hc; p.gout = gout;
+  p.gcoef[0] = gR; p.gcoef[1] = gL; p.gcoef[2] = gH;
+  p.tickets = reinterpret_cast<unsigned*>(workspace);
+  p.partials = reinterpret_cast<float*>(reinterpret_cast<char*>(workspace) + tick_bytes);
+  p.HW = H * W; p.W = W; p.H = H; p.clamp = final_clamp ? 1 : 0;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (cudaMemsetAsync(workspace, 0, tick_bytes, st) != cudaSuccess) return CURL_ERR_LAUNCH;
+  return spatial ? launch_bwd<5>(p, B, st) : launch_bwd<3>(p, B, st);
+}
+
+}  // extern "C"

@@ -313,3 +313,56 @@ class _MetaShape:
     def __init__(self, t, dev):
         self.shape = t.shape
         self.device = dev
+
+
+class TriSpaceFn(torch.autograd.Function):
+    """Fused TriSpaceRegNet.generate_residual (+ generate_image) (reference model.py:486-508) and its
+    recompute backward w.r.t. the polynomial coefficients.  The image is data on this path
+    (model.py:517-519): asking for its gradient raises."""
+
+    @staticmethod
+    def forward(ctx, img, R, L, H, degree, spatial, final_clamp):
+        lib = _lib.load()
+        img = _image(img, "img")
+        dev = img.device
+        B, _, h, w = img.shape
+        nc = lib.curl_trispace_num_coeffs(degree, int(spatial))
+        coefs = []
+        for P, nm in ((R, "R"), (L, "L"), (H, "H")):
+            if not isinstance(P, torch.Tensor) or P.device != dev or P.dtype != torch.float32:
+                raise TypeError("curl_b200: %s must be a float32 tensor on %s" % (nm, dev))
+            if tuple(P.shape) != (B, 3, nc):
+                raise ValueError("curl_b200: %s must have shape [%d, 3, %d] (degree %d, spatial=%s), got %s"
+                                 % (nm, B, nc, degree, bool(spatial), tuple(P.shape)))
+            coefs.append(P.contiguous())
+        out = torch.empty_like(img)
+        with torch.cuda.device(dev):
+            rc = lib.curl_trispace_fwd_f32(_ptr(img), _ptr(coefs[0]), _ptr(coefs[1]), _ptr(coefs[2]), degree,
+                                           int(spatial), int(final_clamp), _ptr(out), B, h, w, _stream(dev))
+        _lib.check(rc, "curl_trispace_fwd_f32")
+        _lib.count_launch()
+        ctx.save_for_backward(img, *coefs)
+        ctx.cfg = (degree, int(spatial), int(final_clamp))
+        return out
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, gout):
+        if ctx.needs_input_grad[0]:
+            raise RuntimeError("curl_b200: the TriSpace residual has no image gradient (the image is data on this "
+                               "path, reference model.py:517-519); detach the image")
+        lib = _lib.load()
+        img, R, L, H = ctx.saved_tensors
+        degree, spatial, final_clamp = ctx.cfg
+        dev = img.device
+        B, _, h, w = img.shape
+        gout = gout.contiguous()
+        gR, gL, gH = torch.empty_like(R), torch.empty_like(L), torch.empty_like(H)
+        n = lib.curl_trispace_bwd_workspace_bytes(B, h, w, degree, spatial)
+        ws = torch.empty(n, dtype=torch.uint8, device=dev)
+        with torch.cuda.device(dev):
+            rc = lib.curl_trispace_bwd_f32(_ptr(img), _ptr(R), _ptr(L), _ptr(H), degree, spatial, final_clamp,
+                                           _ptr(gout), _ptr(gR), _ptr(gL), _ptr(gH), _ptr(ws), n, B, h, w, _stream(dev))
+        _lib.check(rc, "curl_trispace_bwd_f32")
+        _lib.count_launch(2)
+        return None, gR, gL, gH, None, None, None

@@ -103,3 +103,109 @@ def _forward_u8(self, img_u8, mask, L, R, H, layout="CHW", out_layout=None):
 
 
 CURLLayer.forward_u8 = _forward_u8
+
+
+class ChannelPolyLayer(nn.Module):
+    """Holder of the reference's ChannelPolyLayer state (model.py:206-219): `degree`,
+    `num_variables`, `num_out`, `num_coeffs` and the frozen `powers` parameter (state-dict key
+    `polylayer.powers`), in the coefficient order of generate_powers (model.py:221-243).  The
+    arithmetic itself only exists fused into the TriSpace kernels (curl_trispace_*), so calling the
+    layer on its own raises."""
+
+    def __init__(self, degree=3, num_variables=3, num_out=None):
+        super().__init__()
+        if not (isinstance(degree, int) and degree >= 0 and isinstance(num_variables, int) and num_variables >= 0):
+            raise ValueError("`degree` and `num_variables` must be non-negative integers")
+        self.degree = degree
+        self.num_variables = num_variables
+        self.num_out = num_variables if num_out is None else num_out
+        powers = list(self.generate_powers(degree, num_variables))
+        self.num_coeffs = len(powers)
+        self.powers = nn.Parameter(torch.tensor(powers, dtype=torch.float32), requires_grad=False)
+
+    @staticmethod
+    def generate_powers(order, n_variables):
+        """Exponent tuples by total degree, lexicographically descending inside a degree."""
+        import itertools
+        for d in range(order + 1):
+            yield from sorted((t for t in itertools.product(range(d + 1), repeat=n_variables) if sum(t) == d),
+                              reverse=True)
+
+    def forward(self, img, coeffs):
+        raise NotImplementedError("curl_b200: ChannelPolyLayer runs only fused inside TriSpaceRegNet."
+                                  "generate_residual (curl_trispace_fwd_f32); there is no stand-alone kernel")
+
+
+class TriSpaceRegNet(nn.Module):
+    """The reference's TriSpaceRegNet (model.py:411-520) with its per-pixel part -- colour
+    conversions, three polynomials, sigmoids, inverse conversions, residual sum, final clamp -- as one
+    fused sm_100a kernel forward and one backward.  Same constructor arguments, attribute and
+    state-dict names (`polylayer`, `backbone`, `rgb2lab` .. `hsv2rgb`, `x`, `y`) and methods
+    (generate_coefficients, generate_residual, generate_image, forward).  Only polynomial_order == 4
+    (the default) is built.  `backbone`: any module mapping [B,3,H,W] -> [B, 9 * num_coeffs]; without
+    it the reference's timm EfficientNetV2 + 4-layer head (model.py:427-435) is created, which needs
+    timm.  The backbone stays on PyTorch/cuDNN."""
+
+    def __init__(self, polynomial_order=4, spatial=False, max_resolution=10000, is_train=True,
+                 use_sync_bn=False, polylayer=None, backbone=None, pretrained=True):
+        super().__init__()
+        self.num_channels = 3
+        self.num_spaces = 3
+        self.spatial = bool(spatial)
+        self.num_in = self.num_channels + 2 * self.spatial
+        self.order = polynomial_order
+        self.is_train = is_train
+        self.max_resolution = max_resolution
+        self.polylayer = polylayer if polylayer is not None else ChannelPolyLayer(
+            degree=self.order, num_variables=self.num_in, num_out=self.num_channels)
+        self.num_coeffs = self.polylayer.num_coeffs
+        if backbone is None:
+            try:
+                import timm
+            except ImportError as e:
+                raise ImportError("TriSpaceRegNet: timm is not installed; pass backbone=<nn.Module producing "
+                                  "[B, %d] coefficients>" % (9 * self.num_coeffs)) from e
+            backbone = timm.create_model("efficientnetv2_rw_t", pretrained=pretrained)              # model.py:427
+            if use_sync_bn:
+                backbone = nn.SyncBatchNorm.convert_sync_batchnorm(backbone)
+            backbone.classifier = nn.Sequential(nn.Linear(1024, 1024), nn.Linear(1024, 512), nn.Linear(512, 512),
+                                                nn.Linear(512, 9 * self.num_coeffs))                # model.py:430-434
+        self.backbone = backbone
+        self.rgb2lab = colors.RGB2LAB()
+        self.lab2rgb = colors.LAB2RGB()
+        self.rgb2hsv = colors.RGB2HSV()
+        self.hsv2rgb = colors.HSV2RGB()
+        self.sigmoid = nn.Sigmoid()
+        if not self.spatial:                                                                       # model.py:444-452
+            x = torch.zeros(1, 0, 1, max_resolution)
+            y = torch.zeros(1, 0, max_resolution, 1)
+        else:
+            x = torch.arange(0, max_resolution).reshape(1, 1, 1, max_resolution)
+            y = torch.arange(0, max_resolution).reshape(1, 1, max_resolution, 1)
+        self.x = nn.Parameter(x, requires_grad=False)
+        self.y = nn.Parameter(y, requires_grad=False)
+
+    def _fused(self, img, R, L, H, final_clamp):
+        from .functional import TriSpaceFn
+        if img.shape[2] > self.max_resolution or img.shape[3] > self.max_resolution:
+            raise ValueError("img width and height must be less than `max_resolution` (%d)" % self.max_resolution)
+        for m in (self.rgb2lab, self.lab2rgb, self.rgb2hsv, self.hsv2rgb):
+            m._check_constants()
+        return TriSpaceFn.apply(img, R, L, H, self.order, self.spatial, final_clamp)
+
+    def generate_residual(self, img, R, L, H):                                                     # model.py:486-503
+        return self._fused(img, R, L, H, False)
+
+    @staticmethod
+    def generate_image(img, residual):                                                             # model.py:505-508
+        return torch.clamp(img + residual, 0.0, 1.0)
+
+    def generate_coefficients(self, img, mask):                                                    # model.py:510-515
+        coeffs = self.backbone(img * mask).reshape(img.shape[0], self.num_spaces, self.num_channels, self.num_coeffs)
+        return coeffs[:, 0], coeffs[:, 1], coeffs[:, 2]
+
+    def forward(self, img, mask, target_img=None):                                                 # model.py:517-522
+        R, L, H = self.generate_coefficients(img, mask)
+        input_img = img if target_img is None else target_img
+        # training: residual and generate_image in the same kernel; inference: the residual itself
+        return self._fused(input_img, R, L, H, bool(self.is_train))

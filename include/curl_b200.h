@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define CURL_ABI_VERSION 2
+#define CURL_ABI_VERSION 3
 
 /* error codes */
 #define CURL_OK 0
@@ -138,6 +138,41 @@ int curl_apply_curve_bwd_f32(const float* in, const float* C, int64_t ldC, int c
                              const float* gout, const float* greg, float* gin, float* gC,
                              void* workspace, size_t workspace_bytes,
                              int B, int H, int W, int K, void* stream);
+
+/*
+ * Polynomial colour regression ("TriSpace" residual): the per-pixel path of TriSpaceRegNet, which
+ * is what the reference's main.py / infer.py run (model.py:411-520).
+ *
+ * curl_trispace_fwd_f32 replaces TriSpaceRegNet.generate_residual (model.py:486-503) and, when
+ * final_clamp != 0, generate_image (model.py:505-508) as well:
+ *   residual = 2(sigmoid(P_R(rgb)) - .5) + 2(lab2rgb(sigmoid(P_L(rgb2lab(rgb)))) - .5)
+ *            + 2(hsv2rgb(sigmoid(P_H(rgb2hsv(rgb)))) - .5);     out = clamp(img + residual, 0, 1) | residual
+ * P_* = ChannelPolyLayer(degree, num_variables = 3 + 2*spatial, num_out = 3) (model.py:206-333; the
+ * Deg4MobilePolyLayer of model.py:336-408 is the same function): all monomials up to `degree` in the
+ * three colour channels and, if spatial, x = column/W and y = row/H (model.py:472-484), coefficient
+ * order as ChannelPolyLayer.generate_powers enumerates them.  R, L, Hc: [B][3][NC] contiguous,
+ * NC = curl_trispace_num_coeffs(degree, spatial) (35 / 126 for degree 4).  One pass per pixel; the
+ * reference's [B, H, W, NC] monomial tensor (504 B/px per space) is never formed.
+ * Only degree == 4 (the reference's polynomial_order default) is built; other degrees return
+ * CURL_ERR_BAD_ARG.
+ */
+int curl_trispace_num_coeffs(int degree, int spatial);
+int curl_trispace_fwd_f32(const float* img, const float* R, const float* L, const float* Hc,
+                          int degree, int spatial, int final_clamp, float* out,
+                          int B, int H, int W, void* stream);
+/*
+ * Backward of the above w.r.t. the coefficients: gR, gL, gH [B][3][NC] dense, given gout[B][3][H][W].
+ * Replaces torch.autograd over model.py:486-508.  The image is data on this path
+ * (TriSpaceRegNet.forward feeds the input or target image, model.py:517-519), so there is no image
+ * gradient.  Recomputes the forward per pixel; per image the reduction is a [3 x N].[N x NC]
+ * product per space, done tile by tile in shared memory, then one partial row per block, one atomic
+ * ticket per block and a fixed-order fold in double by the image's last block (deterministic).
+ */
+size_t curl_trispace_bwd_workspace_bytes(int B, int H, int W, int degree, int spatial);
+int curl_trispace_bwd_f32(const float* img, const float* R, const float* L, const float* Hc,
+                          int degree, int spatial, int final_clamp, const float* gout,
+                          float* gR, float* gL, float* gH, void* workspace, size_t workspace_bytes,
+                          int B, int H, int W, void* stream);
 
 #ifdef __cplusplus
 }

@@ -272,3 +272,71 @@ def curl_layer_u8(img_u8, mask, L, R, H, **kw):
     """uint8 CHW image in, uint8 CHW image out; returns (out_u8, reg, out_fp32)."""
     out, reg = curl_layer(u8_to_unit(img_u8), mask, L, R, H, **kw)
     return unit_to_u8(out), reg, out
+
+
+# ---------------------------------------------------------------------------------------------
+# Polynomial colour regression ("TriSpace" residual): ChannelPolyLayer (model.py:206-333) and
+# TriSpaceRegNet.generate_residual / generate_image (model.py:472-508)
+# ---------------------------------------------------------------------------------------------
+
+def poly_powers(degree, num_variables):
+    """The exponent tuples in the order ChannelPolyLayer.generate_powers (model.py:221-243) yields
+    them: by total degree, and within a degree lexicographically descending.  Pinned against the
+    reference generator in tests/test_oracle_pins.py."""
+    import itertools
+    out = []
+    for d in range(degree + 1):
+        tuples = [t for t in itertools.product(range(d + 1), repeat=num_variables) if sum(t) == d]
+        out.extend(sorted(tuples, reverse=True))
+    return out
+
+
+def channel_poly(img, coeffs, degree):
+    """ChannelPolyLayer.forward (model.py:319-333): img [B,V,H,W], coeffs [B,C,NC] -> [B,C,H,W]."""
+    nv = img.shape[1]
+    powers = torch.tensor(poly_powers(degree, nv), dtype=torch.float32).to(img.dtype).to(img.device)
+    nc = powers.shape[0]
+    img_us = torch.unsqueeze(img, dim=0)                                                       # model.py:319
+    pwrs_rs = powers.reshape(nc, 1, nv, 1, 1)                                                  # model.py:320
+    poly_terms = torch.permute(torch.pow(img_us, pwrs_rs), [1, 2, 3, 4, 0]).prod(dim=1)        # model.py:321
+    return (coeffs.reshape(img.shape[0], coeffs.shape[1], 1, 1, nc) *
+            torch.unsqueeze(poly_terms, dim=1)).sum(dim=-1)                                    # model.py:332-333
+
+
+def cat_coords(img, spatial):
+    """TriSpaceRegNet.cat_coords (model.py:472-484): appends x = column/width, y = row/height."""
+    if not spatial:
+        return img
+    B, _, H, W = img.shape
+    zeros = img[:, 0:1] * 0.0
+    x = zeros + torch.arange(0, W, device=img.device).reshape(1, 1, 1, W) / W
+    y = zeros + torch.arange(0, H, device=img.device).reshape(1, 1, H, 1) / H
+    return torch.cat([img, x.to(img.dtype), y.to(img.dtype)], dim=1)
+
+
+def trispace_residual(img, R, L, H, degree=4, spatial=False):
+    """TriSpaceRegNet.generate_residual (model.py:486-503)."""
+    img_rgb = cat_coords(img, spatial)
+    img_lab = cat_coords(rgb2lab(img), spatial)
+    img_hsv = cat_coords(rgb2hsv(img), spatial)
+    rgb_res = torch.sigmoid(channel_poly(img_rgb, R, degree))
+    lab_res = lab2rgb(torch.sigmoid(channel_poly(img_lab, L, degree)))
+    hsv_res = hsv2rgb(torch.sigmoid(channel_poly(img_hsv, H, degree)))
+    rgb_res = 2 * (rgb_res - 0.5)
+    lab_res = 2 * (lab_res - 0.5)
+    hsv_res = 2 * (hsv_res - 0.5)
+    return rgb_res + lab_res + hsv_res
+
+
+def trispace_image(img, residual):
+    """TriSpaceRegNet.generate_image (model.py:505-508)."""
+    return torch.clamp(img + residual, 0.0, 1.0)
+
+
+def trispace_fwd_bwd(img, R, L, H, gout, degree=4, spatial=False, final_clamp=True):
+    R, L, H = (t.detach().clone().requires_grad_(True) for t in (R, L, H))
+    out = trispace_residual(img, R, L, H, degree, spatial)
+    if final_clamp:
+        out = trispace_image(img, out)
+    gR, gL, gH = torch.autograd.grad((out * gout).sum(), (R, L, H))
+    return {"out": out.detach(), "gR": gR, "gL": gL, "gH": gH}

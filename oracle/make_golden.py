@@ -143,8 +143,52 @@ def main():
                 blob[f"{cname}.{aname}.{tag}.gx"] = gx.numpy()
                 blob[f"{cname}.{aname}.{tag}.gP"] = gP.numpy()
     np.savez_compressed(os.path.join(GOLDEN_DIR, "stages.npz"), **blob)
-    for f in ("layer.npz", "stages.npz"):
+    trispace_golden()
+    for f in ("layer.npz", "stages.npz", "trispace.npz"):
         print(f, os.path.getsize(os.path.join(GOLDEN_DIR, f)), "bytes")
+
+
+TRISPACE_CASES = ["rgb", "spatial", "spatial_mobile", "uint8", "edges"]
+
+
+def trispace_golden():
+    """tests/golden/trispace.npz: the reference's TriSpaceRegNet.generate_residual / generate_image
+    (model.py:486-508) executed through oracle/ref_loader.load_trispace, fp32 and fp64, with the
+    coefficient gradients of loss = sum(out * gout) by autograd."""
+    g = torch.Generator().manual_seed(20261105)
+    blob = {}
+    for case in TRISPACE_CASES:
+        spatial = case.startswith("spatial")
+        B, H, W = (1, 16, 32) if case == "edges" else (2, 14, 18)
+        if case == "edges":
+            img = _edge_image()
+        else:
+            img = torch.rand(B, 3, H, W, generator=g)
+            if case == "uint8":
+                img = (img * 255).round() / 255
+        _, net = ref_loader.load_trispace(4, spatial, mobile=(case == "spatial_mobile"))
+        nc = net.polylayer.num_coeffs
+        R, L, Hc = (0.3 * torch.randn(B, 3, nc, generator=g) for _ in range(3))
+        gout = torch.randn(B, 3, H, W, generator=g)
+        blob.update({f"{case}.img": img.numpy(), f"{case}.R": R.numpy(), f"{case}.L": L.numpy(),
+                     f"{case}.H": Hc.numpy(), f"{case}.gout": gout.numpy(),
+                     f"{case}.spatial": np.array(int(spatial))})
+        for tag, dtype in (("f32", torch.float32), ("f64", torch.float64)):
+            net_d = net.to(dtype) if dtype == torch.float64 else net
+            for clamp in (0, 1):
+                a = [t.to(dtype).clone().requires_grad_(True) for t in (R, L, Hc)]
+                xi = img.to(dtype)
+                if dtype == torch.float64:                    # x / y coordinate parameters are int64: keep them
+                    net_d.x.data = net_d.x.data.to(torch.int64) if spatial else net_d.x.data
+                    net_d.y.data = net_d.y.data.to(torch.int64) if spatial else net_d.y.data
+                out = net_d.generate_residual(xi, a[0], a[1], a[2])
+                if clamp:
+                    out = net_d.generate_image(xi, out)
+                gr = torch.autograd.grad((out * gout.to(dtype)).sum(), a)
+                blob[f"{case}.{tag}.c{clamp}.out"] = out.detach().numpy()
+                for k, v in zip(("gR", "gL", "gH"), gr):
+                    blob[f"{case}.{tag}.c{clamp}.{k}"] = v.numpy()
+    np.savez_compressed(os.path.join(GOLDEN_DIR, "trispace.npz"), **blob)
 
 
 if __name__ == "__main__":

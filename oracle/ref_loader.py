@@ -59,3 +59,52 @@ def load():
     ns = {"torch": torch, "nn": nn, "colors": colors, "curves": curves}
     exec(compile("\n".join(kept), os.path.join(REFERENCE_ROOT, "model.py"), "exec"), ns)
     return colors, curves, ns["CURLLayer"]
+
+
+def load_trispace(degree=4, spatial=False, mobile=False):
+    """Returns (ChannelPolyLayer_class, net) where `net` is a reference TriSpaceRegNet carrying
+    everything its generate_residual / generate_image need, WITHOUT its backbone: __init__
+    (model.py:413-457) calls timm.create_model, which is not installed, so the object is made with
+    __new__ and given the attributes __init__ would set (polylayer, the four colour modules, sigmoid,
+    the x / y coordinate parameters of model.py:444-452).  The classes themselves are the reference's
+    source, extracted from model.py with ast and executed unmodified.
+    mobile=True uses the reference's Deg4MobilePolyLayer (model.py:336-408) as the polylayer."""
+    import functools
+    import operator
+    import torch
+    import torch.nn as nn
+
+    colors, _, _ = load()
+    with open(os.path.join(REFERENCE_ROOT, "model.py")) as f:
+        msrc = f.read()
+    tree = ast.parse(msrc)
+    ns = {"torch": torch, "nn": nn, "colors": colors, "op": operator, "reduce": functools.reduce}
+    for name in ("ChannelPolyLayer", "Deg4MobilePolyLayer", "TriSpaceRegNet"):
+        cls = [n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == name]
+        assert len(cls) == 1, name
+        src = "\n".join(msrc.splitlines()[cls[0].lineno - 1: cls[0].end_lineno])
+        exec(compile(src, os.path.join(REFERENCE_ROOT, "model.py"), "exec"), ns)
+    Net = ns["TriSpaceRegNet"]
+    net = Net.__new__(Net)
+    nn.Module.__init__(net)
+    net.num_channels, net.num_spaces = 3, 3
+    net.num_in = 3 + 2 * spatial
+    net.order = degree
+    net.max_resolution = 10000
+    if mobile:
+        assert degree == 4 and spatial
+        net.polylayer = ns["Deg4MobilePolyLayer"]()
+    else:
+        net.polylayer = ns["ChannelPolyLayer"](degree=degree, num_variables=net.num_in, num_out=3)
+    net.rgb2lab, net.lab2rgb = colors.RGB2LAB(), colors.LAB2RGB()
+    net.rgb2hsv, net.hsv2rgb = colors.RGB2HSV(), colors.HSV2RGB()
+    net.sigmoid = nn.Sigmoid()
+    if not spatial:                                                            # model.py:444-452
+        x = torch.zeros(1, 0, 1, net.max_resolution)
+        y = torch.zeros(1, 0, net.max_resolution, 1)
+    else:
+        x = torch.arange(0, net.max_resolution).reshape(1, 1, 1, net.max_resolution)
+        y = torch.arange(0, net.max_resolution).reshape(1, 1, net.max_resolution, 1)
+    net.x = torch.nn.Parameter(x, requires_grad=False)
+    net.y = torch.nn.Parameter(y, requires_grad=False)
+    return ns["ChannelPolyLayer"], net

@@ -12,6 +12,7 @@ for p in (ROOT, os.path.join(ROOT, "tests")):
 GOLDEN = os.path.join(ROOT, "tests", "golden")
 LAYER_CASES = ["smooth", "uint8", "edges", "identity", "strong", "widek", "floatmask"]
 STAGE_CASES = ["wide", "edges", "unit"]
+TRISPACE_CASES = ["rgb", "spatial", "spatial_mobile", "uint8", "edges"]
 
 
 def pytest_configure(config):
@@ -26,6 +27,11 @@ def layer_golden():
 @pytest.fixture(scope="session")
 def stage_golden():
     return np.load(os.path.join(GOLDEN, "stages.npz"))
+
+
+@pytest.fixture(scope="session")
+def trispace_golden():
+    return np.load(os.path.join(GOLDEN, "trispace.npz"))
 
 
 def rel_to_max(a, ref):

@@ -10,6 +10,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(HERE, "pixel_sim.cpp")
 HDR = os.path.join(HERE, "..", "..", "curl_b200", "csrc", "curl_pixel.cuh")
 HDR2 = os.path.join(HERE, "..", "..", "curl_b200", "csrc", "curl_vec.cuh")
+HDR3 = os.path.join(HERE, "..", "..", "curl_b200", "csrc", "curl_poly.cuh")
 OUT = os.path.join(HERE, "_build", "libpixel_sim.so")
 
 _lib = None
@@ -19,7 +20,7 @@ def lib():
     global _lib
     if _lib is not None:
         return _lib
-    newest = max(os.path.getmtime(SRC), os.path.getmtime(HDR), os.path.getmtime(HDR2))
+    newest = max(os.path.getmtime(SRC), os.path.getmtime(HDR), os.path.getmtime(HDR2), os.path.getmtime(HDR3))
     if not os.path.exists(OUT) or os.path.getmtime(OUT) < newest:
         os.makedirs(os.path.dirname(OUT), exist_ok=True)
         subprocess.check_call(["g++", "-O2", "-std=c++17", "-shared", "-fPIC", "-o", OUT, SRC])
@@ -103,3 +104,19 @@ def unit_to_u8(y):
     out = np.empty(y.shape, np.uint8)
     lib().sim_unit_to_u8(_f(y), _f(out), ctypes.c_longlong(y.size))
     return out
+
+
+def trispace(img, R, L, Hc, spatial, clamp, gout=None):
+    """Returns out[B,3,H,W] or, when gout is given, dict(gR, gL, gH)."""
+    img = _c(img); R = _c(R); L = _c(L); Hc = _c(Hc)
+    B, _, h, w = img.shape
+    if gout is None:
+        out = np.empty_like(img)
+        rc = lib().sim_trispace(0, _f(img), _f(R), _f(L), _f(Hc), int(spatial), int(clamp), None, _f(out), None, None, None, B, h, w)
+        assert rc == 0
+        return out
+    gout = _c(gout)
+    gR = np.empty_like(R); gL = np.empty_like(L); gH = np.empty_like(Hc)
+    rc = lib().sim_trispace(1, _f(img), _f(R), _f(L), _f(Hc), int(spatial), int(clamp), _f(gout), None, _f(gR), _f(gL), _f(gH), B, h, w)
+    assert rc == 0
+    return dict(gR=gR, gL=gL, gH=gH)

@@ -13,6 +13,7 @@
 #include <vector>
 
 #include "../../curl_b200/csrc/curl_pixel.cuh"
+#include "../../curl_b200/csrc/curl_poly.cuh"
 
 using namespace curl;
 
@@ -162,6 +163,57 @@ int sim_adjust(int do_bwd, int group, const float* in, const float* P, int64_t l
     }
     if (do_bwd) cv.grads(segs, 1, b, momd, greg ? (double)greg[b] : 0.0);
   }
+  return 0;
+}
+
+// TriSpace polynomial residual (curl_poly.cuh), host instantiation.  do_bwd == 0: out[B][3][HW];
+// do_bwd == 1: gR/gL/gH[B][3][NC] accumulated in double over the image (the device kernel's tiling
+// and reduction are not modelled -- only the per-pixel math and the monomial order).
+}  // extern "C"
+template <int NV>
+static void sim_trispace_nv(int do_bwd, const float* img, const float* R, const float* L, const float* Hc, int clamp,
+                            const float* gout, float* out, float* gR, float* gL, float* gH, int B, int H, int W) {
+  constexpr int NC = poly_num_coeffs(NV, 4);
+  const int HW = H * W;
+  std::vector<float> coef(9 * NC), terms(NC);
+  std::vector<double> acc(9 * NC);
+  for (int b = 0; b < B; ++b) {
+    const float* src[3] = {R, L, Hc};
+    for (int s = 0; s < 3; ++s) memcpy(&coef[s * 3 * NC], src[s] + (size_t)b * 3 * NC, sizeof(float) * 3 * NC);
+    std::fill(acc.begin(), acc.end(), 0.0);
+    for (int i = 0; i < HW; ++i) {
+      const float x[3] = {img[((size_t)b * 3 + 0) * HW + i], img[((size_t)b * 3 + 1) * HW + i], img[((size_t)b * 3 + 2) * HW + i]};
+      const float xs = NV == 5 ? (float)(i % W) / (float)W : 0.f, ys = NV == 5 ? (float)(i / W) / (float)H : 0.f;
+      if (!do_bwd) {
+        float y[3];
+        trispace_fwd<float, NV, 4>(x, xs, ys, coef.data(), clamp != 0, y);
+        for (int c = 0; c < 3; ++c) out[((size_t)b * 3 + c) * HW + i] = y[c];
+      } else {
+        const float g[3] = {gout[((size_t)b * 3 + 0) * HW + i], gout[((size_t)b * 3 + 1) * HW + i], gout[((size_t)b * 3 + 2) * HW + i]};
+        float vars[3][3], gp[3][3];
+        trispace_gpoly<float, NV, 4>(x, xs, ys, coef.data(), clamp != 0, g, vars, gp);
+        for (int s = 0; s < 3; ++s) {
+          const float v[5] = {vars[s][0], vars[s][1], vars[s][2], xs, ys};
+          terms[0] = 1.0f;
+          MonoStore<float> st{terms.data(), 1};
+          mono_visit<float, NV, 4>(v, st);
+          for (int c = 0; c < 3; ++c)
+            for (int k = 0; k < NC; ++k) acc[(s * 3 + c) * NC + k] += (double)gp[s][c] * (double)terms[k];
+        }
+      }
+    }
+    if (do_bwd) {
+      float* dst[3] = {gR, gL, gH};
+      for (int s = 0; s < 3; ++s)
+        for (int j = 0; j < 3 * NC; ++j) dst[s][(size_t)b * 3 * NC + j] = (float)acc[s * 3 * NC + j];
+    }
+  }
+}
+extern "C" {
+int sim_trispace(int do_bwd, const float* img, const float* R, const float* L, const float* Hc, int spatial, int clamp,
+                 const float* gout, float* out, float* gR, float* gL, float* gH, int B, int H, int W) {
+  if (spatial) sim_trispace_nv<5>(do_bwd, img, R, L, Hc, clamp, gout, out, gR, gL, gH, B, H, W);
+  else sim_trispace_nv<3>(do_bwd, img, R, L, Hc, clamp, gout, out, gR, gL, gH, B, H, W);
   return 0;
 }
 

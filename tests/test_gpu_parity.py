@@ -15,6 +15,10 @@ pytestmark = pytest.mark.gpu
 
 REPORT = {}
 
+# the stand-in backbones run on cuDNN; keep them in true fp32 so that they can be compared with the CPU
+torch.backends.cudnn.allow_tf32 = False
+torch.backends.cuda.matmul.allow_tf32 = False
+
 
 def _dev():
     assert torch.cuda.is_available(), "GPU tests need a CUDA device"
@@ -396,3 +400,103 @@ def test_layer_u8_errors():
         layer.forward_u8(torch.zeros(1, 3, 8, 8, dtype=torch.uint8, device=dev), None, z(48), z(48), z(64), layout="NHWC")
     with pytest.raises(RuntimeError, match="inference only"):
         layer.forward_u8(torch.zeros(1, 3, 8, 8, dtype=torch.uint8, device=dev), None, z(48).requires_grad_(True), z(48), z(64))
+
+
+# ---- TriSpace polynomial residual (curl_trispace_*) -----------------------------------------------------
+
+def _tri_check(out, r32, r64, grads, g64):
+    own = np.abs(r32 - r64).max()
+    assert np.abs(out - r64).max() <= max(2e-5, 3 * own)
+    assert frac_over(out, r32, 1e-5) <= 2e-3
+    for k, v in grads.items():
+        assert rel_to_max(v, g64[k]) <= 1e-4, k
+
+
+@pytest.mark.parametrize("clamp", [0, 1])
+@pytest.mark.parametrize("case", ["rgb", "spatial", "spatial_mobile", "uint8", "edges"])
+def test_trispace_vs_golden(case, clamp, trispace_golden):
+    """Fused generate_residual (+ generate_image) forward and coefficient gradients against the
+    fixtures the reference itself produced (model.py:486-508 through oracle/ref_loader)."""
+    import curl_b200
+    import torch.nn as nn
+    g = trispace_golden
+    dev = _dev()
+    spatial = bool(g[f"{case}.spatial"])
+    net = curl_b200.TriSpaceRegNet(spatial=spatial, backbone=nn.Identity()).to(dev)
+    img = torch.from_numpy(g[f"{case}.img"]).to(dev)
+    R, L, Hc = (torch.from_numpy(g[f"{case}.{k}"]).to(dev).requires_grad_(True) for k in ("R", "L", "H"))
+    out = net.generate_residual(img, R, L, Hc) if not clamp else net._fused(img, R, L, Hc, True)
+    out.backward(torch.from_numpy(g[f"{case}.gout"]).to(dev))
+    if clamp:       # the two-step public route gives the same image as the fused one
+        two = net.generate_image(img, net.generate_residual(img, R.detach(), L.detach(), Hc.detach()))
+        assert (two - out.detach()).abs().max().item() <= 1e-6
+    _tri_check(out.detach().cpu().numpy(), g[f"{case}.f32.c{clamp}.out"], g[f"{case}.f64.c{clamp}.out"],
+               dict(gR=R.grad.cpu().numpy(), gL=L.grad.cpu().numpy(), gH=Hc.grad.cpu().numpy()),
+               {k: g[f"{case}.f64.c{clamp}.{k}"] for k in ("gR", "gL", "gH")})
+
+
+@pytest.mark.parametrize("shape,spatial", [((2, 3, 96, 128), True), ((3, 3, 37, 53), True), ((2, 3, 64, 64), False),
+                                           ((1, 3, 255, 131), False)])
+def test_trispace_training_step_vs_oracle(shape, spatial):
+    """TriSpaceRegNet.forward (is_train=True) with a stand-in backbone: output image and every
+    backbone gradient against the oracle on CPU (fp32 and fp64); odd sizes take the scalar path."""
+    import copy
+    import curl_b200
+    import torch.nn as nn
+    from oracle import curl_oracle as O
+    dev = _dev()
+    B, _, H, W = shape
+    gen = torch.Generator().manual_seed(100 + H)
+    nc = 126 if spatial else 35
+    torch.manual_seed(3)
+    bb = nn.Sequential(nn.Conv2d(3, 8, 3, stride=4, padding=1), nn.SiLU(), nn.AdaptiveAvgPool2d(2), nn.Flatten(),
+                       nn.Linear(32, 9 * nc))
+    with torch.no_grad():
+        bb[-1].weight.mul_(0.5); bb[-1].bias.normal_(0.0, 0.3)
+    img = torch.rand(shape, generator=gen)
+    mask = (torch.rand(B, 1, H, W, generator=gen) > 0.1).float()
+    gout = torch.randn(shape, generator=gen)
+    net = curl_b200.TriSpaceRegNet(spatial=spatial, backbone=copy.deepcopy(bb)).to(dev)
+    out = net(img.to(dev), mask.to(dev))
+    out.backward(gout.to(dev))
+    res = {}
+    for dtype in (torch.float32, torch.float64):
+        b2 = copy.deepcopy(bb).to(dtype)
+        co = b2(img.to(dtype) * mask.to(dtype)).reshape(B, 3, 3, nc)
+        o = O.trispace_image(img.to(dtype), O.trispace_residual(img.to(dtype), co[:, 0], co[:, 1], co[:, 2], 4, spatial))
+        (o * gout.to(dtype)).sum().backward()
+        res[dtype] = (o.detach().numpy(), [q.grad.numpy() for q in b2.parameters()])
+    own = np.abs(res[torch.float32][0] - res[torch.float64][0]).max()
+    o = out.detach().cpu().numpy()
+    assert np.abs(o - res[torch.float64][0]).max() <= max(2e-5, 3 * own)
+    assert frac_over(o, res[torch.float32][0], 1e-5) <= 2e-3
+    for pg, g64 in zip(net.backbone.parameters(), res[torch.float64][1]):
+        assert rel_to_max(pg.grad.cpu().numpy(), g64) <= 2e-4
+
+
+def test_trispace_deterministic_and_errors():
+    import curl_b200
+    import torch.nn as nn
+    dev = _dev()
+    net = curl_b200.TriSpaceRegNet(spatial=True, backbone=nn.Identity()).to(dev)
+    gen = torch.Generator().manual_seed(8)
+    img = torch.rand(2, 3, 120, 200, generator=gen).to(dev)
+    gout = torch.randn(2, 3, 120, 200, generator=gen).to(dev)
+    co = [(0.3 * torch.randn(2, 3, 126, generator=gen)).to(dev) for _ in range(3)]
+    runs = []
+    for _ in range(2):
+        a = [c.clone().requires_grad_(True) for c in co]
+        net._fused(img, *a, True).backward(gout)
+        runs.append([t.grad.clone() for t in a])
+    for x, y in zip(*runs):
+        assert torch.equal(x, y)                              # fixed-order reduction
+    with pytest.raises(ValueError, match="shape"):
+        net.generate_residual(img, co[0][:, :, :35], co[1], co[2])
+    with pytest.raises(RuntimeError, match="no image gradient"):
+        a = [c.clone().requires_grad_(True) for c in co]
+        net._fused(img.clone().requires_grad_(True), *a, True).sum().backward()
+    with pytest.raises(NotImplementedError):
+        net.polylayer(img, co[0])
+    with pytest.raises(RuntimeError, match="bad argument"):
+        curl_b200.TriSpaceRegNet(polynomial_order=3, spatial=False, backbone=nn.Identity()).to(dev).generate_residual(
+            img, *[c[:, :, :20].contiguous() for c in co])

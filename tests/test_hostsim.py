@@ -8,7 +8,7 @@ import pytest
 
 import hostsim
 import parity
-from conftest import LAYER_CASES, STAGE_CASES
+from conftest import LAYER_CASES, STAGE_CASES, rel_to_max
 
 
 @pytest.mark.parametrize("case", LAYER_CASES)
@@ -93,3 +93,21 @@ def test_u8_conversions_are_exact():
     got = hostsim.unit_to_u8(y)
     assert np.array_equal(got, O.unit_to_u8(torch.from_numpy(y)).numpy())
     assert np.array_equal(got, (y * np.float32(255)).astype("uint8"))
+
+
+@pytest.mark.parametrize("case", ["rgb", "spatial", "spatial_mobile", "uint8", "edges"])
+def test_hostsim_trispace_vs_golden(case, trispace_golden):
+    """Per-pixel TriSpace math of the kernels (curl_poly.cuh: compile-time monomial order, fused
+    sigmoid / colour chain, hand-derived coefficient gradient) against the reference fixtures."""
+    g = trispace_golden
+    spatial = bool(g[f"{case}.spatial"])
+    img, R, L, Hc, gout = (g[f"{case}.{k}"] for k in ("img", "R", "L", "H", "gout"))
+    for clamp in (0, 1):
+        out = hostsim.trispace(img, R, L, Hc, spatial, clamp)
+        r32, r64 = g[f"{case}.f32.c{clamp}.out"], g[f"{case}.f64.c{clamp}.out"]
+        own = np.abs(r32 - r64).max()
+        assert np.abs(out - r64).max() <= max(2e-5, 3 * own), (case, clamp)
+        assert (np.abs(out - r32) > 1e-5).mean() <= 2e-3, (case, clamp)
+        gr = hostsim.trispace(img, R, L, Hc, spatial, clamp, gout)
+        for k in ("gR", "gL", "gH"):
+            assert rel_to_max(gr[k], g[f"{case}.f64.c{clamp}.{k}"]) <= 1e-4, (case, clamp, k)

@@ -107,3 +107,21 @@ def test_gcurlnet_api():
     except ImportError:
         with pytest.raises(ImportError, match="backbone="):
             curl_b200.GCURLNet()
+
+
+def test_trispace_api():
+    """TriSpaceRegNet / ChannelPolyLayer (reference model.py:206-333, 411-520): names, shapes, order."""
+    import torch.nn as nn
+    net = curl_b200.TriSpaceRegNet(spatial=True, backbone=nn.Identity())
+    sd = net.state_dict()
+    assert {"x", "y", "polylayer.powers", "rgb2lab.rgb_to_xyz", "hsv2rgb" not in sd and "rgb2hsv.comparison_zero"} <= set(sd)
+    assert sd["polylayer.powers"].shape == (126, 5) and sd["x"].shape == (1, 1, 1, 10000) and sd["y"].shape == (1, 1, 10000, 1)
+    assert (net.num_coeffs, net.num_in, net.num_spaces, net.order) == (126, 5, 3, 4)
+    flat = curl_b200.TriSpaceRegNet(spatial=False, backbone=nn.Identity())
+    assert flat.num_coeffs == 35 and flat.state_dict()["x"].shape == (1, 0, 1, 10000)
+    assert [tuple(int(v) for v in r) for r in flat.polylayer.powers.tolist()] == O.poly_powers(4, 3)
+    assert curl_b200.ChannelPolyLayer(3, 3).num_coeffs == 20
+    with pytest.raises(RuntimeError, match="CUDA"):
+        flat.generate_residual(torch.rand(1, 3, 4, 4), *[torch.zeros(1, 3, 35)] * 3)
+    x = torch.rand(1, 3, 4, 4)
+    assert torch.equal(flat.generate_image(x, x), torch.clamp(x + x, 0, 1))
