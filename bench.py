@@ -369,6 +369,29 @@ def run_ours(args):
             extras["fwd_u8_4k_b%d" % B]["e2e_mpx_per_s"] = n_px / 1e6 / (ms / 1e3)
             extras["fwd_u8_4k_b%d" % B]["e2e_what"] = "pinned host u8 image + bool mask -> H2D -> kernel -> D2H u8 image (7 B/px over PCIe)"
             del i8, h_i8, h_o8
+        # TriSpace polynomial residual (TriSpaceRegNet's per-pixel path), spatial=True (126 coefficients),
+        # BASELINE configs[2]'s shape: 512 x 512, batch 32; forward incl. generate_image, and backward
+        import torch.nn as nn
+        tri = curl_b200.TriSpaceRegNet(spatial=True, backbone=nn.Identity()).to(dev)
+        gt = torch.Generator(device=dev).manual_seed(7)
+        ti = torch.rand(32, 3, 512, 512, generator=gt, device=dev)
+        tg = torch.randn(32, 3, 512, 512, generator=gt, device=dev)
+        tc = [(0.3 * torch.randn(32, 3, 126, generator=gt, device=dev)).requires_grad_(True) for _ in range(3)]
+        with torch.no_grad():
+            ms_f = timed(lambda: tri._fused(ti, tc[0], tc[1], tc[2], True), 10)
+
+        def tri_step():
+            for c in tc:
+                c.grad = None
+            tri._fused(ti, tc[0], tc[1], tc[2], True).backward(tg)
+        ms_s = timed(tri_step, 10)
+        tpx = 32 * 512 * 512
+        extras["trispace_512_b32_spatial"] = {
+            "fwd_ms": ms_f, "fwd_mpx_per_s": tpx / 1e6 / (ms_f / 1e3), "fwd_bwd_ms": ms_s,
+            "fwd_bwd_mpx_per_s": tpx / 1e6 / (ms_s / 1e3),
+            "fwd_tflops_fp32": tpx * 3 * (126 + 2 * 3 * 126) / (ms_f / 1e3) / 1e12,
+            "what": "fused generate_residual + generate_image, degree 4, 5 variables; FMA-bound (2646 flop/px forward)"}
+        del ti, tg, tc
 
     if rank == 0:
         peak, peak_src = measured_peak()

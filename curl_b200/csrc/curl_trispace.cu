@@ -115,12 +115,15 @@ constexpr size_t bwd_smem_bytes() {
   return ((size_t)9 * poly_num_coeffs(NV, DEG) + (size_t)poly_num_coeffs(NV, DEG) * T_PITCH + (size_t)BT * 4) * sizeof(float);
 }
 
+#ifndef TRI_BWD_MIN_BLOCKS
+#define TRI_BWD_MIN_BLOCKS 3   // measured: 2 -> 3.80, 3 -> 3.94, 4 -> 3.83 Gpx/s (4K x 8, 126 coefficients)
+#endif
 template <int NV>
-__global__ void __launch_bounds__(BT) trispace_bwd_kernel(const TParams p) {
+__global__ void __launch_bounds__(BT, TRI_BWD_MIN_BLOCKS) trispace_bwd_kernel(const TParams p) {
   constexpr int NC = poly_num_coeffs(NV, DEG);
   constexpr int NG = 9 * NC;
   extern __shared__ __align__(16) float smem[];
-  float* s_G = smem;                        // [BT][4]   (16-byte aligned)
+  float* s_G = smem;                        // [3][BT] + pad (16-byte aligned)
   float* s_T = smem + BT * 4;               // [NC][T_PITCH]
   float* s_coef = s_T + NC * T_PITCH;       // [9 * NC]
   __shared__ unsigned s_ticket;
@@ -155,7 +158,7 @@ __global__ void __launch_bounds__(BT) trispace_bwd_kernel(const TParams p) {
       s_T[t] = 1.0f;                                 // the constant term
       MonoStore<float> st{s_T + t, T_PITCH};
       mono_visit<float, NV, DEG>(v, st);
-      reinterpret_cast<float4*>(s_G)[t] = make_float4(gp[sp][0], gp[sp][1], gp[sp][2], 0.0f);
+      s_G[t] = gp[sp][0]; s_G[BT + t] = gp[sp][1]; s_G[2 * BT + t] = gp[sp][2];
       __syncthreads();
       if (t < NC) {
         const float4* row = reinterpret_cast<const float4*>(s_T + t * T_PITCH);
@@ -163,14 +166,13 @@ __global__ void __launch_bounds__(BT) trispace_bwd_kernel(const TParams p) {
 #pragma unroll 4
         for (int q = 0; q < BT / 4; ++q) {
           const float4 m = row[q];
-          const float4 g0 = reinterpret_cast<const float4*>(s_G)[4 * q + 0];
-          const float4 g1 = reinterpret_cast<const float4*>(s_G)[4 * q + 1];
-          const float4 g2 = reinterpret_cast<const float4*>(s_G)[4 * q + 2];
-          const float4 g3 = reinterpret_cast<const float4*>(s_G)[4 * q + 3];
-          a0 = fmaf(g0.x, m.x, a0); a1 = fmaf(g0.y, m.x, a1); a2 = fmaf(g0.z, m.x, a2);
-          a0 = fmaf(g1.x, m.y, a0); a1 = fmaf(g1.y, m.y, a1); a2 = fmaf(g1.z, m.y, a2);
-          a0 = fmaf(g2.x, m.z, a0); a1 = fmaf(g2.y, m.z, a1); a2 = fmaf(g2.z, m.z, a2);
-          a0 = fmaf(g3.x, m.w, a0); a1 = fmaf(g3.y, m.w, a1); a2 = fmaf(g3.z, m.w, a2);
+          const float4 g0 = reinterpret_cast<const float4*>(s_G)[q];                  // channel 0, four pixels
+          const float4 g1 = reinterpret_cast<const float4*>(s_G + BT)[q];
+          const float4 g2 = reinterpret_cast<const float4*>(s_G + 2 * BT)[q];
+          a0 = fmaf(g0.x, m.x, a0); a1 = fmaf(g1.x, m.x, a1); a2 = fmaf(g2.x, m.x, a2);
+          a0 = fmaf(g0.y, m.y, a0); a1 = fmaf(g1.y, m.y, a1); a2 = fmaf(g2.y, m.y, a2);
+          a0 = fmaf(g0.z, m.z, a0); a1 = fmaf(g1.z, m.z, a1); a2 = fmaf(g2.z, m.z, a2);
+          a0 = fmaf(g0.w, m.w, a0); a1 = fmaf(g1.w, m.w, a1); a2 = fmaf(g2.w, m.w, a2);
         }
         acc[sp][0] = a0; acc[sp][1] = a1; acc[sp][2] = a2;
       }

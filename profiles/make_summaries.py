@@ -14,7 +14,7 @@ for r in rows[1:]:
 with open('profiles/r01_launches.csv','w') as f:
     csv.writer(f).writerows(out)
 tot=sum(sum(v) for v in agg.values())
-lines=['# Round 1 -- ncu launch list (`profiles/prof.sh`, bench.py --batch 8 --steps 2 --warmup 3 --no-cpu)','',
+lines=['# Round 1 -- ncu launch list (`profiles/prof.sh`, bench.py --batch 8 --steps 2 --warmup 3 --no-cpu --no-extras)','',
  'Per-launch times under ncu are cold-cache and serialised: compare SHARES, not absolutes.','',
  '| kernel | launches | total us | share |','|---|---|---|---|']
 for k,v in sorted(agg.items(), key=lambda kv:-sum(kv[1])):
