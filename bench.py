@@ -344,7 +344,7 @@ def run_ours(args):
         return a.elapsed_time(b_) / reps
 
     extras = {}
-    if rank == 0 and not args.no_extras:
+    if rank == 0 and world == 1 and not args.no_extras:
         with torch.no_grad():
             # BASELINE.json configs[1]: forward only, 1080p, batch 16 (398 MB per tensor > L2)
             gi, gm, gl, gr, gh = make_inputs(16, 1080, 1920, dev, 4321)
