@@ -249,7 +249,12 @@ CURL_HD void rgb2hsv_fwd(const T x[3], T hsv[3], HsvJac<T>* jac) {
   const T mx = vmax(xc[0], vmax(xc[1], xc[2]));                // colors.py:211
   const T mn = vmin(xc[0], vmin(xc[1], xc[2]));                // colors.py:212
   const T df = vsub(mx, mn);                                   // colors.py:214
-  const T dinv = vsel_eq(df, T(0.0f), T(0.0f), vrcp(df));      // colors.py:186-193,220
+  // 1/df and 1/mx from ONE reciprocal, r = 1/(df mx): MUFU is the forward kernel's busiest pipe.
+  // dfc keeps the product away from zero on grey pixels (df == 0), where 1/df is defined as 0
+  // (colors.py:186-193) and 1/mx must stay exact: dfc r = 1/mx either way.
+  const T dfc = vmax(df, T(1e-20f));
+  const T rr = vrcp(vmul(dfc, mx));
+  const T dinv = vsel_eq(df, T(0.0f), T(0.0f), vmul(mx, rr));  // colors.py:186-193,220
   const T nz = vgate_ne(df, T(0.0f));
   const T s0 = vgate_eq(xc[0], mx), s1 = vgate_eq(xc[1], mx), s2 = vgate_eq(xc[2], mx);
   const T d12 = vsub(xc[1], xc[2]), d20 = vsub(xc[2], xc[0]), d01 = vsub(xc[0], xc[1]);
@@ -260,7 +265,7 @@ CURL_HD void rgb2hsv_fwd(const T x[3], T hsv[3], HsvJac<T>* jac) {
   hr = vmul(hr, nz);
   // colors.py:225-231:  h = (60 hr (+360 if negative)) / 360
   const T h = vfma(hr, T((float)(1.0 / 6.0)), vgate_lt(hr, T(0.0f)));
-  const T minv = vrcp(mx);                                     // colors.py:234 (mx >= 1e-9, never 0)
+  const T minv = vmul(dfc, rr);                                // colors.py:234 (mx >= 1e-9, never 0)
   const T s = vmul(df, minv);                                  // colors.py:235-237
   // colors.py:240
   hsv[0] = vmin(vmax(h, T(k::HSV_LO)), T(1.0f));

@@ -38,11 +38,12 @@ static int sm_count() {
   return n;
 }
 
+// coefficients of image b -> shared memory as [space][monomial] Coef4 records {c0, c1, c2, 0}
 template <int NC>
-__device__ __forceinline__ void stage_coef(const TParams& p, int b, float* s_coef) {
-  for (int i = threadIdx.x; i < 9 * NC; i += blockDim.x) {
-    const int s = i / (3 * NC), j = i - s * 3 * NC;
-    s_coef[i] = p.coef[s][(size_t)b * 3 * NC + j];
+__device__ __forceinline__ void stage_coef(const TParams& p, int b, Coef4* s_coef) {
+  for (int i = threadIdx.x; i < 3 * NC * 4; i += blockDim.x) {
+    const int s = i / (4 * NC), r = i - s * 4 * NC, k = r >> 2, c = r & 3;
+    s_coef[s * NC + k].v[c] = c < 3 ? p.coef[s][((size_t)b * 3 + c) * NC + k] : 0.0f;
   }
   __syncthreads();
 }
@@ -62,7 +63,7 @@ __device__ __forceinline__ void coords(int idx, int W, float fW, float fH, float
 template <int NV, int VEC>
 __global__ void __launch_bounds__(THREADS, 2) trispace_fwd_kernel(const TParams p) {
   constexpr int NC = poly_num_coeffs(NV, DEG);
-  __shared__ float s_coef[9 * NC];
+  __shared__ Coef4 s_coef[3 * NC];
   const int b = blockIdx.y;
   stage_coef<NC>(p, b, s_coef);
   const int HW = p.HW;
@@ -98,21 +99,24 @@ __global__ void __launch_bounds__(THREADS, 2) trispace_fwd_kernel(const TParams 
 // ---------------------------------------------------------------------------------------------
 // Backward: coefficient gradients  g[s][c][k] = sum_px gp_s_c(px) * monomial_s_k(px), per image a
 // [3 x N] . [N x NC] product for each of the three spaces.  Tiles of 128 pixels:
-//   phase A (thread = pixel):   recompute the forward, get gp (trispace_gpoly), write the tile's
-//            monomials to shared memory T[k][px] (conflict-free: consecutive threads, consecutive px)
-//            and gp to G[px];
-//   phase B (thread = monomial k): acc[c] += G[px][c] * T[k][px] over the tile's pixels (row pitch
-//            132 words: a quarter-warp's 128-bit loads fall in 32 distinct banks).
+//   phase A (thread = packed pixel pair, first half of the block): recompute the forward, get gp
+//            (trispace_gpoly), write the tile's monomials to shared memory T[k][px] (64-bit stores,
+//            consecutive threads -> consecutive pairs: conflict-free) and gp to G[c][px];
+//   phase B (thread = monomial k): acc[c] += G[c][px] * T[k][px] over the tile's pixels, two pixels
+//            per FFMA2 (row pitch 132 words: a quarter-warp's 128-bit loads fall in 32 distinct banks).
 // Nine accumulators per thread live across the whole image share; at the end one partial row per
 // block goes to global memory, one atomic ticket per block, and the last block of the image folds
 // the rows in a fixed order in double (bitwise deterministic, no float atomics).
 // ---------------------------------------------------------------------------------------------
-constexpr int BT = 128;              // threads per block = pixels per tile
+#ifndef TRI_BT
+#define TRI_BT 128
+#endif
+constexpr int BT = TRI_BT;           // threads per block = pixels per tile
 constexpr int T_PITCH = BT + 4;
 
 template <int NV>
 constexpr size_t bwd_smem_bytes() {
-  return ((size_t)9 * poly_num_coeffs(NV, DEG) + (size_t)poly_num_coeffs(NV, DEG) * T_PITCH + (size_t)BT * 4) * sizeof(float);
+  return ((size_t)12 * poly_num_coeffs(NV, DEG) + (size_t)poly_num_coeffs(NV, DEG) * T_PITCH + (size_t)BT * 4) * sizeof(float);
 }
 
 #ifndef TRI_BWD_MIN_BLOCKS
@@ -125,7 +129,7 @@ __global__ void __launch_bounds__(BT, TRI_BWD_MIN_BLOCKS) trispace_bwd_kernel(co
   extern __shared__ __align__(16) float smem[];
   float* s_G = smem;                        // [3][BT] + pad (16-byte aligned)
   float* s_T = smem + BT * 4;               // [NC][T_PITCH]
-  float* s_coef = s_T + NC * T_PITCH;       // [9 * NC]
+  Coef4* s_coef = reinterpret_cast<Coef4*>(s_T + NC * T_PITCH);   // [3 * NC] records (16-byte aligned: T_PITCH % 4 == 0)
   __shared__ unsigned s_ticket;
   const int b = blockIdx.y;
   const int t = threadIdx.x;
@@ -135,55 +139,82 @@ __global__ void __launch_bounds__(BT, TRI_BWD_MIN_BLOCKS) trispace_bwd_kernel(co
   const float* go = p.gout + (size_t)b * 3 * HW;
   const float fW = (float)p.W, fH = (float)p.H;
   const bool clamp = p.clamp != 0;
-  float acc[3][3];
+  // accumulators: [space][channel], packed over (even pixel, odd pixel) of the tile
+  constexpr int J = (NC + BT - 1) / BT;           // monomials per thread in phase B
+  F2 acc[3][J][3];
 #pragma unroll
-  for (int sp = 0; sp < 3; ++sp) acc[sp][0] = acc[sp][1] = acc[sp][2] = 0.0f;
+  for (int sp = 0; sp < 3; ++sp)
+#pragma unroll
+    for (int j = 0; j < J; ++j) acc[sp][j][0] = acc[sp][j][1] = acc[sp][j][2] = F2(0.0f);
   const int n_tiles = (HW + BT - 1) / BT;
   for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    const int i = tile * BT + t;
-    const bool valid = i < HW;
-    float x[3], g[3], xs = 0.f, ys = 0.f;
+    // phase A runs on the first BT/2 threads, one packed pixel pair each (half the warp
+    // instructions of a scalar pass over BT threads); the other warps wait at the barrier while
+    // the SM's other resident blocks use the pipes.
+    F2 vars[3][3], gp[3][3], xs2 = F2(0.0f), ys2 = F2(0.0f);
+    if (t < BT / 2) {
+      const int i = tile * BT + 2 * t;
+      const bool v0 = i < HW, v1 = i + 1 < HW;
+      F2 x[3], g[3];
 #pragma unroll
-    for (int c = 0; c < 3; ++c) {
-      x[c] = valid ? __ldcs(in + (size_t)c * HW + i) : 0.5f;
-      g[c] = valid ? __ldcs(go + (size_t)c * HW + i) : 0.0f;
+      for (int c = 0; c < 3; ++c) {
+        const float a0 = v0 ? __ldcs(in + (size_t)c * HW + i) : 0.5f, a1 = v1 ? __ldcs(in + (size_t)c * HW + i + 1) : 0.5f;
+        const float g0 = v0 ? __ldcs(go + (size_t)c * HW + i) : 0.0f, g1 = v1 ? __ldcs(go + (size_t)c * HW + i + 1) : 0.0f;
+        x[c] = F2(a0, a1); g[c] = F2(g0, g1);
+      }
+      if (NV == 5) {
+        float xa, ya, xb, yb;
+        coords(v0 ? i : 0, p.W, fW, fH, &xa, &ya);
+        coords(v1 ? i + 1 : 0, p.W, fW, fH, &xb, &yb);
+        xs2 = F2(xa, xb); ys2 = F2(ya, yb);
+      }
+      trispace_gpoly<F2, NV, DEG>(x, xs2, ys2, s_coef, clamp, g, vars, gp);
     }
-    if (NV == 5) coords(valid ? i : 0, p.W, fW, fH, &xs, &ys);
-    float vars[3][3], gp[3][3];
-    trispace_gpoly<float, NV, DEG>(x, xs, ys, s_coef, clamp, g, vars, gp);
 #pragma unroll
     for (int sp = 0; sp < 3; ++sp) {
       __syncthreads();                               // phase B of the previous space is done with T, G
-      const float v[5] = {vars[sp][0], vars[sp][1], vars[sp][2], xs, ys};
-      s_T[t] = 1.0f;                                 // the constant term
-      MonoStore<float> st{s_T + t, T_PITCH};
-      mono_visit<float, NV, DEG>(v, st);
-      s_G[t] = gp[sp][0]; s_G[BT + t] = gp[sp][1]; s_G[2 * BT + t] = gp[sp][2];
+      if (t < BT / 2) {
+        const F2 v[5] = {vars[sp][0], vars[sp][1], vars[sp][2], xs2, ys2};
+        F2* col = reinterpret_cast<F2*>(s_T + 2 * t);
+        col[0] = F2(1.0f);                           // the constant term
+        MonoStore<F2> st{col, T_PITCH / 2};
+        mono_visit<F2, NV, DEG>(v, st);
+#pragma unroll
+        for (int c = 0; c < 3; ++c) reinterpret_cast<F2*>(s_G + c * BT)[t] = gp[sp][c];
+      }
       __syncthreads();
       if (t < NC) {
-        const float4* row = reinterpret_cast<const float4*>(s_T + t * T_PITCH);
-        float a0 = acc[sp][0], a1 = acc[sp][1], a2 = acc[sp][2];
-#pragma unroll 4
+#pragma unroll 2
         for (int q = 0; q < BT / 4; ++q) {
-          const float4 m = row[q];
           const float4 g0 = reinterpret_cast<const float4*>(s_G)[q];                  // channel 0, four pixels
           const float4 g1 = reinterpret_cast<const float4*>(s_G + BT)[q];
           const float4 g2 = reinterpret_cast<const float4*>(s_G + 2 * BT)[q];
-          a0 = fmaf(g0.x, m.x, a0); a1 = fmaf(g1.x, m.x, a1); a2 = fmaf(g2.x, m.x, a2);
-          a0 = fmaf(g0.y, m.y, a0); a1 = fmaf(g1.y, m.y, a1); a2 = fmaf(g2.y, m.y, a2);
-          a0 = fmaf(g0.z, m.z, a0); a1 = fmaf(g1.z, m.z, a1); a2 = fmaf(g2.z, m.z, a2);
-          a0 = fmaf(g0.w, m.w, a0); a1 = fmaf(g1.w, m.w, a1); a2 = fmaf(g2.w, m.w, a2);
+#pragma unroll
+          for (int j = 0; j < J; ++j) {
+            const int k = t + j * BT < NC ? t + j * BT : t;       // surplus slots redo row t; never stored
+            const float4 m = reinterpret_cast<const float4*>(s_T + k * T_PITCH)[q];
+            const F2 mlo(m.x, m.y), mhi(m.z, m.w);
+            acc[sp][j][0] = vfma(F2(g0.x, g0.y), mlo, acc[sp][j][0]);
+            acc[sp][j][1] = vfma(F2(g1.x, g1.y), mlo, acc[sp][j][1]);
+            acc[sp][j][2] = vfma(F2(g2.x, g2.y), mlo, acc[sp][j][2]);
+            acc[sp][j][0] = vfma(F2(g0.z, g0.w), mhi, acc[sp][j][0]);
+            acc[sp][j][1] = vfma(F2(g1.z, g1.w), mhi, acc[sp][j][1]);
+            acc[sp][j][2] = vfma(F2(g2.z, g2.w), mhi, acc[sp][j][2]);
+          }
         }
-        acc[sp][0] = a0; acc[sp][1] = a1; acc[sp][2] = a2;
       }
     }
   }
   float* row = p.partials + ((size_t)b * gridDim.x + blockIdx.x) * NG;
-  if (t < NC) {
 #pragma unroll
-    for (int sp = 0; sp < 3; ++sp)
+  for (int j = 0; j < J; ++j) {
+    const int k = t + j * BT;
+    if (k < NC) {
 #pragma unroll
-      for (int c = 0; c < 3; ++c) row[(sp * 3 + c) * NC + t] = acc[sp][c];
+      for (int sp = 0; sp < 3; ++sp)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) row[(sp * 3 + c) * NC + k] = vhsum(acc[sp][j][c]);
+    }
   }
   __threadfence();
   __syncthreads();

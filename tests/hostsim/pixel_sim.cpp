@@ -175,11 +175,16 @@ static void sim_trispace_nv(int do_bwd, const float* img, const float* R, const 
                             const float* gout, float* out, float* gR, float* gL, float* gH, int B, int H, int W) {
   constexpr int NC = poly_num_coeffs(NV, 4);
   const int HW = H * W;
-  std::vector<float> coef(9 * NC), terms(NC);
+  std::vector<Coef4> coef(3 * NC);
+  std::vector<float> terms(NC);
   std::vector<double> acc(9 * NC);
   for (int b = 0; b < B; ++b) {
     const float* src[3] = {R, L, Hc};
-    for (int s = 0; s < 3; ++s) memcpy(&coef[s * 3 * NC], src[s] + (size_t)b * 3 * NC, sizeof(float) * 3 * NC);
+    for (int s = 0; s < 3; ++s)
+      for (int k = 0; k < NC; ++k) {
+        for (int c = 0; c < 3; ++c) coef[s * NC + k].v[c] = src[s][((size_t)b * 3 + c) * NC + k];
+        coef[s * NC + k].v[3] = 0.f;
+      }
     std::fill(acc.begin(), acc.end(), 0.0);
     for (int i = 0; i < HW; ++i) {
       const float x[3] = {img[((size_t)b * 3 + 0) * HW + i], img[((size_t)b * 3 + 1) * HW + i], img[((size_t)b * 3 + 2) * HW + i]};
