@@ -9,7 +9,7 @@ Mirrors the reference's module API for this path:
 All of them run hand-written CUDA kernels through the C ABI in include/curl_b200.h; there is no
 CPU or PyTorch fallback.
 """
-from . import colors, curves, model  # noqa: F401
-from .model import CURLLayer, GCURLNet, ChannelPolyLayer, TriSpaceRegNet  # noqa: F401
+from . import colors, curves, metric, model  # noqa: F401
+from .model import CURLLayer, CURLLoss, GCURLNet, ChannelPolyLayer, TriSpaceRegNet  # noqa: F401
 
-__all__ = ["colors", "curves", "model", "CURLLayer", "GCURLNet", "ChannelPolyLayer", "TriSpaceRegNet"]
+__all__ = ["colors", "curves", "metric", "model", "CURLLayer", "CURLLoss", "GCURLNet", "ChannelPolyLayer", "TriSpaceRegNet"]

@@ -366,3 +366,59 @@ class TriSpaceFn(torch.autograd.Function):
         _lib.check(rc, "curl_trispace_bwd_f32")
         _lib.count_launch(2)
         return None, gR, gL, gH, None, None, None
+
+
+class LossTermsFn(torch.autograd.Function):
+    """Colour terms of CURLLoss in one pass (reference model.py:89-108): returns
+    (sums[B, 5], L_pred[B, 1, H, W], L_target[B, 1, H, W]) -- see include/curl_b200.h for the five
+    sums.  Differentiable w.r.t. pred only (the target is data; its L plane carries no gradient)."""
+
+    @staticmethod
+    def forward(ctx, pred, target, mask):
+        lib = _lib.load()
+        pred = _image(pred, "predicted_img_batch")
+        target = _image(target, "target_img_batch")
+        if target.shape != pred.shape or target.device != pred.device:
+            raise ValueError("curl_b200: predicted and target batches differ: %s on %s vs %s on %s"
+                             % (tuple(pred.shape), pred.device, tuple(target.shape), target.device))
+        m, kind = _mask(mask, pred)
+        dev = pred.device
+        B, _, h, w = pred.shape
+        sums = torch.empty(B, 5, dtype=torch.float32, device=dev)
+        L_pred = torch.empty(B, 1, h, w, dtype=torch.float32, device=dev)
+        L_target = torch.empty(B, 1, h, w, dtype=torch.float32, device=dev)
+        n = lib.curl_loss_terms_workspace_bytes(B, h, w)
+        ws = torch.empty(n, dtype=torch.uint8, device=dev)
+        with torch.cuda.device(dev):
+            rc = lib.curl_loss_terms_fwd_f32(_ptr(pred), _ptr(target), _ptr(m), kind, _ptr(sums), _ptr(L_pred),
+                                             _ptr(L_target), _ptr(ws), n, B, h, w, _stream(dev))
+        _lib.check(rc, "curl_loss_terms_fwd_f32")
+        _lib.count_launch()
+        ctx.save_for_backward(pred, target, m)
+        ctx.kind = kind
+        ctx.mark_non_differentiable(L_target)
+        return sums, L_pred, L_target
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, gsums, gL_pred, _gL_target):
+        if ctx.needs_input_grad[1]:
+            raise RuntimeError("curl_b200: the loss terms have no gradient w.r.t. the target batch; detach it")
+        lib = _lib.load()
+        pred, target, m = ctx.saved_tensors
+        dev = pred.device
+        B, _, h, w = pred.shape
+        wts = gsums[:, :4].to(torch.float32).contiguous()
+        gL = None if gL_pred is None else gL_pred.to(torch.float32).contiguous()
+        gpred = torch.empty_like(pred)
+        with torch.cuda.device(dev):
+            rc = lib.curl_loss_terms_bwd_f32(_ptr(pred), _ptr(target), _ptr(m), ctx.kind, _ptr(wts), _ptr(gL),
+                                             _ptr(gpred), B, h, w, _stream(dev))
+        _lib.check(rc, "curl_loss_terms_bwd_f32")
+        _lib.count_launch()
+        return gpred, None, None
+
+
+def loss_terms(pred, target, mask):
+    """(sums[B, 5], L_pred, L_target) of the fused CURLLoss colour terms; see LossTermsFn."""
+    return LossTermsFn.apply(pred, target, mask)

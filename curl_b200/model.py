@@ -209,3 +209,60 @@ class TriSpaceRegNet(nn.Module):
         input_img = img if target_img is None else target_img
         # training: residual and generate_image in the same kernel; inference: the residual itself
         return self._fused(input_img, R, L, H, bool(self.is_train))
+
+
+class CURLLoss(nn.Module):
+    """Reference model.py:36-118, same constructor, attributes, state-dict keys and value:
+        (L1_rgb + cosine_rgb + L1_lab + L1_hsv_cone + 10 * (1 - MS-SSIM(L))) / 5, masked.
+    The colour terms -- masking, both RGB2LAB and both RGB2HSV conversions, the cone, the three L1
+    sums and the cosine similarity -- are ONE kernel pass over (pred, target, mask) producing five
+    sums per image and the two L planes; MS-SSIM of the L planes stays on the library convolution
+    (metric.MSSSIMMetric).  The scalar arithmetic that combines the sums runs on the device (no
+    host synchronisation), and autograd carries it back into the fused backward kernel."""
+
+    def __init__(self, ssim_window_size=5, num_channel=1):
+        super().__init__()
+        from . import metric
+        self.ssim_window_size = ssim_window_size
+        self.num_channel = num_channel
+        self.msssim_layer = metric.MSSSIMMetric(num_channel=num_channel)
+        self.rgb2lab = colors.RGB2LAB()
+        self.rgb2hsv = colors.RGB2HSV()
+
+    def batch_lab_convert(self, img_batch):
+        return torch.clamp(self.rgb2lab(img_batch), 0.0, 1.0)                       # model.py:55-58
+
+    @staticmethod
+    def batch_L_ssim_convert(lab_img_batch):
+        return lab_img_batch[:, 0, :, :].unsqueeze(1)                               # model.py:60-62
+
+    def batch_hsv_convert(self, img_batch):
+        import math
+        hsv = torch.clamp(self.rgb2hsv(img_batch), 0.0, 1.0)                        # model.py:64-79
+        hue, sat, val = 2 * math.pi * hsv[:, 0], hsv[:, 1], hsv[:, 2]
+        return torch.stack((val * sat * torch.cos(hue), val * sat * torch.sin(hue), val), 1)
+
+    def terms(self, predicted_img_batch, target_img_batch, mask):
+        """The five terms of model.py:91-108 as a dict of 0-d tensors (rgb, cosine, lab, hsv, ssim)."""
+        from .functional import loss_terms
+        for m in (self.rgb2lab, self.rgb2hsv):
+            m._check_constants()
+        sums, L_pred, L_target = loss_terms(predicted_img_batch, target_img_batch, mask)
+        B, C, H, W = predicted_img_batch.shape
+        tot = sums.sum(dim=0)
+        n_px = float(B * H * W)
+        if mask is None:
+            n_masked = 0.0
+        elif mask.dtype in (torch.bool, torch.uint8):
+            n_masked = n_px - tot[4]
+        else:
+            n_masked = torch.logical_not(mask).expand(B, 1, H, W).sum()
+        unmasked = C * tot[4]                                                       # model.py:90
+        ssim = (1.0 - self.msssim_layer(L_pred, L_target)).mean()                   # model.py:104
+        return {"rgb": tot[0] / unmasked,
+                "cosine": 1.0 - (tot[1] + n_masked) / n_px,                         # model.py:95-96
+                "lab": tot[2] / unmasked, "hsv": tot[3] / unmasked, "ssim": ssim}
+
+    def forward(self, predicted_img_batch, target_img_batch, mask):
+        t = self.terms(predicted_img_batch, target_img_batch, mask)
+        return (t["rgb"] + t["cosine"] + t["lab"] + t["hsv"] + 10 * t["ssim"]) / 5  # model.py:110-116

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define CURL_ABI_VERSION 3
+#define CURL_ABI_VERSION 4
 
 /* error codes */
 #define CURL_OK 0
@@ -173,6 +173,37 @@ int curl_trispace_bwd_f32(const float* img, const float* R, const float* L, cons
                           int degree, int spatial, int final_clamp, const float* gout,
                           float* gR, float* gL, float* gH, void* workspace, size_t workspace_bytes,
                           int B, int H, int W, void* stream);
+
+/*
+ * Colour terms of CURLLoss (model.py:36-118): everything in that loss except MS-SSIM.
+ *
+ * curl_loss_terms_fwd_f32 replaces, in ONE pass over (pred, target, mask), model.py:89 (masking),
+ * :91 (L1 in RGB), :95 (cosine_similarity over channels), :57-58 + :98-100 (clamped RGB2LAB of both
+ * images and their L1), :66-79 + :106-108 (HSV cone of both images and their L1) and :102-103 (the
+ * two Lab L planes MS-SSIM consumes).  Per image b it writes sums[b][0..4]:
+ *   [0] sum |p - t|   [1] sum cos_sim(p, t)   [2] sum |lab(p) - lab(t)|   [3] sum |cone(p) - cone(t)|
+ *   [4] sum mask                                     (p = pred * mask, t = target * mask)
+ * from which the caller forms model.py:90-117:
+ *   n = 3 * sum_b s4;  rgb = sum_b s0 / n;  lab = sum_b s2 / n;  hsv = sum_b s3 / n;
+ *   cosine = 1 - (sum_b s1 + (B*H*W - sum_b s4)) / (B*H*W)      (mask is 0/1; model.py:96 broadcasts
+ *   [B,H,W] + [B,1,H,W] to [B,B,H,W], whose mean is mean(cos) + mean(!mask));
+ *   loss = (rgb + cosine + lab + hsv + 10 * (1 - msssim(L_pred, L_target)).mean()) / 5.
+ * L_pred / L_target: [B][H][W] or NULL.  Deterministic: one partial row per block, an atomic ticket
+ * per block, fixed-order fold in double by each image's last block.
+ */
+size_t curl_loss_terms_workspace_bytes(int B, int H, int W);
+int curl_loss_terms_fwd_f32(const float* pred, const float* target, const void* mask, int mask_kind,
+                            float* sums /*[B][5]*/, float* L_pred, float* L_target,
+                            void* workspace, size_t workspace_bytes, int B, int H, int W, void* stream);
+/*
+ * Backward w.r.t. pred (the target is data).  w: DEVICE pointer to [B][4] = d loss / d sums[b][0..3]
+ * (they depend on sum mask, which lives on the device; no host round trip); gL_pred: [B][H][W]
+ * gradient arriving at L_pred from MS-SSIM, or NULL.  Recomputes the conversions per pixel;
+ * replaces torch.autograd over model.py:89-108.
+ */
+int curl_loss_terms_bwd_f32(const float* pred, const float* target, const void* mask, int mask_kind,
+                            const float* w, const float* gL_pred, float* gpred,
+                            int B, int H, int W, void* stream);
 
 #ifdef __cplusplus
 }

@@ -340,3 +340,111 @@ def trispace_fwd_bwd(img, R, L, H, gout, degree=4, spatial=False, final_clamp=Tr
         out = trispace_image(img, out)
     gR, gL, gH = torch.autograd.grad((out * gout).sum(), (R, L, H))
     return {"out": out.detach(), "gR": gR, "gL": gL, "gH": gH}
+
+
+# ---------------------------------------------------------------------------------------------
+# CURLLoss (model.py:36-118) and the MS-SSIM it calls (metric.py:75-214).
+# ---------------------------------------------------------------------------------------------
+import math
+
+MSSSIM_WEIGHTS = (0.0448, 0.2856, 0.3001, 0.2363, 0.1333)                                      # metric.py:78
+
+
+def ssim_window(window_size=11, sigma=1.5, dtype=torch.float32, device=None):
+    """MSSSIMMetric.gaussian / create_window (metric.py:88-117): fp32 weights, outer product."""
+    g = torch.tensor([math.exp(-(x - window_size // 2) ** 2 / float(2 * sigma ** 2)) for x in range(window_size)],
+                     dtype=torch.float32, device=device)
+    g = (g / g.sum()).unsqueeze(1)
+    return g.mm(g.t()).float().unsqueeze(0).unsqueeze(0).to(dtype)
+
+
+def ssim(img1, img2, window):
+    """MSSSIMMetric.compute_ssim (metric.py:119-160), one channel."""
+    F = torch.nn.functional
+    pad = window.shape[-1] // 2
+    mu1 = F.conv2d(img1, window, padding=pad, groups=1)
+    mu2 = F.conv2d(img2, window, padding=pad, groups=1)
+    mu1_sq = mu1.pow(2)
+    mu2_sq = mu2.pow(2)
+    mu1_mu2 = mu1 * mu2
+    sigma1_sq = F.conv2d(img1 * img1, window, padding=pad, groups=1) - mu1_sq
+    sigma2_sq = F.conv2d(img2 * img2, window, padding=pad, groups=1) - mu2_sq
+    sigma12 = F.conv2d(img1 * img2, window, padding=pad, groups=1) - mu1_mu2
+    C1 = 0.01 ** 2
+    C2 = 0.03 ** 2
+    ssim_map1 = ((2 * mu1_mu2 + C1) * (2 * sigma12 + C2))
+    ssim_map2 = ((mu1_sq + mu2_sq + C1) * (sigma1_sq + sigma2_sq + C2))
+    ssim_map = ssim_map1 / ssim_map2
+    v1 = 2.0 * sigma12 + C2
+    v2 = sigma1_sq + sigma2_sq + C2
+    cs = torch.mean(v1 / v2, dim=(1, 2, 3))
+    return ssim_map.mean(dim=(1, 2, 3)), cs
+
+
+def msssim(img1, img2):
+    """MSSSIMMetric.compute_msssim (metric.py:162-211) for [B,1,H,W] inputs."""
+    F = torch.nn.functional
+    window = ssim_window(dtype=img1.dtype, device=img1.device)
+    weights = torch.tensor(MSSSIM_WEIGHTS, dtype=torch.float32, device=img1.device).to(img1.dtype)
+    ssims, mcs = [], []
+    for _ in range(len(MSSSIM_WEIGHTS)):
+        s, cs = ssim(img1, img2, window)
+        ssims.append(s)
+        mcs.append(cs)
+        img1 = F.avg_pool2d(img1, (2, 2))
+        img2 = F.avg_pool2d(img2, (2, 2))
+    ssims = (torch.stack(ssims, dim=1) + 1) / 2
+    mcs = (torch.stack(mcs, dim=1) + 1) / 2
+    pow1 = mcs ** weights.reshape(1, -1)
+    pow2 = ssims ** weights.reshape(1, -1)
+    return torch.prod(pow1[:, :-1] * pow2[:, -1].reshape(-1, 1), dim=1)
+
+
+def loss_lab(img):
+    """CURLLoss.batch_lab_convert (model.py:55-58)."""
+    return torch.clamp(rgb2lab(img), 0.0, 1.0)
+
+
+def loss_hsv_cone(img):
+    """CURLLoss.batch_hsv_convert (model.py:64-79)."""
+    hsv = torch.clamp(rgb2hsv(img), 0.0, 1.0)
+    hue = 2 * math.pi * hsv[:, 0, :, :]
+    val = hsv[:, 2, :, :]
+    sat = hsv[:, 1, :, :]
+    c1 = val * sat * torch.cos(hue)
+    c2 = val * sat * torch.sin(hue)
+    return torch.stack((c1, c2, val), 1)
+
+
+def curl_loss_parts(pred, target, mask):
+    """CURLLoss.forward (model.py:81-118), returning every term and the L planes."""
+    F = torch.nn.functional
+    unmasked = pred.shape[1] * mask.sum()                                                      # model.py:90
+    pred, target = pred * mask, target * mask
+    rgb = F.l1_loss(pred, target, reduction='sum') / unmasked
+    base_cos_sim = F.cosine_similarity(pred, target, dim=1)
+    # model.py:96: [B,H,W] + [B,1,H,W] broadcasts to [B,B,H,W]; kept as the reference has it
+    cosine = (1.0 - (base_cos_sim + torch.logical_not(mask)).mean(dim=(1, 2))).mean()
+    target_lab = loss_lab(target)
+    pred_lab = loss_lab(pred)
+    lab = F.l1_loss(pred_lab, target_lab, reduction='sum') / unmasked
+    L_target = target_lab[:, 0, :, :].unsqueeze(1)
+    L_pred = pred_lab[:, 0, :, :].unsqueeze(1)
+    ssim_term = (1.0 - msssim(L_pred, L_target)).mean()
+    hsv = F.l1_loss(loss_hsv_cone(pred), loss_hsv_cone(target), reduction='sum') / unmasked
+    total = (rgb + cosine + lab + hsv + 10 * ssim_term) / 5
+    return {"loss": total, "rgb": rgb, "cosine": cosine, "lab": lab, "hsv": hsv, "ssim": ssim_term,
+            "L_pred": L_pred, "L_target": L_target}
+
+
+def curl_loss(pred, target, mask):
+    return curl_loss_parts(pred, target, mask)["loss"]
+
+
+def curl_loss_fwd_bwd(pred, target, mask):
+    pred = pred.detach().clone().requires_grad_(True)
+    parts = curl_loss_parts(pred, target, mask)
+    (gpred,) = torch.autograd.grad(parts["loss"], (pred,))
+    out = {k: v.detach() for k, v in parts.items()}
+    out["gpred"] = gpred
+    return out

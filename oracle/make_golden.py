@@ -144,7 +144,8 @@ def main():
                 blob[f"{cname}.{aname}.{tag}.gP"] = gP.numpy()
     np.savez_compressed(os.path.join(GOLDEN_DIR, "stages.npz"), **blob)
     trispace_golden()
-    for f in ("layer.npz", "stages.npz", "trispace.npz"):
+    loss_golden()
+    for f in ("layer.npz", "stages.npz", "trispace.npz", "loss.npz"):
         print(f, os.path.getsize(os.path.join(GOLDEN_DIR, f)), "bytes")
 
 
@@ -191,5 +192,44 @@ def trispace_golden():
     np.savez_compressed(os.path.join(GOLDEN_DIR, "trispace.npz"), **blob)
 
 
+LOSS_CASES = ["near", "random", "uint8", "odd", "allmasked_image", "floatmask"]
+
+
+def loss_golden():
+    """tests/golden/loss.npz: the reference's CURLLoss.forward (model.py:81-118, with the reference's
+    MSSSIMMetric inside) executed through oracle/ref_loader.load_loss, fp32 and fp64, with the
+    gradient w.r.t. the predicted batch by autograd."""
+    g = torch.Generator().manual_seed(20261106)
+    blob = {}
+    for case in LOSS_CASES:
+        B, H, W = (1, 37, 53) if case == "odd" else (2, 32, 36)
+        target = torch.rand(B, 3, H, W, generator=g)
+        if case == "random":
+            pred = torch.rand(B, 3, H, W, generator=g)
+        else:
+            pred = (target + 0.05 * torch.randn(B, 3, H, W, generator=g)).clamp(0.0, 1.0)
+        if case == "uint8":                      # quantised: exact ties pred == target (sign(0) = 0), black pixels
+            pred, target = (pred * 255).round() / 255, (target * 255).round() / 255
+            pred[:, :, :2] = 0.0
+            target[:, :, 1:3] = 0.0
+        mask = torch.rand(B, 1, H, W, generator=g) > 0.15
+        if case == "allmasked_image":
+            mask[1] = False                      # one image contributes nothing
+        if case == "floatmask":
+            mask = mask.to(torch.float32)
+        blob.update({f"{case}.pred": pred.numpy(), f"{case}.target": target.numpy(), f"{case}.mask": mask.numpy()})
+        for tag, dtype in (("f32", torch.float32), ("f64", torch.float64)):
+            crit = ref_loader.load_loss().to(dtype)
+            p = pred.to(dtype).clone().requires_grad_(True)
+            loss = crit(p, target.to(dtype), mask)
+            (gp,) = torch.autograd.grad(loss, p)
+            blob[f"{case}.{tag}.loss"] = loss.detach().numpy()
+            blob[f"{case}.{tag}.gpred"] = gp.numpy()
+    np.savez_compressed(os.path.join(GOLDEN_DIR, "loss.npz"), **blob)
+
+
 if __name__ == "__main__":
-    main()
+    if "--loss-only" in sys.argv:
+        loss_golden()
+    else:
+        main()

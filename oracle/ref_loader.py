@@ -108,3 +108,37 @@ def load_trispace(degree=4, spatial=False, mobile=False):
     net.x = torch.nn.Parameter(x, requires_grad=False)
     net.y = torch.nn.Parameter(y, requires_grad=False)
     return ns["ChannelPolyLayer"], net
+
+
+def load_loss():
+    """Returns a reference CURLLoss instance (model.py:36-118) with the reference's own MSSSIMMetric
+    (metric.py:75-214) inside.  Both classes are the reference's source, extracted with ast; one
+    patch: metric.py hard-codes `.cuda()` on intermediates (metric.py:116,150-157), which cannot run
+    in this GPU-less container, so every `.cuda()` is dropped (a no-op for CPU tensors)."""
+    import math
+    import torch
+    import torch.nn as nn
+    import torch.nn.functional as F
+    from torch.autograd import Variable
+
+    colors, _, _ = load()
+    with open(os.path.join(REFERENCE_ROOT, "metric.py")) as f:
+        src = f.read()
+    tree = ast.parse(src)
+    cls = [n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == "MSSSIMMetric"]
+    assert len(cls) == 1
+    csrc = "\n".join(src.splitlines()[cls[0].lineno - 1: cls[0].end_lineno])
+    assert csrc.count(".cuda()") == 10, "reference metric.py changed; re-derive the patch"
+    metric = types.ModuleType("_ref_metric")
+    metric.__dict__.update({"torch": torch, "nn": nn, "F": F, "Variable": Variable, "exp": math.exp})
+    exec(compile(csrc.replace(".cuda()", ""), os.path.join(REFERENCE_ROOT, "metric.py"), "exec"), metric.__dict__)
+
+    with open(os.path.join(REFERENCE_ROOT, "model.py")) as f:
+        msrc = f.read()
+    tree = ast.parse(msrc)
+    cls = [n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == "CURLLoss"]
+    assert len(cls) == 1
+    lsrc = "\n".join(msrc.splitlines()[cls[0].lineno - 1: cls[0].end_lineno])
+    ns = {"torch": torch, "nn": nn, "F": F, "math": math, "colors": colors, "metric": metric}
+    exec(compile(lsrc, os.path.join(REFERENCE_ROOT, "model.py"), "exec"), ns)
+    return ns["CURLLoss"]()

@@ -13,6 +13,7 @@ GOLDEN = os.path.join(ROOT, "tests", "golden")
 LAYER_CASES = ["smooth", "uint8", "edges", "identity", "strong", "widek", "floatmask"]
 STAGE_CASES = ["wide", "edges", "unit"]
 TRISPACE_CASES = ["rgb", "spatial", "spatial_mobile", "uint8", "edges"]
+LOSS_CASES = ["near", "random", "uint8", "odd", "allmasked_image", "floatmask"]
 
 
 def pytest_configure(config):
@@ -32,6 +33,11 @@ def stage_golden():
 @pytest.fixture(scope="session")
 def trispace_golden():
     return np.load(os.path.join(GOLDEN, "trispace.npz"))
+
+
+@pytest.fixture(scope="session")
+def loss_golden():
+    return np.load(os.path.join(GOLDEN, "loss.npz"))
 
 
 def rel_to_max(a, ref):

@@ -11,6 +11,7 @@ SRC = os.path.join(HERE, "pixel_sim.cpp")
 HDR = os.path.join(HERE, "..", "..", "curl_b200", "csrc", "curl_pixel.cuh")
 HDR2 = os.path.join(HERE, "..", "..", "curl_b200", "csrc", "curl_vec.cuh")
 HDR3 = os.path.join(HERE, "..", "..", "curl_b200", "csrc", "curl_poly.cuh")
+HDR4 = os.path.join(HERE, "..", "..", "curl_b200", "csrc", "curl_loss.cuh")
 OUT = os.path.join(HERE, "_build", "libpixel_sim.so")
 
 _lib = None
@@ -20,7 +21,7 @@ def lib():
     global _lib
     if _lib is not None:
         return _lib
-    newest = max(os.path.getmtime(SRC), os.path.getmtime(HDR), os.path.getmtime(HDR2), os.path.getmtime(HDR3))
+    newest = max(os.path.getmtime(SRC), os.path.getmtime(HDR), os.path.getmtime(HDR2), os.path.getmtime(HDR3), os.path.getmtime(HDR4))
     if not os.path.exists(OUT) or os.path.getmtime(OUT) < newest:
         os.makedirs(os.path.dirname(OUT), exist_ok=True)
         subprocess.check_call(["g++", "-O2", "-std=c++17", "-shared", "-fPIC", "-o", OUT, SRC])
@@ -120,3 +121,21 @@ def trispace(img, R, L, Hc, spatial, clamp, gout=None):
     rc = lib().sim_trispace(1, _f(img), _f(R), _f(L), _f(Hc), int(spatial), int(clamp), _f(gout), None, _f(gR), _f(gL), _f(gH), B, h, w)
     assert rc == 0
     return dict(gR=gR, gL=gL, gH=gH)
+
+
+def loss_terms(pred, target, mask, w=None, gL=None):
+    """Returns dict(sums[B,5], L_pred, L_target) or, when w[B,4] is given, gpred[B,3,H,W]."""
+    pred = _c(pred); target = _c(target)
+    B, _, h, wd = pred.shape
+    m = None if mask is None else _c(np.broadcast_to(np.asarray(mask, dtype=np.float32), (B, 1, h, wd)))
+    if w is None:
+        sums = np.empty((B, 5), np.float32)
+        Lp = np.empty((B, 1, h, wd), np.float32); Lt = np.empty((B, 1, h, wd), np.float32)
+        rc = lib().sim_loss_terms(0, _f(pred), _f(target), _f(m), _f(sums), _f(Lp), _f(Lt), None, None, None, B, h * wd)
+        assert rc == 0
+        return dict(sums=sums, L_pred=Lp, L_target=Lt)
+    w = _c(w); gL = _c(gL)
+    gpred = np.empty_like(pred)
+    rc = lib().sim_loss_terms(1, _f(pred), _f(target), _f(m), None, None, None, _f(w), _f(gL), _f(gpred), B, h * wd)
+    assert rc == 0
+    return gpred

@@ -14,6 +14,7 @@
 
 #include "../../curl_b200/csrc/curl_pixel.cuh"
 #include "../../curl_b200/csrc/curl_poly.cuh"
+#include "../../curl_b200/csrc/curl_loss.cuh"
 
 using namespace curl;
 
@@ -229,6 +230,33 @@ void sim_u8_to_unit_table(float* out) {
 }
 void sim_unit_to_u8(const float* y, unsigned char* out, long long n) {
   for (long long i = 0; i < n; ++i) out[i] = (unsigned char)curl::unit_to_u8(y[i]);
+}
+
+// Colour terms of CURLLoss (curl_loss.cuh), host instantiation.  do_bwd = 0: sums[B][5] (double
+// accumulation) and the two L planes; do_bwd = 1: gpred given w[B][4] and gL (nullable).
+int sim_loss_terms(int do_bwd, const float* pred, const float* target, const float* mask, float* sums, float* L_pred,
+                   float* L_target, const float* w, const float* gL, float* gpred, int B, int HW) {
+  for (int b = 0; b < B; ++b) {
+    double acc[5] = {0, 0, 0, 0, 0};
+    for (int i = 0; i < HW; ++i) {
+      const float x[3] = {pred[((size_t)b * 3 + 0) * HW + i], pred[((size_t)b * 3 + 1) * HW + i], pred[((size_t)b * 3 + 2) * HW + i]};
+      const float y[3] = {target[((size_t)b * 3 + 0) * HW + i], target[((size_t)b * 3 + 1) * HW + i], target[((size_t)b * 3 + 2) * HW + i]};
+      const float m = mask ? mask[(size_t)b * HW + i] : 1.0f;
+      if (!do_bwd) {
+        float s[4], lp, lt;
+        loss_terms_fwd<float>(x, y, m, s, &lp, &lt);
+        for (int k = 0; k < 4; ++k) acc[k] += (double)s[k];
+        acc[4] += (double)m;
+        L_pred[(size_t)b * HW + i] = lp; L_target[(size_t)b * HW + i] = lt;
+      } else {
+        float g[3];
+        loss_terms_bwd<float>(x, y, m, w + b * 4, gL ? gL[(size_t)b * HW + i] : 0.0f, g);
+        for (int c = 0; c < 3; ++c) gpred[((size_t)b * 3 + c) * HW + i] = g[c];
+      }
+    }
+    if (!do_bwd) for (int k = 0; k < 5; ++k) sums[b * 5 + k] = (float)acc[k];
+  }
+  return 0;
 }
 
 }  // extern "C"

@@ -9,7 +9,7 @@ import pytest
 import torch
 
 import parity
-from conftest import LAYER_CASES, STAGE_CASES, ROOT, frac_over, rel_to_max
+from conftest import LAYER_CASES, LOSS_CASES, STAGE_CASES, ROOT, frac_over, rel_to_max
 
 pytestmark = pytest.mark.gpu
 
@@ -500,3 +500,142 @@ def test_trispace_deterministic_and_errors():
     with pytest.raises(RuntimeError, match="bad argument"):
         curl_b200.TriSpaceRegNet(polynomial_order=3, spatial=False, backbone=nn.Identity()).to(dev).generate_residual(
             img, *[c[:, :, :20].contiguous() for c in co])
+
+
+# ---- fused colour terms of CURLLoss (reference model.py:36-118) -------------------------------------
+from oracle import curl_oracle as O  # noqa: E402
+
+def _run_loss(pred, target, mask, dev):
+    import curl_b200
+    crit = curl_b200.CURLLoss().to(dev)
+    p = torch.as_tensor(pred).to(dev).requires_grad_(True)
+    m = None if mask is None else torch.as_tensor(mask).to(dev)
+    loss = crit(p, torch.as_tensor(target).to(dev), m)
+    loss.backward()
+    return float(loss.detach().cpu()), p.grad.cpu().numpy()
+
+
+@pytest.mark.parametrize("case", LOSS_CASES)
+def test_loss_vs_golden(case, loss_golden):
+    """curl_b200.CURLLoss (fused colour-term kernels + library MS-SSIM) against the fixtures generated
+    by the reference's CURLLoss: loss within 1e-5, gradient within 1e-4 of its max-norm (or 3x the
+    reference's own fp32 error)."""
+    g = loss_golden
+    loss, gp = _run_loss(g[f"{case}.pred"], g[f"{case}.target"], g[f"{case}.mask"], _dev())
+    r32, r64 = g[f"{case}.f32.gpred"], g[f"{case}.f64.gpred"]
+    REPORT[f"loss.{case}"] = dict(loss_err=abs(loss - float(g[f"{case}.f64.loss"])), gpred_rel=rel_to_max(gp, r64),
+                                  ref32_gpred_rel=rel_to_max(r32, r64))
+    assert abs(loss - float(g[f"{case}.f64.loss"])) <= 1e-5, case
+    assert rel_to_max(gp, r64) <= max(1e-4, 3 * rel_to_max(r32, r64)), case
+
+
+@pytest.mark.parametrize("shape,masked", [((4, 3, 128, 160), True), ((2, 3, 67, 91), True), ((1, 3, 256, 256), False)])
+def test_loss_vs_oracle_seeded(shape, masked):
+    """Larger seeded batches (even and odd H*W: packed and scalar kernels) against the CPU oracle in
+    fp64, every term separately, and the gradient."""
+    import curl_b200
+    dev = _dev()
+    gen = torch.Generator().manual_seed(sum(shape))
+    target = torch.rand(shape, generator=gen)
+    pred = (target + 0.08 * torch.randn(shape, generator=gen)).clamp(0, 1)
+    mask = (torch.rand(shape[0], 1, *shape[2:], generator=gen) > 0.1) if masked else torch.ones(shape[0], 1, *shape[2:], dtype=torch.bool)
+    ref = O.curl_loss_fwd_bwd(pred.double(), target.double(), mask)
+    ref32 = O.curl_loss_fwd_bwd(pred, target, mask)
+    crit = curl_b200.CURLLoss().to(dev)
+    p = pred.to(dev).requires_grad_(True)
+    terms = crit.terms(p, target.to(dev), mask.to(dev) if masked else None)
+    for k in ("rgb", "cosine", "lab", "hsv", "ssim"):
+        assert abs(float(terms[k].detach()) - float(ref[k])) <= 1e-5, (k, float(terms[k].detach()), float(ref[k]))
+    loss = crit(p, target.to(dev), mask.to(dev))
+    loss.backward()
+    assert abs(float(loss.detach()) - float(ref["loss"])) <= 1e-5
+    gp, r64, r32 = p.grad.cpu().numpy(), ref["gpred"].numpy(), ref32["gpred"].numpy()
+    REPORT[f"loss.seeded.{shape}"] = dict(gpred_rel=rel_to_max(gp, r64), ref32_gpred_rel=rel_to_max(r32, r64),
+                                          frac_over_1e4=frac_over(gp / np.abs(r64).max(), r64 / np.abs(r64).max(), 1e-4))
+    assert rel_to_max(gp, r64) <= max(1e-4, 3 * rel_to_max(r32, r64))
+    # masked pixels get exactly zero gradient
+    if masked:
+        dead = ~mask.expand(-1, 3, -1, -1).numpy()
+        assert np.all(gp[dead] == 0.0)
+
+
+def test_loss_terms_abi_deterministic_and_errors():
+    """The C-ABI entry points directly: sums and L planes against the oracle, run-to-run bit
+    identity of the ticketed reduction, float mask == bool mask, argument errors."""
+    import curl_b200
+    from curl_b200 import _lib, functional
+    dev = _dev()
+    gen = torch.Generator().manual_seed(77)
+    B, H, W = 3, 96, 112
+    target = torch.rand(B, 3, H, W, generator=gen)
+    pred = torch.rand(B, 3, H, W, generator=gen)
+    mask = torch.rand(B, 1, H, W, generator=gen) > 0.25
+    a = functional.loss_terms(pred.to(dev), target.to(dev), mask.to(dev))
+    b = functional.loss_terms(pred.to(dev), target.to(dev), mask.to(dev))
+    c = functional.loss_terms(pred.to(dev), target.to(dev), mask.float().to(dev))
+    for x, y, z in zip(a, b, c):
+        assert torch.equal(x, y) and torch.equal(x, z)
+    sums = a[0].cpu().double()
+    pm, tm = pred.double() * mask, target.double() * mask
+    want = torch.stack([(pm - tm).abs().sum(dim=(1, 2, 3)),
+                        torch.nn.functional.cosine_similarity(pm, tm, dim=1).sum(dim=(1, 2)),
+                        (O.loss_lab(pm) - O.loss_lab(tm)).abs().sum(dim=(1, 2, 3)),
+                        (O.loss_hsv_cone(pm) - O.loss_hsv_cone(tm)).abs().sum(dim=(1, 2, 3)),
+                        mask.double().sum(dim=(1, 2, 3))], dim=1)
+    assert torch.all((sums - want).abs() <= 2e-6 * want.abs().clamp(min=1.0)), (sums, want)
+    assert torch.equal(sums[:, 4], want[:, 4])
+    assert (a[1].cpu() - O.loss_lab(pm)[:, 0:1].float()).abs().max() <= 1e-5
+    assert (a[2].cpu() - O.loss_lab(tm)[:, 0:1].float()).abs().max() <= 1e-5
+    # raw ABI errors
+    lib = _lib.load()
+    p, t = pred.to(dev), target.to(dev)
+    s = torch.empty(B, 5, device=dev)
+    n = lib.curl_loss_terms_workspace_bytes(B, H, W)
+    ws = torch.empty(n, dtype=torch.uint8, device=dev)
+    ok = lambda *args: lib.curl_loss_terms_fwd_f32(*args)
+    st = torch.cuda.current_stream(dev).cuda_stream
+    assert ok(p.data_ptr(), t.data_ptr(), None, 0, s.data_ptr(), None, None, ws.data_ptr(), n, B, H, W, st) == 0
+    assert ok(None, t.data_ptr(), None, 0, s.data_ptr(), None, None, ws.data_ptr(), n, B, H, W, st) == -1
+    assert ok(p.data_ptr(), t.data_ptr(), None, 1, s.data_ptr(), None, None, ws.data_ptr(), n, B, H, W, st) == -1
+    assert ok(p.data_ptr(), t.data_ptr(), None, 0, s.data_ptr(), None, None, ws.data_ptr(), n - 1, B, H, W, st) == -3
+    assert ok(p.data_ptr(), t.data_ptr(), None, 0, s.data_ptr(), None, None, ws.data_ptr(), n, 0, H, W, st) == -1
+    assert lib.curl_loss_terms_bwd_f32(p.data_ptr(), t.data_ptr(), None, 0, None, None, p.data_ptr(), B, H, W, st) == -1
+    assert lib.curl_loss_terms_workspace_bytes(0, H, W) == 0
+    torch.cuda.synchronize()
+    # module-level errors
+    crit = curl_b200.CURLLoss().to(dev)
+    with pytest.raises(ValueError):
+        crit(p, t[:, :, :-1], mask.to(dev))
+    with pytest.raises(RuntimeError):
+        crit(p, t.clone().requires_grad_(True), mask.to(dev)).backward()
+    bad = curl_b200.CURLLoss().to(dev)
+    with torch.no_grad():
+        bad.rgb2lab.rgb_to_xyz.mul_(1.01)
+    with pytest.raises(RuntimeError):
+        bad(p, t, mask.to(dev))
+
+
+def test_loss_training_step_through_layer():
+    """criterion(net(img), target, mask).backward() with the curve layer underneath: gradients reach
+    the knots through both fused backward kernels and match the oracle chain."""
+    import curl_b200
+    dev = _dev()
+    gen = torch.Generator().manual_seed(123)
+    B, H, W = 2, 64, 80
+    img = torch.rand(B, 3, H, W, generator=gen)
+    target = (img * 1.1 + 0.02).clamp(0, 1)
+    mask = torch.rand(B, 1, H, W, generator=gen) > 0.1
+    knots = [0.1 * torch.randn(B, n, generator=gen) for n in (48, 48, 64)]
+    # oracle, fp64
+    kd = [k.double().requires_grad_(True) for k in knots]
+    out, reg = O.curl_layer(img.double(), mask, *kd)
+    ref_loss = O.curl_loss(out, target.double(), mask) + 1e-6 * reg.sum()
+    ref_g = torch.autograd.grad(ref_loss, kd)
+    layer, crit = curl_b200.CURLLayer().to(dev), curl_b200.CURLLoss().to(dev)
+    kg = [k.to(dev).requires_grad_(True) for k in knots]
+    out, reg = layer(img.to(dev), mask.to(dev), *kg)
+    loss = crit(out, target.to(dev), mask.to(dev)) + 1e-6 * reg.sum()
+    loss.backward()
+    assert abs(float(loss.detach()) - float(ref_loss.detach())) <= 1e-5
+    for k, r in zip(kg, ref_g):
+        assert rel_to_max(k.grad.cpu().numpy(), r.numpy()) <= 1e-4

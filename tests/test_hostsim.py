@@ -5,10 +5,12 @@ a GPU; the GPU tests then only have to establish that the MUFU approximations an
 arithmetic stay inside the same bounds."""
 import numpy as np
 import pytest
+import torch
 
 import hostsim
 import parity
-from conftest import LAYER_CASES, STAGE_CASES, rel_to_max
+from conftest import LAYER_CASES, LOSS_CASES, STAGE_CASES, rel_to_max
+from oracle import curl_oracle as O
 
 
 @pytest.mark.parametrize("case", LAYER_CASES)
@@ -111,3 +113,31 @@ def test_hostsim_trispace_vs_golden(case, trispace_golden):
         gr = hostsim.trispace(img, R, L, Hc, spatial, clamp, gout)
         for k in ("gR", "gL", "gH"):
             assert rel_to_max(gr[k], g[f"{case}.f64.c{clamp}.{k}"]) <= 1e-4, (case, clamp, k)
+
+
+def _loss_from_terms(sums, L_pred, L_target, mask, msssim):
+    """model.py:90-117 from the five per-image sums and the L planes (what curl_b200.CURLLoss does)."""
+    B, _, H, W = L_pred.shape
+    tot = sums.sum(0)
+    n = 3 * tot[4]
+    n_masked = 0.0 if mask is None else float((np.asarray(mask) == 0).sum())
+    return (tot[0] / n + 1.0 - (tot[1] + n_masked) / (B * H * W) + tot[2] / n + tot[3] / n
+            + 10 * (1.0 - msssim(L_pred, L_target)).mean()) / 5
+
+
+@pytest.mark.parametrize("case", LOSS_CASES)
+def test_hostsim_loss_terms_vs_golden(case, loss_golden):
+    """Per-pixel math of the fused CURLLoss colour terms (curl_loss.cuh: cosine similarity, clamped
+    Lab, HSV cone and the hand-derived gradient) against the reference fixtures; MS-SSIM (library
+    path) is taken from the oracle and differentiated by autograd down to the L plane."""
+    g = loss_golden
+    pred, target, mask = g[f"{case}.pred"], g[f"{case}.target"], g[f"{case}.mask"]
+    r = hostsim.loss_terms(pred, target, mask)
+    sums = torch.from_numpy(r["sums"]).requires_grad_(True)
+    Lp = torch.from_numpy(r["L_pred"]).requires_grad_(True)
+    loss = _loss_from_terms(sums, Lp, torch.from_numpy(r["L_target"]), mask, O.msssim)
+    assert abs(float(loss.detach()) - float(g[f"{case}.f64.loss"])) <= 1e-5, case          # fp tolerance of north_star
+    gs, gL = torch.autograd.grad(loss, (sums, Lp))
+    gp = hostsim.loss_terms(pred, target, mask, w=gs[:, :4].numpy(), gL=gL.numpy())
+    r32, r64 = g[f"{case}.f32.gpred"], g[f"{case}.f64.gpred"]
+    assert rel_to_max(gp, r64) <= max(1e-4, 3 * rel_to_max(r32, r64)), case

@@ -125,3 +125,32 @@ def test_trispace_api():
         flat.generate_residual(torch.rand(1, 3, 4, 4), *[torch.zeros(1, 3, 35)] * 3)
     x = torch.rand(1, 3, 4, 4)
     assert torch.equal(flat.generate_image(x, x), torch.clamp(x + x, 0, 1))
+
+
+def test_curlloss_api():
+    """CURLLoss / MSSSIMMetric (reference model.py:36-118, metric.py:75-214): constructor, attributes,
+    state-dict keys; MS-SSIM (the library part of the loss) equals the oracle's on CPU; the fused
+    colour terms have no CPU path."""
+    crit = curl_b200.CURLLoss()
+    assert (crit.ssim_window_size, crit.num_channel) == (5, 1)
+    assert list(crit.state_dict()) == ["msssim_layer.msssim_weights", "rgb2lab.rgb_to_xyz", "rgb2lab.fxfyfz_to_lab",
+                                       "rgb2lab.xyz_to_rgb_mult", "rgb2lab.lab_to_fxfyfz_offset",
+                                       "rgb2hsv.comparison_zero"]
+    ms = crit.msssim_layer
+    assert isinstance(ms, curl_b200.metric.MSSSIMMetric)
+    assert (ms.window_size, ms.num_channel, ms.levels) == (11, 1, 5) and ms.gaussian_window.shape == (1, 1, 11, 11)
+    assert torch.equal(ms.gaussian_window, O.ssim_window())
+    gen = torch.Generator().manual_seed(2)
+    a = torch.rand(2, 1, 48, 40, generator=gen)
+    b = (a + 0.1 * torch.randn(2, 1, 48, 40, generator=gen)).clamp(0, 1)
+    assert torch.allclose(ms(a, b), O.msssim(a, b), rtol=0, atol=2e-6)
+    a64 = a.double().requires_grad_(True)
+    ga, = torch.autograd.grad(ms.double()(a64, b.double()).sum(), a64)
+    a64o = a.double().requires_grad_(True)
+    go, = torch.autograd.grad(O.msssim(a64o, b.double()).sum(), a64o)
+    assert torch.allclose(ga, go, rtol=1e-9, atol=1e-12)
+    with pytest.raises(RuntimeError, match="four dimensions"):
+        ms(a[0], b[0])
+    with pytest.raises(RuntimeError, match="CUDA"):
+        crit(torch.rand(1, 3, 32, 32), torch.rand(1, 3, 32, 32), torch.ones(1, 1, 32, 32, dtype=torch.bool))
+    assert torch.equal(crit.batch_L_ssim_convert(torch.arange(24.).reshape(1, 3, 2, 4)), torch.arange(8.).reshape(1, 1, 2, 4))
