@@ -392,6 +392,36 @@ def run_ours(args):
             "fwd_tflops_fp32": tpx * 3 * (126 + 2 * 3 * 126) / (ms_f / 1e3) / 1e12,
             "what": "fused generate_residual + generate_image, degree 4, 5 variables; FMA-bound (2646 flop/px forward)"}
         del ti, tg, tc
+        # CURLLoss (model.py:36-118): fused colour terms (one forward + one backward kernel) and the whole
+        # criterion step incl. library MS-SSIM, on the headline batch (pred = the layer's output)
+        from curl_b200.functional import loss_terms
+        crit = curl_b200.CURLLoss().to(dev)
+        with torch.no_grad():
+            l_target = (img.detach() * 0.9 + 0.05)
+            l_pred = layer(img.detach(), mask, Ld, Rd, Hd)[0]
+            ms_lf = timed(lambda: loss_terms(l_pred, l_target, mask), 10)
+        l_pred.requires_grad_(True)
+        l_w = torch.full((B, 5), 1e-7, device=dev)
+        l_gl = torch.full((B, 1) + tuple(img.shape[2:]), 1e-7, device=dev)
+
+        def terms_step():
+            l_pred.grad = None
+            s, lp, _ = loss_terms(l_pred, l_target, mask)
+            torch.autograd.backward([s, lp], [l_w, l_gl])
+        ms_ls = timed(terms_step, 5)
+
+        def crit_step():
+            l_pred.grad = None
+            crit(l_pred, l_target, mask).backward()
+        ms_lc = timed(crit_step, 3)
+        extras["curlloss_4k_b%d" % B] = {
+            "terms_fwd_ms": ms_lf, "terms_fwd_mpx_per_s": n_px / 1e6 / (ms_lf / 1e3),
+            "terms_fwd_gbs": n_px * 33 / (ms_lf / 1e3) / 1e9,
+            "terms_fwd_bwd_ms": ms_ls, "terms_fwd_bwd_mpx_per_s": n_px / 1e6 / (ms_ls / 1e3),
+            "criterion_fwd_bwd_ms": ms_lc,
+            "what": "fused colour terms: 33 B/px forward (pred, target, mask in; 2 L planes out), 41 B/px backward; "
+                    "criterion = terms + MS-SSIM of the L planes on the library convolution path"}
+        del l_pred, l_target, l_gl, crit
 
     if rank == 0:
         peak, peak_src = measured_peak()

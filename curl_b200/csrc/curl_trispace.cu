@@ -122,6 +122,9 @@ constexpr size_t bwd_smem_bytes() {
 #ifndef TRI_BWD_MIN_BLOCKS
 #define TRI_BWD_MIN_BLOCKS 3   // measured: 2 -> 3.80, 3 -> 3.94, 4 -> 3.83 Gpx/s (4K x 8, 126 coefficients)
 #endif
+#ifndef TRI_SKEW_NS
+#define TRI_SKEW_NS 0
+#endif
 template <int NV>
 __global__ void __launch_bounds__(BT, TRI_BWD_MIN_BLOCKS) trispace_bwd_kernel(const TParams p) {
   constexpr int NC = poly_num_coeffs(NV, DEG);
@@ -134,26 +137,41 @@ __global__ void __launch_bounds__(BT, TRI_BWD_MIN_BLOCKS) trispace_bwd_kernel(co
   const int b = blockIdx.y;
   const int t = threadIdx.x;
   stage_coef<NC>(p, b, s_coef);
+#if TRI_SKEW_NS > 0
+  {
+    // The resident blocks of one SM start together and, their phases taking equally long, stay in
+    // lock-step: all in the FMA-bound phase A, then all in the shared-memory-bound phase B.  A
+    // one-off start delay per residency slot puts them out of phase for the rest of the kernel.
+    unsigned nsm;
+    asm("mov.u32 %0, %%nsmid;" : "=r"(nsm));
+    const unsigned slot = ((blockIdx.y * gridDim.x + blockIdx.x) / nsm) % TRI_BWD_MIN_BLOCKS;
+    if (slot) __nanosleep(slot * TRI_SKEW_NS);
+  }
+#endif
   const int HW = p.HW;
   const float* in = p.img + (size_t)b * 3 * HW;
   const float* go = p.gout + (size_t)b * 3 * HW;
   const float fW = (float)p.W, fH = (float)p.H;
   const bool clamp = p.clamp != 0;
-  // accumulators: [space][channel], packed over (even pixel, odd pixel) of the tile
-  constexpr int J = (NC + BT - 1) / BT;           // monomials per thread in phase B
+  // Phase B mapping: warp w takes the w-th share of the half tile's pixels, lane l the monomials
+  // l, l + 32, ..: every 128-bit load of G (a broadcast, two shared-memory wavefronts) then feeds J
+  // monomials instead of one.  Accumulators: [space][monomial slot][channel], packed over (even, odd) pixel.
+  constexpr int NWARP = BT / 32;
+  constexpr int J = (NC + 31) / 32;               // monomials per thread in phase B
+  constexpr int QW = BT / 4 / NWARP;              // groups of four pixels per warp
+  const int lane = t & 31, warp = t >> 5;
   F2 acc[3][J][3];
 #pragma unroll
   for (int sp = 0; sp < 3; ++sp)
 #pragma unroll
     for (int j = 0; j < J; ++j) acc[sp][j][0] = acc[sp][j][1] = acc[sp][j][2] = F2(0.0f);
-  const int n_tiles = (HW + BT - 1) / BT;
+  const int n_tiles = (HW + 2 * BT - 1) / (2 * BT);
   for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    // phase A runs on the first BT/2 threads, one packed pixel pair each (half the warp
-    // instructions of a scalar pass over BT threads); the other warps wait at the barrier while
-    // the SM's other resident blocks use the pipes.
+    // phase A, part 1: every thread takes one packed pixel pair of the 2*BT-pixel tile (all four
+    // scheduler partitions busy), recomputes the forward and keeps vars / gp in registers.
     F2 vars[3][3], gp[3][3], xs2 = F2(0.0f), ys2 = F2(0.0f);
-    if (t < BT / 2) {
-      const int i = tile * BT + 2 * t;
+    {
+      const int i = tile * 2 * BT + 2 * t;
       const bool v0 = i < HW, v1 = i + 1 < HW;
       F2 x[3], g[3];
 #pragma unroll
@@ -170,51 +188,68 @@ __global__ void __launch_bounds__(BT, TRI_BWD_MIN_BLOCKS) trispace_bwd_kernel(co
       }
       trispace_gpoly<F2, NV, DEG>(x, xs2, ys2, s_coef, clamp, g, vars, gp);
     }
+    // part 2 + phase B, per space and per half tile: the half's BT/2 threads write their monomials
+    // and gp to shared memory, then all threads multiply.  The halves alternate between the lower
+    // and the upper warps, so the store work is spread over the partitions as well.
 #pragma unroll
-    for (int sp = 0; sp < 3; ++sp) {
-      __syncthreads();                               // phase B of the previous space is done with T, G
-      if (t < BT / 2) {
-        const F2 v[5] = {vars[sp][0], vars[sp][1], vars[sp][2], xs2, ys2};
-        F2* col = reinterpret_cast<F2*>(s_T + 2 * t);
+    for (int sp = 0; sp < 3; ++sp)
+#pragma unroll 1
+    for (int half = 0; half < 2; ++half) {
+      __syncthreads();                               // the previous product is done with T, G
+      if ((t >= BT / 2) == (half == 1)) {
+        const int tl = t - half * (BT / 2);
+        F2 v[5] = {vars[sp][0], vars[sp][1], vars[sp][2], xs2, ys2};
+#pragma unroll
+        for (int q = 0; q < 5; ++q) asm volatile("" : "+l"(v[q].u));   // keeps the monomial products inside this
+        F2* col = reinterpret_cast<F2*>(s_T + 2 * tl);                  // branch (else hoisted out of the half loop into local memory)
         col[0] = F2(1.0f);                           // the constant term
         MonoStore<F2> st{col, T_PITCH / 2};
         mono_visit<F2, NV, DEG>(v, st);
 #pragma unroll
-        for (int c = 0; c < 3; ++c) reinterpret_cast<F2*>(s_G + c * BT)[t] = gp[sp][c];
+        for (int c = 0; c < 3; ++c) reinterpret_cast<F2*>(s_G + c * BT)[tl] = gp[sp][c];
       }
       __syncthreads();
-      if (t < NC) {
 #pragma unroll 2
-        for (int q = 0; q < BT / 4; ++q) {
-          const float4 g0 = reinterpret_cast<const float4*>(s_G)[q];                  // channel 0, four pixels
-          const float4 g1 = reinterpret_cast<const float4*>(s_G + BT)[q];
-          const float4 g2 = reinterpret_cast<const float4*>(s_G + 2 * BT)[q];
+      for (int qi = 0; qi < QW; ++qi) {
+        const int q = warp * QW + qi;
+        const float4 g0 = reinterpret_cast<const float4*>(s_G)[q];                  // channel 0, four pixels
+        const float4 g1 = reinterpret_cast<const float4*>(s_G + BT)[q];
+        const float4 g2 = reinterpret_cast<const float4*>(s_G + 2 * BT)[q];
 #pragma unroll
-          for (int j = 0; j < J; ++j) {
-            const int k = t + j * BT < NC ? t + j * BT : t;       // surplus slots redo row t; never stored
-            const float4 m = reinterpret_cast<const float4*>(s_T + k * T_PITCH)[q];
-            const F2 mlo(m.x, m.y), mhi(m.z, m.w);
-            acc[sp][j][0] = vfma(F2(g0.x, g0.y), mlo, acc[sp][j][0]);
-            acc[sp][j][1] = vfma(F2(g1.x, g1.y), mlo, acc[sp][j][1]);
-            acc[sp][j][2] = vfma(F2(g2.x, g2.y), mlo, acc[sp][j][2]);
-            acc[sp][j][0] = vfma(F2(g0.z, g0.w), mhi, acc[sp][j][0]);
-            acc[sp][j][1] = vfma(F2(g1.z, g1.w), mhi, acc[sp][j][1]);
-            acc[sp][j][2] = vfma(F2(g2.z, g2.w), mhi, acc[sp][j][2]);
-          }
+        for (int j = 0; j < J; ++j) {
+          const int k = lane + 32 * j < NC ? lane + 32 * j : lane;   // surplus slots redo row `lane`; never stored
+          const float4 m = reinterpret_cast<const float4*>(s_T + k * T_PITCH)[q];
+          const F2 mlo(m.x, m.y), mhi(m.z, m.w);
+          acc[sp][j][0] = vfma(F2(g0.x, g0.y), mlo, acc[sp][j][0]);
+          acc[sp][j][1] = vfma(F2(g1.x, g1.y), mlo, acc[sp][j][1]);
+          acc[sp][j][2] = vfma(F2(g2.x, g2.y), mlo, acc[sp][j][2]);
+          acc[sp][j][0] = vfma(F2(g0.z, g0.w), mhi, acc[sp][j][0]);
+          acc[sp][j][1] = vfma(F2(g1.z, g1.w), mhi, acc[sp][j][1]);
+          acc[sp][j][2] = vfma(F2(g2.z, g2.w), mhi, acc[sp][j][2]);
         }
       }
     }
   }
-  float* row = p.partials + ((size_t)b * gridDim.x + blockIdx.x) * NG;
+  // fold the warps' shares: through shared memory (T is free now), fixed order
+  __syncthreads();
+  float* s_red = s_T;                               // [NWARP][NG]
 #pragma unroll
   for (int j = 0; j < J; ++j) {
-    const int k = t + j * BT;
+    const int k = lane + 32 * j;
     if (k < NC) {
 #pragma unroll
       for (int sp = 0; sp < 3; ++sp)
 #pragma unroll
-        for (int c = 0; c < 3; ++c) row[(sp * 3 + c) * NC + k] = vhsum(acc[sp][j][c]);
+        for (int c = 0; c < 3; ++c) s_red[warp * NG + (sp * 3 + c) * NC + k] = vhsum(acc[sp][j][c]);
     }
+  }
+  __syncthreads();
+  float* row = p.partials + ((size_t)b * gridDim.x + blockIdx.x) * NG;
+  for (int k = t; k < NG; k += BT) {
+    float a = 0.0f;
+#pragma unroll
+    for (int w = 0; w < NWARP; ++w) a += s_red[w * NG + k];
+    row[k] = a;
   }
   __threadfence();
   __syncthreads();
@@ -245,7 +280,7 @@ static int grid_x(int B, int HW, int px_per_block, int blocks_per_sm) {
 }
 constexpr int FWD_BLOCKS_PER_SM = 16;
 constexpr int BWD_BLOCKS_PER_SM = 12;   // 3 resident blocks per SM (73 KB of shared memory each) x 4 waves
-static int bwd_grid_x(int B, int HW) { return grid_x(B, HW, BT, BWD_BLOCKS_PER_SM); }
+static int bwd_grid_x(int B, int HW) { return grid_x(B, HW, 2 * BT, BWD_BLOCKS_PER_SM); }
 
 static int check_args(const float* img, const float* R, const float* L, const float* Hc, int degree, int spatial,
                       int B, int H, int W) {

@@ -5,10 +5,13 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from curl_b200 import _lib as L
 lib = ctypes.CDLL(sys.argv[1] if len(sys.argv) > 1 else L.LIB_PATH)
 for name, (res, args) in L.SIGNATURES.items():
+    if not hasattr(lib, name):
+        continue        # a trispace-only experiment build
     fn = getattr(lib, name); fn.restype = res; fn.argtypes = args
 dev = torch.device("cuda:0")
 st = torch.cuda.current_stream().cuda_stream
-for (B, H, W) in ((32, 512, 512), (8, 2160, 3840)):
+SHAPES = ((8, 2160, 3840),) if os.environ.get('TB_4K') else ((32, 512, 512), (8, 2160, 3840))
+for (B, H, W) in SHAPES:
     for spatial in (1, 0):
         nc = lib.curl_trispace_num_coeffs(4, spatial)
         g = torch.Generator(device=dev).manual_seed(1)
