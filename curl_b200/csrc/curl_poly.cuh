@@ -120,26 +120,32 @@ CURL_HD T vsigmoid(T p) {
 // NV = 3 (spatial=False) or 5 (spatial=True: x = column / width, y = row / height appended, model.py:472-484).
 // coef: [space R, L, H][NC] Coef4 records.
 // ------------------------------------------------------------------------------------------------
+// sig (nullable): receives the nine sigmoid outputs [space][channel], which is all the backward needs
+// besides the image to skip re-evaluating the three polynomials.
 template <class T, int NV, int DEG>
-CURL_HD void trispace_fwd(const T rgb[3], T xs, T ys, const Coef4* coef, bool clamp, T out[3]) {
+CURL_HD void trispace_fwd(const T rgb[3], T xs, T ys, const Coef4* coef, bool clamp, T out[3], T* sig = nullptr) {
   constexpr int NC = poly_num_coeffs(NV, DEG);
   T v[5], p[3], s[3], r[3], res[3];
   v[3] = xs; v[4] = ys;
   v[0] = rgb[0]; v[1] = rgb[1]; v[2] = rgb[2];
   poly_eval<T, NV, DEG>(v, coef, p);
 #pragma unroll
-  for (int k = 0; k < 3; ++k) res[k] = vfma(vsigmoid(p[k]), T(2.0f), T(-1.0f));           // model.py:490,497
+  for (int k = 0; k < 3; ++k) {
+    s[k] = vsigmoid(p[k]);
+    if (sig) sig[k] = s[k];
+    res[k] = vfma(s[k], T(2.0f), T(-1.0f));                                                // model.py:490,497
+  }
   rgb2lab_fwd<T, false>(rgb, v, nullptr);
   poly_eval<T, NV, DEG>(v, coef + NC, p);
 #pragma unroll
-  for (int k = 0; k < 3; ++k) s[k] = vsigmoid(p[k]);
+  for (int k = 0; k < 3; ++k) { s[k] = vsigmoid(p[k]); if (sig) sig[3 + k] = s[k]; }
   lab2rgb_fwd<T, false>(s, r, nullptr);                                                    // model.py:491
 #pragma unroll
   for (int k = 0; k < 3; ++k) res[k] = vadd(res[k], vfma(r[k], T(2.0f), T(-1.0f)));        // model.py:498,501
   rgb2hsv_fwd<T, false, false>(rgb, v, nullptr);
   poly_eval<T, NV, DEG>(v, coef + 2 * NC, p);
 #pragma unroll
-  for (int k = 0; k < 3; ++k) s[k] = vsigmoid(p[k]);
+  for (int k = 0; k < 3; ++k) { s[k] = vsigmoid(p[k]); if (sig) sig[6 + k] = s[k]; }
   hsv2rgb_fwd<T, false, false>(s, r, nullptr);                                             // model.py:492
 #pragma unroll
   for (int k = 0; k < 3; ++k) {
@@ -154,28 +160,36 @@ CURL_HD void trispace_fwd(const T rgb[3], T xs, T ys, const Coef4* coef, bool cl
 // arriving at the polynomial's three outputs (gp[s]).  The coefficient gradient is then
 //   d coef[s][c][k] = sum over pixels of gp[s][c] * monomial_k(vars[s] | x, y),
 // a reduction the caller organises (curl_trispace.cu).
+// sig (nullable): the nine sigmoid outputs the forward saved; when given, no polynomial is evaluated here.
 template <class T, int NV, int DEG>
 CURL_HD void trispace_gpoly(const T rgb[3], T xs, T ys, const Coef4* coef, bool clamp, const T gout[3],
-                            T vars[3][3], T gp[3][3]) {
+                            T vars[3][3], T gp[3][3], const T* sig = nullptr) {
   constexpr int NC = poly_num_coeffs(NV, DEG);
   T v[5], p[3], s[3][3], r_lab[3], r_hsv[3];
   RgbJac<T> jl; Hsv2RgbJac<T> jh;
   v[3] = xs; v[4] = ys;
   v[0] = vars[0][0] = rgb[0]; v[1] = vars[0][1] = rgb[1]; v[2] = vars[0][2] = rgb[2];
-  poly_eval<T, NV, DEG>(v, coef, p);
-#pragma unroll
-  for (int k = 0; k < 3; ++k) s[0][k] = vsigmoid(p[k]);
   rgb2lab_fwd<T, false>(rgb, vars[1], nullptr);
-  v[0] = vars[1][0]; v[1] = vars[1][1]; v[2] = vars[1][2];
-  poly_eval<T, NV, DEG>(v, coef + NC, p);
-#pragma unroll
-  for (int k = 0; k < 3; ++k) s[1][k] = vsigmoid(p[k]);
-  lab2rgb_fwd<T, true>(s[1], r_lab, &jl);
   rgb2hsv_fwd<T, false, false>(rgb, vars[2], nullptr);
-  v[0] = vars[2][0]; v[1] = vars[2][1]; v[2] = vars[2][2];
-  poly_eval<T, NV, DEG>(v, coef + 2 * NC, p);
+  if (sig) {
 #pragma unroll
-  for (int k = 0; k < 3; ++k) s[2][k] = vsigmoid(p[k]);
+    for (int sp = 0; sp < 3; ++sp)
+#pragma unroll
+      for (int k = 0; k < 3; ++k) s[sp][k] = sig[sp * 3 + k];
+  } else {
+    poly_eval<T, NV, DEG>(v, coef, p);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) s[0][k] = vsigmoid(p[k]);
+    v[0] = vars[1][0]; v[1] = vars[1][1]; v[2] = vars[1][2];
+    poly_eval<T, NV, DEG>(v, coef + NC, p);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) s[1][k] = vsigmoid(p[k]);
+    v[0] = vars[2][0]; v[1] = vars[2][1]; v[2] = vars[2][2];
+    poly_eval<T, NV, DEG>(v, coef + 2 * NC, p);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) s[2][k] = vsigmoid(p[k]);
+  }
+  lab2rgb_fwd<T, true>(s[1], r_lab, &jl);
   hsv2rgb_fwd<T, true, false>(s[2], r_hsv, &jh);
   T g2[3];
 #pragma unroll

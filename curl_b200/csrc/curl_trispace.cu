@@ -25,6 +25,7 @@ struct TParams {
   const float* gout;     // backward: [B][3][HW]
   float* out;            // forward: [B][3][HW]
   float* gcoef[3];       // backward: [B][3][NC]
+  float* sig;            // [B][9][HW] sigmoid outputs: written by the forward (SAVE), read by the backward (SAVED); or null
   float* partials;       // backward: [B][gridDim.x][9*NC]
   unsigned* tickets;     // backward: [B], zero on entry
   int HW, W, H;
@@ -60,7 +61,7 @@ __device__ __forceinline__ void coords(int idx, int W, float fW, float fH, float
 // kernel is FMA-bound (about 1500 multiply-adds per pixel), not HBM-bound, and the fully unrolled
 // monomial walk wants its registers; VEC = 1: scalar path for odd HW or unaligned bases.
 // ---------------------------------------------------------------------------------------------
-template <int NV, int VEC>
+template <int NV, int VEC, bool SAVE>
 __global__ void __launch_bounds__(THREADS, 2) trispace_fwd_kernel(const TParams p) {
   constexpr int NC = poly_num_coeffs(NV, DEG);
   __shared__ Coef4 s_coef[3 * NC];
@@ -69,6 +70,7 @@ __global__ void __launch_bounds__(THREADS, 2) trispace_fwd_kernel(const TParams 
   const int HW = p.HW;
   const float* in = p.img + (size_t)b * 3 * HW;
   float* out = p.out + (size_t)b * 3 * HW;
+  float* sg = SAVE ? p.sig + (size_t)b * 9 * HW : nullptr;
   const float fW = (float)p.W, fH = (float)p.H;
   const bool clamp = p.clamp != 0;
   const int stride = gridDim.x * THREADS * VEC;
@@ -80,18 +82,27 @@ __global__ void __launch_bounds__(THREADS, 2) trispace_fwd_kernel(const TParams 
       float xs[2] = {0.f, 0.f}, ys[2] = {0.f, 0.f};
       if (NV == 5) { coords(i, p.W, fW, fH, &xs[0], &ys[0]); coords(i + 1, p.W, fW, fH, &xs[1], &ys[1]); }
       const F2 x[3] = {F2(c0.x, c0.y), F2(c1.x, c1.y), F2(c2.x, c2.y)};
-      F2 y[3];
-      trispace_fwd<F2, NV, DEG>(x, F2(xs[0], xs[1]), F2(ys[0], ys[1]), s_coef, clamp, y);
+      F2 y[3], sv[9];
+      trispace_fwd<F2, NV, DEG>(x, F2(xs[0], xs[1]), F2(ys[0], ys[1]), s_coef, clamp, y, SAVE ? sv : nullptr);
 #pragma unroll
       for (int c = 0; c < 3; ++c)
         __stcs(reinterpret_cast<float2*>(out + (size_t)c * HW + i), make_float2(y[c].lo(), y[c].hi()));
+      if constexpr (SAVE) {
+#pragma unroll
+        for (int c = 0; c < 9; ++c)
+          __stcs(reinterpret_cast<float2*>(sg + (size_t)c * HW + i), make_float2(sv[c].lo(), sv[c].hi()));
+      }
     } else {
       const float x[3] = {__ldcs(in + i), __ldcs(in + HW + i), __ldcs(in + 2 * (size_t)HW + i)};
-      float xs = 0.f, ys = 0.f, y[3];
+      float xs = 0.f, ys = 0.f, y[3], sv[9];
       if (NV == 5) coords(i, p.W, fW, fH, &xs, &ys);
-      trispace_fwd<float, NV, DEG>(x, xs, ys, s_coef, clamp, y);
+      trispace_fwd<float, NV, DEG>(x, xs, ys, s_coef, clamp, y, SAVE ? sv : nullptr);
 #pragma unroll
       for (int c = 0; c < 3; ++c) __stcs(out + (size_t)c * HW + i, y[c]);
+      if constexpr (SAVE) {
+#pragma unroll
+        for (int c = 0; c < 9; ++c) __stcs(sg + (size_t)c * HW + i, sv[c]);
+      }
     }
   }
 }
@@ -125,7 +136,7 @@ constexpr size_t bwd_smem_bytes() {
 #ifndef TRI_SKEW_NS
 #define TRI_SKEW_NS 0
 #endif
-template <int NV>
+template <int NV, bool SAVED>
 __global__ void __launch_bounds__(BT, TRI_BWD_MIN_BLOCKS) trispace_bwd_kernel(const TParams p) {
   constexpr int NC = poly_num_coeffs(NV, DEG);
   constexpr int NG = 9 * NC;
@@ -151,6 +162,7 @@ __global__ void __launch_bounds__(BT, TRI_BWD_MIN_BLOCKS) trispace_bwd_kernel(co
   const int HW = p.HW;
   const float* in = p.img + (size_t)b * 3 * HW;
   const float* go = p.gout + (size_t)b * 3 * HW;
+  const float* sg = SAVED ? p.sig + (size_t)b * 9 * HW : nullptr;
   const float fW = (float)p.W, fH = (float)p.H;
   const bool clamp = p.clamp != 0;
   // Phase B mapping: warp w takes the w-th share of the half tile's pixels, lane l the monomials
@@ -186,7 +198,15 @@ __global__ void __launch_bounds__(BT, TRI_BWD_MIN_BLOCKS) trispace_bwd_kernel(co
         coords(v1 ? i + 1 : 0, p.W, fW, fH, &xb, &yb);
         xs2 = F2(xa, xb); ys2 = F2(ya, yb);
       }
-      trispace_gpoly<F2, NV, DEG>(x, xs2, ys2, s_coef, clamp, g, vars, gp);
+      F2 sv[9];
+      if constexpr (SAVED) {
+#pragma unroll
+        for (int c = 0; c < 9; ++c) {
+          const float s0 = v0 ? __ldcs(sg + (size_t)c * HW + i) : 0.5f, s1 = v1 ? __ldcs(sg + (size_t)c * HW + i + 1) : 0.5f;
+          sv[c] = F2(s0, s1);
+        }
+      }
+      trispace_gpoly<F2, NV, DEG>(x, xs2, ys2, s_coef, clamp, g, vars, gp, SAVED ? sv : nullptr);
     }
     // part 2 + phase B, per space and per half tile: the half's BT/2 threads write their monomials
     // and gp to shared memory, then all threads multiply.  The halves alternate between the lower
@@ -294,17 +314,23 @@ static int check_args(const float* img, const float* R, const float* L, const fl
 template <int NV>
 static int launch_fwd(const TParams& p, int B, bool vec2, cudaStream_t st) {
   dim3 grid(grid_x(B, p.HW, THREADS * (vec2 ? 2 : 1), FWD_BLOCKS_PER_SM), B);
-  if (vec2) trispace_fwd_kernel<NV, 2><<<grid, THREADS, 0, st>>>(p);
-  else trispace_fwd_kernel<NV, 1><<<grid, THREADS, 0, st>>>(p);
+  if (p.sig) {
+    if (vec2) trispace_fwd_kernel<NV, 2, true><<<grid, THREADS, 0, st>>>(p);
+    else trispace_fwd_kernel<NV, 1, true><<<grid, THREADS, 0, st>>>(p);
+  } else {
+    if (vec2) trispace_fwd_kernel<NV, 2, false><<<grid, THREADS, 0, st>>>(p);
+    else trispace_fwd_kernel<NV, 1, false><<<grid, THREADS, 0, st>>>(p);
+  }
   return cudaGetLastError() == cudaSuccess ? CURL_OK : CURL_ERR_LAUNCH;
 }
 
 template <int NV>
 static int launch_bwd(const TParams& p, int B, cudaStream_t st) {
-  if (cudaFuncSetAttribute(trispace_bwd_kernel<NV>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                           (int)bwd_smem_bytes<NV>()) != cudaSuccess) return CURL_ERR_LAUNCH;
+  auto kern = p.sig ? trispace_bwd_kernel<NV, true> : trispace_bwd_kernel<NV, false>;
+  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_smem_bytes<NV>()) != cudaSuccess)
+    return CURL_ERR_LAUNCH;
   dim3 grid(bwd_grid_x(B, p.HW), B);
-  trispace_bwd_kernel<NV><<<grid, BT, bwd_smem_bytes<NV>(), st>>>(p);
+  kern<<<grid, BT, bwd_smem_bytes<NV>(), st>>>(p);
   return cudaGetLastError() == cudaSuccess ? CURL_OK : CURL_ERR_LAUNCH;
 }
 
@@ -322,15 +348,16 @@ int curl_trispace_num_coeffs(int degree, int spatial) {
 }
 
 int curl_trispace_fwd_f32(const float* img, const float* R, const float* L, const float* Hc, int degree,
-                          int spatial, int final_clamp, float* out, int B, int H, int W, void* stream) {
+                          int spatial, int final_clamp, float* out, float* saved, int B, int H, int W, void* stream) {
   int rc = check_args(img, R, L, Hc, degree, spatial, B, H, W);
   if (rc != CURL_OK) return rc;
   if (!out) return CURL_ERR_BAD_ARG;
-  if (!aligned4(out)) return CURL_ERR_MISALIGNED;
+  if (!aligned4(out) || !aligned4(saved)) return CURL_ERR_MISALIGNED;
   TParams p{};
-  p.img = img; p.coef[0] = R; p.coef[1] = L; p.coef[2] = Hc; p.out = out;
+  p.img = img; p.coef[0] = R; p.coef[1] = L; p.coef[2] = Hc; p.out = out; p.sig = saved;
   p.HW = H * W; p.W = W; p.H = H; p.clamp = final_clamp ? 1 : 0;
-  const bool v2 = (p.HW % 2 == 0) && ((reinterpret_cast<uintptr_t>(img) | reinterpret_cast<uintptr_t>(out)) & 7u) == 0;
+  const bool v2 = (p.HW % 2 == 0) && ((reinterpret_cast<uintptr_t>(img) | reinterpret_cast<uintptr_t>(out) |
+                                       reinterpret_cast<uintptr_t>(saved)) & 7u) == 0;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   return spatial ? launch_fwd<5>(p, B, v2, st) : launch_fwd<3>(p, B, v2, st);
 }
@@ -342,18 +369,19 @@ size_t curl_trispace_bwd_workspace_bytes(int B, int H, int W, int degree, int sp
 }
 
 int curl_trispace_bwd_f32(const float* img, const float* R, const float* L, const float* Hc, int degree,
-                          int spatial, int final_clamp, const float* gout, float* gR, float* gL, float* gH,
-                          void* workspace, size_t workspace_bytes, int B, int H, int W, void* stream) {
+                          int spatial, int final_clamp, const float* gout, const float* saved, float* gR, float* gL,
+                          float* gH, void* workspace, size_t workspace_bytes, int B, int H, int W, void* stream) {
   int rc = check_args(img, R, L, Hc, degree, spatial, B, H, W);
   if (rc != CURL_OK) return rc;
   if (!gout || !gR || !gL || !gH) return CURL_ERR_BAD_ARG;
-  if (!aligned4(gout)) return CURL_ERR_MISALIGNED;
+  if (!aligned4(gout) || !aligned4(saved)) return CURL_ERR_MISALIGNED;
   const size_t need = curl_trispace_bwd_workspace_bytes(B, H, W, degree, spatial);
   if (!workspace || workspace_bytes < need || !aligned16(workspace)) return CURL_ERR_WORKSPACE;
   const size_t tick_bytes = ((size_t)B * sizeof(unsigned) + 255) / 256 * 256;
   TParams p{};
   p.img = img; p.coef[0] = R; p.coef[1] = L; p.coef[2] = Hc; p.gout = gout;
   p.gcoef[0] = gR; p.gcoef[1] = gL; p.gcoef[2] = gH;
+  p.sig = const_cast<float*>(saved);
   p.tickets = reinterpret_cast<unsigned*>(workspace);
   p.partials = reinterpret_cast<float*>(reinterpret_cast<char*>(workspace) + tick_bytes);
   p.HW = H * W; p.W = W; p.H = H; p.clamp = final_clamp ? 1 : 0;

@@ -321,7 +321,7 @@ class TriSpaceFn(torch.autograd.Function):
     (model.py:517-519): asking for its gradient raises."""
 
     @staticmethod
-    def forward(ctx, img, R, L, H, degree, spatial, final_clamp):
+    def forward(ctx, img, R, L, H, degree, spatial, final_clamp, save_activations=True):
         lib = _lib.load()
         img = _image(img, "img")
         dev = img.device
@@ -336,12 +336,17 @@ class TriSpaceFn(torch.autograd.Function):
                                  % (nm, B, nc, degree, bool(spatial), tuple(P.shape)))
             coefs.append(P.contiguous())
         out = torch.empty_like(img)
+        # the nine sigmoid outputs (36 B/px): with them the backward evaluates no polynomial
+        saved = None
+        if save_activations and any(ctx.needs_input_grad[1:4]):
+            saved = torch.empty(B, 9, h, w, dtype=torch.float32, device=dev)
         with torch.cuda.device(dev):
             rc = lib.curl_trispace_fwd_f32(_ptr(img), _ptr(coefs[0]), _ptr(coefs[1]), _ptr(coefs[2]), degree,
-                                           int(spatial), int(final_clamp), _ptr(out), B, h, w, _stream(dev))
+                                           int(spatial), int(final_clamp), _ptr(out), _ptr(saved), B, h, w, _stream(dev))
         _lib.check(rc, "curl_trispace_fwd_f32")
         _lib.count_launch()
         ctx.save_for_backward(img, *coefs)
+        ctx.sig = saved
         ctx.cfg = (degree, int(spatial), int(final_clamp))
         return out
 
@@ -362,10 +367,12 @@ class TriSpaceFn(torch.autograd.Function):
         ws = torch.empty(n, dtype=torch.uint8, device=dev)
         with torch.cuda.device(dev):
             rc = lib.curl_trispace_bwd_f32(_ptr(img), _ptr(R), _ptr(L), _ptr(H), degree, spatial, final_clamp,
-                                           _ptr(gout), _ptr(gR), _ptr(gL), _ptr(gH), _ptr(ws), n, B, h, w, _stream(dev))
+                                           _ptr(gout), _ptr(ctx.sig), _ptr(gR), _ptr(gL), _ptr(gH), _ptr(ws), n, B, h, w,
+                                           _stream(dev))
         _lib.check(rc, "curl_trispace_bwd_f32")
         _lib.count_launch(2)
-        return None, gR, gL, gH, None, None, None
+        ctx.sig = None
+        return None, gR, gL, gH, None, None, None, None
 
 
 class LossTermsFn(torch.autograd.Function):

@@ -184,6 +184,9 @@ class TriSpaceRegNet(nn.Module):
             y = torch.arange(0, max_resolution).reshape(1, 1, max_resolution, 1)
         self.x = nn.Parameter(x, requires_grad=False)
         self.y = nn.Parameter(y, requires_grad=False)
+        # keep the nine sigmoid outputs (36 B/px) for the backward instead of recomputing the polynomials;
+        # set False when memory is tighter than time (the reference keeps ~1.5 KB/px for autograd)
+        self.save_activations = True
 
     def _fused(self, img, R, L, H, final_clamp):
         from .functional import TriSpaceFn
@@ -191,7 +194,7 @@ class TriSpaceRegNet(nn.Module):
             raise ValueError("img width and height must be less than `max_resolution` (%d)" % self.max_resolution)
         for m in (self.rgb2lab, self.lab2rgb, self.rgb2hsv, self.hsv2rgb):
             m._check_constants()
-        return TriSpaceFn.apply(img, R, L, H, self.order, self.spatial, final_clamp)
+        return TriSpaceFn.apply(img, R, L, H, self.order, self.spatial, final_clamp, self.save_activations)
 
     def generate_residual(self, img, R, L, H):                                                     # model.py:486-503
         return self._fused(img, R, L, H, False)

@@ -20,12 +20,14 @@ for (B, H, W) in SHAPES:
         gout = torch.randn(B, 3, H, W, generator=g, device=dev)
         out = torch.empty_like(img); gc = [torch.empty_like(c) for c in co]
         n = lib.curl_trispace_bwd_workspace_bytes(B, H, W, 4, spatial); ws = torch.empty(n, dtype=torch.uint8, device=dev)
+        sig = torch.empty(B, 9, H, W, device=dev) if os.environ.get('TB_SAVE', '1') == '1' else None
+        sig_ptr = None if sig is None else sig.data_ptr()
         def fwd():
-            assert lib.curl_trispace_fwd_f32(img.data_ptr(), co[0].data_ptr(), co[1].data_ptr(), co[2].data_ptr(), 4, spatial, 1, out.data_ptr(), B, H, W, st) == 0
+            assert lib.curl_trispace_fwd_f32(img.data_ptr(), co[0].data_ptr(), co[1].data_ptr(), co[2].data_ptr(), 4, spatial, 1, out.data_ptr(), sig_ptr, B, H, W, st) == 0
         def bwd():
-            assert lib.curl_trispace_bwd_f32(img.data_ptr(), co[0].data_ptr(), co[1].data_ptr(), co[2].data_ptr(), 4, spatial, 1, gout.data_ptr(),
+            assert lib.curl_trispace_bwd_f32(img.data_ptr(), co[0].data_ptr(), co[1].data_ptr(), co[2].data_ptr(), 4, spatial, 1, gout.data_ptr(), sig_ptr,
                                              gc[0].data_ptr(), gc[1].data_ptr(), gc[2].data_ptr(), ws.data_ptr(), n, B, H, W, st) == 0
-        res = {"shape": [B, H, W], "spatial": spatial, "nc": nc}
+        res = {"shape": [B, H, W], "spatial": spatial, "nc": nc, "saved": sig is not None}
         for name, fn in (("fwd", fwd), ("bwd", bwd)):
             for _ in range(2): fn()
             torch.cuda.synchronize()

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define CURL_ABI_VERSION 4
+#define CURL_ABI_VERSION 5
 
 /* error codes */
 #define CURL_OK 0
@@ -155,10 +155,14 @@ int curl_apply_curve_bwd_f32(const float* in, const float* C, int64_t ldC, int c
  * reference's [B, H, W, NC] monomial tensor (504 B/px per space) is never formed.
  * Only degree == 4 (the reference's polynomial_order default) is built; other degrees return
  * CURL_ERR_BAD_ARG.
+ * saved: NULL, or [B][9][H][W] receiving the nine sigmoid outputs (3 spaces x 3 channels) -- the only
+ * intermediate the backward needs besides the image.  Handing the same buffer to
+ * curl_trispace_bwd_f32 skips re-evaluating the three polynomials there (36 B/px of HBM for about
+ * 1.4x on the backward); with NULL the backward recomputes everything from the image.
  */
 int curl_trispace_num_coeffs(int degree, int spatial);
 int curl_trispace_fwd_f32(const float* img, const float* R, const float* L, const float* Hc,
-                          int degree, int spatial, int final_clamp, float* out,
+                          int degree, int spatial, int final_clamp, float* out, float* saved,
                           int B, int H, int W, void* stream);
 /*
  * Backward of the above w.r.t. the coefficients: gR, gL, gH [B][3][NC] dense, given gout[B][3][H][W].
@@ -170,7 +174,7 @@ int curl_trispace_fwd_f32(const float* img, const float* R, const float* L, cons
  */
 size_t curl_trispace_bwd_workspace_bytes(int B, int H, int W, int degree, int spatial);
 int curl_trispace_bwd_f32(const float* img, const float* R, const float* L, const float* Hc,
-                          int degree, int spatial, int final_clamp, const float* gout,
+                          int degree, int spatial, int final_clamp, const float* gout, const float* saved,
                           float* gR, float* gL, float* gH, void* workspace, size_t workspace_bytes,
                           int B, int H, int W, void* stream);
 

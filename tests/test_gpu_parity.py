@@ -412,9 +412,10 @@ def _tri_check(out, r32, r64, grads, g64):
         assert rel_to_max(v, g64[k]) <= 1e-4, k
 
 
+@pytest.mark.parametrize("save", [True, False])
 @pytest.mark.parametrize("clamp", [0, 1])
 @pytest.mark.parametrize("case", ["rgb", "spatial", "spatial_mobile", "uint8", "edges"])
-def test_trispace_vs_golden(case, clamp, trispace_golden):
+def test_trispace_vs_golden(case, clamp, save, trispace_golden):
     """Fused generate_residual (+ generate_image) forward and coefficient gradients against the
     fixtures the reference itself produced (model.py:486-508 through oracle/ref_loader)."""
     import curl_b200
@@ -423,6 +424,7 @@ def test_trispace_vs_golden(case, clamp, trispace_golden):
     dev = _dev()
     spatial = bool(g[f"{case}.spatial"])
     net = curl_b200.TriSpaceRegNet(spatial=spatial, backbone=nn.Identity()).to(dev)
+    net.save_activations = save      # backward from the saved sigmoid outputs, or recomputing the polynomials
     img = torch.from_numpy(g[f"{case}.img"]).to(dev)
     R, L, Hc = (torch.from_numpy(g[f"{case}.{k}"]).to(dev).requires_grad_(True) for k in ("R", "L", "H"))
     out = net.generate_residual(img, R, L, Hc) if not clamp else net._fused(img, R, L, Hc, True)
@@ -484,12 +486,14 @@ def test_trispace_deterministic_and_errors():
     gout = torch.randn(2, 3, 120, 200, generator=gen).to(dev)
     co = [(0.3 * torch.randn(2, 3, 126, generator=gen)).to(dev) for _ in range(3)]
     runs = []
-    for _ in range(2):
+    for save in (True, True, False):
+        net.save_activations = save
         a = [c.clone().requires_grad_(True) for c in co]
         net._fused(img, *a, True).backward(gout)
         runs.append([t.grad.clone() for t in a])
-    for x, y in zip(*runs):
+    for x, y, z in zip(*runs):
         assert torch.equal(x, y)                              # fixed-order reduction
+        assert torch.equal(x, z)                              # saved sigmoids == recomputed sigmoids, bit for bit
     with pytest.raises(ValueError, match="shape"):
         net.generate_residual(img, co[0][:, :, :35], co[1], co[2])
     with pytest.raises(RuntimeError, match="no image gradient"):
