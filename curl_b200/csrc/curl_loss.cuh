@@ -42,10 +42,17 @@ CURL_HD float vsqrt(float x) {
   return (float)sqrt((double)x);
 #endif
 }
+CURL_HD float vrsq(float x) {
+#if defined(__CUDA_ARCH__)
+  return __frsqrt_rn(x);
+#else
+  return (float)(1.0 / sqrt((double)x));
+#endif
+}
 CURL_HD float vabs(float x) { return fabsf(x); }
 CURL_HD float vsign(float x) { return x > 0.f ? 1.f : (x < 0.f ? -1.f : 0.f); }   // torch.sign: 0 at 0
 #if defined(__CUDACC__)
-CURL_F2_MAP1(vsin) CURL_F2_MAP1(vcos) CURL_F2_MAP1(vsqrt) CURL_F2_MAP1(vabs) CURL_F2_MAP1(vsign)
+CURL_F2_MAP1(vsin) CURL_F2_MAP1(vcos) CURL_F2_MAP1(vsqrt) CURL_F2_MAP1(vrsq) CURL_F2_MAP1(vabs) CURL_F2_MAP1(vsign)
 #endif
 
 template <class T>
@@ -66,15 +73,17 @@ CURL_HD ConeOf<T> hsv_cone(const T hsv[3]) {
 }
 
 // cosine_similarity of two 3-vectors the way ATen computes it: each vector divided by
-// max(norm, eps) first, then the dot product.
+// max(norm, eps) first, then the dot product.  1 / max(sqrt(n2), eps) == rsqrt(max(n2, eps^2)): one
+// MUFU.RSQ per vector instead of a square root and a reciprocal.  Returns the squared norm of p and
+// 1 / max(|p|, eps) for the backward.
 template <class T>
-CURL_HD T cos_sim3(const T p[3], const T t[3], T pn[3], T tn[3], T* np_out) {
-  const T np = vsqrt(vfma(p[2], p[2], vfma(p[1], p[1], vmul(p[0], p[0]))));
-  const T nt = vsqrt(vfma(t[2], t[2], vfma(t[1], t[1], vmul(t[0], t[0]))));
-  const T ip = vrcp(vmax(np, T(lk::COS_EPS))), it = vrcp(vmax(nt, T(lk::COS_EPS)));
+CURL_HD T cos_sim3(const T p[3], const T t[3], T pn[3], T tn[3], T* np2_out, T* ip_out) {
+  const T np2 = vfma(p[2], p[2], vfma(p[1], p[1], vmul(p[0], p[0])));
+  const T nt2 = vfma(t[2], t[2], vfma(t[1], t[1], vmul(t[0], t[0])));
+  const T ip = vrsq(vmax(np2, T(lk::COS_EPS * lk::COS_EPS))), it = vrsq(vmax(nt2, T(lk::COS_EPS * lk::COS_EPS)));
 #pragma unroll
   for (int c = 0; c < 3; ++c) { pn[c] = vmul(p[c], ip); tn[c] = vmul(t[c], it); }
-  *np_out = np;
+  *np2_out = np2; *ip_out = ip;
   return vfma(pn[2], tn[2], vfma(pn[1], tn[1], vmul(pn[0], tn[0])));
 }
 
@@ -85,8 +94,8 @@ CURL_HD void loss_terms_fwd(const T pred[3], const T target[3], T m, T s[4], T* 
 #pragma unroll
   for (int c = 0; c < 3; ++c) { p[c] = vmul(pred[c], m); t[c] = vmul(target[c], m); }
   s[0] = vadd(vadd(vabs(vsub(p[0], t[0])), vabs(vsub(p[1], t[1]))), vabs(vsub(p[2], t[2])));
-  T pn[3], tn[3], np;
-  s[1] = cos_sim3(p, t, pn, tn, &np);
+  T pn[3], tn[3], np2, ip;
+  s[1] = cos_sim3(p, t, pn, tn, &np2, &ip);
   T lp[3], lt[3];
   rgb2lab_fwd<T, false>(p, lp, nullptr);
   rgb2lab_fwd<T, false>(t, lt, nullptr);
@@ -113,10 +122,9 @@ CURL_HD void loss_terms_bwd(const T pred[3], const T target[3], T m, const float
   for (int c = 0; c < 3; ++c) g[c] = vmul(vsign(vsub(p[c], t[c])), T(w[0]));
   // cosine: cos = sum pn_c tn_c, pn = p / max(|p|, eps); clamp_min passes gradient where |p| >= eps
   {
-    T pn[3], tn[3], np;
-    const T cs = cos_sim3(p, t, pn, tn, &np);
-    const T big = vgate_le(T(lk::COS_EPS), np);             // 1 where the norm itself is used
-    const T ip = vrcp(vmax(np, T(lk::COS_EPS)));
+    T pn[3], tn[3], np2, ip;
+    const T cs = cos_sim3(p, t, pn, tn, &np2, &ip);
+    const T big = vgate_le(T(lk::COS_EPS * lk::COS_EPS), np2);   // 1 where the norm itself is used
     // d cos / d p_c = (tn_c - big * cos * p_c / |p|) / max(|p|, eps);  p_c/|p| == pn_c where big
     const T k = vmul(vmul(cs, big), T(w[1]));
 #pragma unroll

@@ -6,6 +6,8 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from curl_b200 import _lib as L
 lib = ctypes.CDLL(sys.argv[1] if len(sys.argv) > 1 and sys.argv[1].endswith(".so") else L.LIB_PATH)
 for name, (res, args) in L.SIGNATURES.items():
+    if not hasattr(lib, name):
+        continue        # a loss-only experiment build
     fn = getattr(lib, name); fn.restype = res; fn.argtypes = args
 dev = torch.device("cuda:0")
 st = torch.cuda.current_stream().cuda_stream
