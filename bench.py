@@ -389,8 +389,8 @@ def run_ours(args):
         extras["trispace_512_b32_spatial"] = {
             "fwd_ms": ms_f, "fwd_mpx_per_s": tpx / 1e6 / (ms_f / 1e3), "fwd_bwd_ms": ms_s,
             "fwd_bwd_mpx_per_s": tpx / 1e6 / (ms_s / 1e3),
-            "fwd_tflops_fp32": tpx * 3 * (126 + 2 * 3 * 126) / (ms_f / 1e3) / 1e12,
-            "what": "fused generate_residual + generate_image, degree 4, 5 variables; FMA-bound (2646 flop/px forward)"}
+            "fwd_tflops_fp32": tpx * 3 * 2 * 3 * 125 / (ms_f / 1e3) / 1e12,
+            "what": "fused generate_residual + generate_image, degree 4, 5 variables; FMA-bound (nested evaluation, 2250 flop/px forward); backward from the saved sigmoid outputs"}
         del ti, tg, tc
         # CURLLoss (model.py:36-118): fused colour terms (one forward + one backward kernel) and the whole
         # criterion step incl. library MS-SSIM, on the headline batch (pred = the layer's output)

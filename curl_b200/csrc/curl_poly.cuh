@@ -82,25 +82,34 @@ CURL_HD void mono_visit(const T* x, Vis& vis) {
 // shared-memory wavefronts (1134 per 64 pixels = exactly its measured 16.4 Gpx/s).
 struct alignas(16) Coef4 { float v[4]; };
 
-template <class T>
-struct PolyEval {
-  const Coef4* coef;
-  T acc[3];
-  template <int RANK>
-  CURL_HD void operator()(T m) {
-    const Coef4 cf = coef[RANK];
-    acc[0] = vfma(T(cf.v[0]), m, acc[0]);
-    acc[1] = vfma(T(cf.v[1]), m, acc[1]);
-    acc[2] = vfma(T(cf.v[2]), m, acc[2]);
+// Evaluation is nested (multivariate Horner) over the same tree the walk above follows:
+//   node(E) = coef[rank(E)] + sum_{v >= last variable of E} x_v * node(E + e_v),   p = node(0),
+// one multiply-add per non-constant monomial and output channel (3 * 125 for 126 coefficients)
+// instead of a multiply for the monomial plus three multiply-adds (4 * 125).
+template <class T, int NV, int LEFT, int V, int E0, int E1, int E2, int E3, int E4>
+struct HornerNode {
+  template <int v>
+  static CURL_HD void children(const T* x, const Coef4* coef, T acc[3]) {
+    if constexpr (v < NV) {
+      constexpr int F0 = E0 + (v == 0), F1 = E1 + (v == 1), F2_ = E2 + (v == 2), F3 = E3 + (v == 3), F4 = E4 + (v == 4);
+      T ch[3];
+      HornerNode<T, NV, LEFT - 1, v, F0, F1, F2_, F3, F4>::eval(x, coef, ch);
+      acc[0] = vfma(x[v], ch[0], acc[0]);
+      acc[1] = vfma(x[v], ch[1], acc[1]);
+      acc[2] = vfma(x[v], ch[2], acc[2]);
+      children<v + 1>(x, coef, acc);
+    }
+  }
+  static CURL_HD void eval(const T* x, const Coef4* coef, T acc[3]) {
+    const Coef4 cf = coef[mono_rank(NV, E0, E1, E2, E3, E4)];
+    acc[0] = T(cf.v[0]); acc[1] = T(cf.v[1]); acc[2] = T(cf.v[2]);
+    if constexpr (LEFT > 0) children<V>(x, coef, acc);
   }
 };
 
 template <class T, int NV, int DEG>
 CURL_HD void poly_eval(const T* x, const Coef4* coef, T out[3]) {
-  const Coef4 c0 = coef[0];
-  PolyEval<T> ev{coef, {T(c0.v[0]), T(c0.v[1]), T(c0.v[2])}};     // the constant term
-  mono_visit<T, NV, DEG>(x, ev);
-  out[0] = ev.acc[0]; out[1] = ev.acc[1]; out[2] = ev.acc[2];
+  HornerNode<T, NV, DEG, 0, 0, 0, 0, 0, 0>::eval(x, coef, out);
 }
 
 // sigmoid and its derivative from the value

@@ -15,7 +15,13 @@
 namespace curl {
 namespace tri {
 
-constexpr int THREADS = 256;
+#ifndef TRI_FWD_THREADS
+#define TRI_FWD_THREADS 256
+#endif
+#ifndef TRI_FWD_MIN_BLOCKS
+#define TRI_FWD_MIN_BLOCKS 2
+#endif
+constexpr int THREADS = TRI_FWD_THREADS;
 constexpr int DEG = 4;                       // the reference's polynomial_order default (model.py:413)
 constexpr int MAX_NC = poly_num_coeffs(5, DEG);
 
@@ -62,7 +68,7 @@ __device__ __forceinline__ void coords(int idx, int W, float fW, float fH, float
 // monomial walk wants its registers; VEC = 1: scalar path for odd HW or unaligned bases.
 // ---------------------------------------------------------------------------------------------
 template <int NV, int VEC, bool SAVE>
-__global__ void __launch_bounds__(THREADS, 2) trispace_fwd_kernel(const TParams p) {
+__global__ void __launch_bounds__(THREADS, TRI_FWD_MIN_BLOCKS) trispace_fwd_kernel(const TParams p) {
   constexpr int NC = poly_num_coeffs(NV, DEG);
   __shared__ Coef4 s_coef[3 * NC];
   const int b = blockIdx.y;

@@ -37,6 +37,6 @@ for (B, H, W) in SHAPES:
             e1.record(); torch.cuda.synchronize()
             ms = e0.elapsed_time(e1) / 5
             npx = B * H * W
-            flops = npx * (3 * (nc + 2 * 3 * nc)) * (1 if name == "fwd" else 2)      # monomials + 3 outputs, x2 for the gradient product
+            flops = npx * (3 * 2 * 3 * (nc - 1)) if name == "fwd" else npx * 3 * (nc + 2 * 3 * nc)   # nested evaluation: one FMA per coefficient and channel; backward: monomials + the gradient product
             res[name + "_ms"] = round(ms, 3); res[name + "_Gpx"] = round(npx / ms / 1e6, 2); res[name + "_TFLOPs"] = round(flops / ms / 1e9, 2)
         print(json.dumps(res), flush=True)

@@ -643,3 +643,33 @@ def test_loss_training_step_through_layer():
     assert abs(float(loss.detach()) - float(ref_loss.detach())) <= 1e-5
     for k, r in zip(kg, ref_g):
         assert rel_to_max(k.grad.cpu().numpy(), r.numpy()) <= 1e-4
+
+
+def test_loss_full_size_properties():
+    """BASELINE-size images (4K): properties that need no oracle.  pred == target makes the three L1
+    sums exactly zero and the colour-term gradient exactly zero; per-image sums do not depend on
+    what else is in the batch (to reduction-order tolerance); masked pixels never receive gradient."""
+    from curl_b200 import functional
+    dev = _dev()
+    B, H, W = 3, 2160, 3840
+    gen = torch.Generator(device=dev).manual_seed(4)
+    target = torch.rand(B, 3, H, W, generator=gen, device=dev)
+    pred = (target + 0.05 * torch.randn(B, 3, H, W, generator=gen, device=dev)).clamp_(0, 1)
+    mask = torch.rand(B, 1, H, W, generator=gen, device=dev) > 0.1
+    same, Lp, Lt = functional.loss_terms(target, target, mask)
+    assert torch.all(same[:, [0, 2, 3]] == 0) and torch.equal(Lp, Lt)
+    assert torch.equal(same[:, 4], mask.sum(dim=(1, 2, 3)).float())
+    assert torch.all((same[:, 1] - same[:, 4]).abs() <= 1e-5 * same[:, 4])          # cos == 1 on unmasked (non-black) pixels
+    t = target.clone().requires_grad_(True)
+    s, lp, _ = functional.loss_terms(t, target, mask)
+    torch.autograd.backward([s], [torch.tensor([[1.0, 0.0, 1.0, 1.0, 0.0]], device=dev).expand(B, 5).contiguous()])
+    assert torch.count_nonzero(t.grad) == 0                                           # sign(0) == 0 everywhere
+    whole, _, _ = functional.loss_terms(pred, target, mask)
+    for b in range(B):
+        one, _, _ = functional.loss_terms(pred[b:b + 1], target[b:b + 1], mask[b:b + 1])
+        assert torch.all((one[0] - whole[b]).abs() <= 2e-6 * whole[b].abs().clamp(min=1.0)), b
+    p = pred.clone().requires_grad_(True)
+    s, lp, _ = functional.loss_terms(p, target, mask)
+    (s.sum() + lp.sum()).backward()
+    assert torch.count_nonzero(p.grad * (~mask)) == 0
+    assert torch.isfinite(p.grad).all()
