@@ -77,10 +77,11 @@ def _workspace(B, H, W, dev):
 
 
 class CurlLayerFn(torch.autograd.Function):
-    """Fused CURLLayer.forward (reference model.py:137-176) and its recompute backward."""
+    """Fused CURLLayer.forward (reference model.py:137-176) and its recompute backward.
+    segment_clamp=True selects the opt-in curves of the CURL paper's eq. (1) (curl_layer_seg_*)."""
 
     @staticmethod
-    def forward(ctx, img, mask, L, R, H, k_lab, k_rgb, k_hsv):
+    def forward(ctx, img, mask, L, R, H, k_lab, k_rgb, k_hsv, segment_clamp=False):
         lib = _lib.load()
         img = _image(img, "img")
         dev = img.device
@@ -94,13 +95,15 @@ class CurlLayerFn(torch.autograd.Function):
         mask, kind = _mask(mask, img)
         out = torch.empty_like(img)
         reg = torch.empty(B, dtype=torch.float32, device=dev)
+        fwd = lib.curl_layer_seg_fwd_f32 if segment_clamp else lib.curl_layer_fwd_f32
         with torch.cuda.device(dev):
-            rc = lib.curl_layer_fwd_f32(_ptr(img), _ptr(mask), kind, _ptr(L), ldL, _ptr(R), ldR, _ptr(H), ldH,
-                                        _ptr(out), _ptr(reg), B, h, w, k_lab, k_rgb, k_hsv, _stream(dev))
-        _lib.check(rc, "curl_layer_fwd_f32")
+            rc = fwd(_ptr(img), _ptr(mask), kind, _ptr(L), ldL, _ptr(R), ldR, _ptr(H), ldH,
+                     _ptr(out), _ptr(reg), B, h, w, k_lab, k_rgb, k_hsv, _stream(dev))
+        _lib.check(rc, "curl_layer_seg_fwd_f32" if segment_clamp else "curl_layer_fwd_f32")
         _lib.count_launch()
         ctx.save_for_backward(img, mask, L, R, H)
         ctx.cfg = (kind, ldL, ldR, ldH, k_lab, k_rgb, k_hsv)
+        ctx.segment_clamp = bool(segment_clamp)
         return out, reg
 
     @staticmethod
@@ -118,12 +121,18 @@ class CurlLayerFn(torch.autograd.Function):
         gL = torch.empty(B, 3 * k_lab, dtype=torch.float32, device=dev)
         gR = torch.empty(B, 3 * k_rgb, dtype=torch.float32, device=dev)
         gH = torch.empty(B, 4 * k_hsv, dtype=torch.float32, device=dev)
-        ws, ws_bytes = _workspace(B, h, w, dev)
+        if ctx.segment_clamp:
+            ws_bytes = lib.curl_layer_seg_bwd_workspace_bytes(B, h, w, k_lab, k_rgb, k_hsv)
+            ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+            bwd, what = lib.curl_layer_seg_bwd_f32, "curl_layer_seg_bwd_f32"
+        else:
+            ws, ws_bytes = _workspace(B, h, w, dev)
+            bwd, what = lib.curl_layer_bwd_f32, "curl_layer_bwd_f32"
         with torch.cuda.device(dev):
-            rc = lib.curl_layer_bwd_f32(_ptr(img), _ptr(mask), kind, _ptr(L), ldL, _ptr(R), ldR, _ptr(H), ldH,
-                                        _ptr(gout), _ptr(greg), _ptr(gimg), _ptr(gL), _ptr(gR), _ptr(gH),
-                                        _ptr(ws), ws_bytes, B, h, w, k_lab, k_rgb, k_hsv, _stream(dev))
-        _lib.check(rc, "curl_layer_bwd_f32")
+            rc = bwd(_ptr(img), _ptr(mask), kind, _ptr(L), ldL, _ptr(R), ldR, _ptr(H), ldH,
+                     _ptr(gout), _ptr(greg), _ptr(gimg), _ptr(gL), _ptr(gR), _ptr(gH),
+                     _ptr(ws), ws_bytes, B, h, w, k_lab, k_rgb, k_hsv, _stream(dev))
+        _lib.check(rc, what)
         _lib.count_launch()
 
         def widen(g, P):
@@ -134,7 +143,7 @@ class CurlLayerFn(torch.autograd.Function):
             full[:, :g.shape[1]] = g
             return full
 
-        return gimg, None, widen(gL, L), widen(gR, R), widen(gH, H), None, None, None
+        return gimg, None, widen(gL, L), widen(gR, R), widen(gH, H), None, None, None, None
 
 
 class ColorFn(torch.autograd.Function):

@@ -13,10 +13,16 @@ class CURLLayer(nn.Module):
 
     Only the leading num_lab_points / num_rgb_points / num_hsv_points columns of L / R / H are read
     (model.py:153,159,165); K = points / 3 (Lab, RGB) or / 4 (HSV) knots per curve.
+
+    segment_clamp=True (not in the reference; default False) evaluates the curves as eq. (1) of the
+    CURL paper defines them -- piecewise linear through all K knots, each segment term clamped to
+    [0, 1] -- instead of the reference's unclamped sum (curves.py:29-32), through the
+    curl_layer_seg_* kernels.
     """
 
-    def __init__(self, num_lab_points=48, num_rgb_points=48, num_hsv_points=64):
+    def __init__(self, num_lab_points=48, num_rgb_points=48, num_hsv_points=64, segment_clamp=False):
         super().__init__()
+        self.segment_clamp = bool(segment_clamp)
         if num_lab_points % 3 or num_rgb_points % 3 or num_hsv_points % 4:
             raise ValueError("num_lab_points and num_rgb_points must be multiples of 3, num_hsv_points of 4")
         if num_lab_points < 9 or num_rgb_points < 9 or num_hsv_points < 12:
@@ -41,7 +47,7 @@ class CURLLayer(nn.Module):
         for m in (self.rgb2lab, self.lab2rgb, self.rgb2hsv, self.hsv2rgb):
             m._check_constants()
         return CurlLayerFn.apply(img, mask, L, R, H, self.num_lab_points // 3, self.num_rgb_points // 3,
-                                 self.num_hsv_points // 4)
+                                 self.num_hsv_points // 4, self.segment_clamp)
 
 
 class GCURLNet(nn.Module):

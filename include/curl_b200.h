@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define CURL_ABI_VERSION 5
+#define CURL_ABI_VERSION 6
 
 /* error codes */
 #define CURL_OK 0
@@ -208,6 +208,32 @@ int curl_loss_terms_fwd_f32(const float* pred, const float* target, const void* 
 int curl_loss_terms_bwd_f32(const float* pred, const float* target, const void* mask, int mask_kind,
                             const float* w, const float* gL_pred, float* gpred,
                             int B, int H, int W, void* stream);
+
+/*
+ * Opt-in: the layer with SEGMENT-CLAMPED curves -- eq. (1) of the CURL paper (arXiv 1911.13175),
+ *   scale(x) = k_0 + sum_{i=0}^{K-2} (k_{i+1} - k_i) * clamp((K-1) x - i, 0, 1),
+ * the piecewise-linear curve through all K knots.  This is NOT what the reference evaluates
+ * (curves.py:29-32 sums the unclamped terms and leaves the last slope out, which is affine in x);
+ * everything else -- curve wiring, whole-pixel clamps, regulariser, layer chain, arguments -- is as
+ * in curl_layer_fwd_f32 / curl_layer_bwd_f32 above.  Scalar kernels (the segment is a per-pixel
+ * lookup); knot gradients are a per-segment reduction through per-warp shared-memory histograms
+ * (float atomics: last bits are not run-to-run reproducible), then partial rows + ticket + a
+ * fixed-order fold in double.  No reference code exists for this variant: checked against the
+ * oracle's restatement of the published formula only (parity unpinned).
+ */
+int curl_layer_seg_fwd_f32(const float* img, const void* mask, int mask_kind,
+                           const float* L, int64_t ldL, const float* R, int64_t ldR,
+                           const float* Hk, int64_t ldH,
+                           float* out, float* reg,
+                           int B, int H, int W, int K_lab, int K_rgb, int K_hsv, void* stream);
+size_t curl_layer_seg_bwd_workspace_bytes(int B, int H, int W, int K_lab, int K_rgb, int K_hsv);
+int curl_layer_seg_bwd_f32(const float* img, const void* mask, int mask_kind,
+                           const float* L, int64_t ldL, const float* R, int64_t ldR,
+                           const float* Hk, int64_t ldH,
+                           const float* gout, const float* greg,
+                           float* gimg, float* gL, float* gR, float* gH,
+                           void* workspace, size_t workspace_bytes,
+                           int B, int H, int W, int K_lab, int K_rgb, int K_hsv, void* stream);
 
 #ifdef __cplusplus
 }

@@ -182,58 +182,70 @@ def hsv2rgb(img):
 # Knot curves
 # ---------------------------------------------------------------------------------------------
 
-def apply_curve(img, C, reg, channel_in, channel_out):
-    """curves.py:4-38.  NB: no per-segment clamp -- the scale is affine in the pixel."""
+def apply_curve(img, C, reg, channel_in, channel_out, segment_clamp=False):
+    """curves.py:4-38.  NB: no per-segment clamp -- the scale is affine in the pixel.
+
+    segment_clamp=True is NOT the reference: it is eq. (1) of the CURL paper (arXiv 1911.13175),
+        scale = k_0 + sum_{i=0}^{K-2} (k_{i+1} - k_i) * clamp((K-1) x - i, 0, 1),
+    the piecewise-linear curve through all K knots, which the reference code dropped (it sums the
+    unclamped terms and leaves the last slope out).  PARITY UNPINNED for this flag: there is no
+    reference code to execute; this restatement of the published formula is the only checker."""
     steps_n = C.shape[1] - 1                                                       # curves.py:14
     slope = C[:, 1:] - C[:, 0:-1]                                                  # curves.py:19
     reg = reg + ((slope[:, 1:] - slope[:, 0:-1]) ** 2).sum(1)                      # curves.py:24
-    idx = torch.arange(0, slope.shape[1] - 1, device=img.device)                   # curves.py:29
     chan = torch.unsqueeze(img[:, channel_in, :, :], 1)                            # curves.py:30
-    scale = C[:, 0].reshape(-1, 1, 1) + (
-        slope[:, :-1].reshape(slope.shape[0], slope.shape[1] - 1, 1, 1)
-        * (steps_n * chan - idx.reshape(1, idx.shape[0], 1, 1))).sum(1)           # curves.py:31-32
+    if segment_clamp:
+        idx = torch.arange(0, slope.shape[1], device=img.device)
+        scale = C[:, 0].reshape(-1, 1, 1) + (
+            slope.reshape(slope.shape[0], slope.shape[1], 1, 1)
+            * torch.clamp(steps_n * chan - idx.reshape(1, idx.shape[0], 1, 1), 0.0, 1.0)).sum(1)
+    else:
+        idx = torch.arange(0, slope.shape[1] - 1, device=img.device)               # curves.py:29
+        scale = C[:, 0].reshape(-1, 1, 1) + (
+            slope[:, :-1].reshape(slope.shape[0], slope.shape[1] - 1, 1, 1)
+            * (steps_n * chan - idx.reshape(1, idx.shape[0], 1, 1))).sum(1)       # curves.py:31-32
     out = img.clone()                                                              # curves.py:34
     out[:, channel_out, :, :] = img[:, channel_out, :, :] * scale                  # curves.py:35
     return torch.clamp(out, 0.0, 1.0), reg                                         # curves.py:36-38
 
 
-def _adjust(img, P, wiring):
+def _adjust(img, P, wiring, segment_clamp=False):
     img = img.contiguous()
     knots = [torch.exp(p) for p in torch.chunk(P, len(wiring), dim=1)]             # curves.py:53-54 etc.
     reg = 0.0
     for C, (cin, cout) in zip(knots, wiring):
-        img, reg = apply_curve(img, C, reg, cin, cout)
+        img, reg = apply_curve(img, C, reg, cin, cout, segment_clamp)
     return img.clone().contiguous(), reg
 
 
-def adjust_lab(img, L):
+def adjust_lab(img, L, segment_clamp=False):
     """curves.py:136-180: three curves, channel c -> c."""
-    return _adjust(img, L, ((0, 0), (1, 1), (2, 2)))
+    return _adjust(img, L, ((0, 0), (1, 1), (2, 2)), segment_clamp)
 
 
-def adjust_rgb(img, R):
+def adjust_rgb(img, R, segment_clamp=False):
     """curves.py:90-133: three curves, channel c -> c."""
-    return _adjust(img, R, ((0, 0), (1, 1), (2, 2)))
+    return _adjust(img, R, ((0, 0), (1, 1), (2, 2)), segment_clamp)
 
 
-def adjust_hsv(img, S):
+def adjust_hsv(img, S, segment_clamp=False):
     """curves.py:41-87: hue<-f(hue), sat<-f(adjusted hue), sat<-f(sat), val<-f(val)."""
-    return _adjust(img, S, ((0, 0), (0, 1), (1, 1), (2, 2)))
+    return _adjust(img, S, ((0, 0), (0, 1), (1, 1), (2, 2)), segment_clamp)
 
 
 # ---------------------------------------------------------------------------------------------
 # The layer (model.py:137-176 without the three dead `feat` lines)
 # ---------------------------------------------------------------------------------------------
 
-def curl_layer(img, mask, L, R, H, num_lab_points=48, num_rgb_points=48, num_hsv_points=64):
+def curl_layer(img, mask, L, R, H, num_lab_points=48, num_rgb_points=48, num_hsv_points=64, segment_clamp=False):
     lab = rgb2lab(img)                                                             # model.py:151
-    lab, reg_lab = adjust_lab(lab, L[:, :num_lab_points])                          # model.py:153
+    lab, reg_lab = adjust_lab(lab, L[:, :num_lab_points], segment_clamp)           # model.py:153
     lab = lab * mask                                                               # model.py:154
     rgb = lab2rgb(lab)                                                             # model.py:157
-    rgb, reg_rgb = adjust_rgb(rgb, R[:, :num_rgb_points])                          # model.py:159
+    rgb, reg_rgb = adjust_rgb(rgb, R[:, :num_rgb_points], segment_clamp)           # model.py:159
     rgb = rgb * mask                                                               # model.py:160
     hsv = rgb2hsv(rgb)                                                             # model.py:163
-    hsv, reg_hsv = adjust_hsv(hsv, H[:, :num_hsv_points])                          # model.py:165
+    hsv, reg_hsv = adjust_hsv(hsv, H[:, :num_hsv_points], segment_clamp)           # model.py:165
     hsv = hsv * mask                                                               # model.py:166
     res = hsv2rgb(hsv)                                                             # model.py:169
     out = torch.clamp(img + res, 0.0, 1.0) * mask                                  # model.py:170

@@ -12,6 +12,7 @@ HDR = os.path.join(HERE, "..", "..", "curl_b200", "csrc", "curl_pixel.cuh")
 HDR2 = os.path.join(HERE, "..", "..", "curl_b200", "csrc", "curl_vec.cuh")
 HDR3 = os.path.join(HERE, "..", "..", "curl_b200", "csrc", "curl_poly.cuh")
 HDR4 = os.path.join(HERE, "..", "..", "curl_b200", "csrc", "curl_loss.cuh")
+HDR5 = os.path.join(HERE, "..", "..", "curl_b200", "csrc", "curl_seg.cuh")
 OUT = os.path.join(HERE, "_build", "libpixel_sim.so")
 
 _lib = None
@@ -21,7 +22,7 @@ def lib():
     global _lib
     if _lib is not None:
         return _lib
-    newest = max(os.path.getmtime(SRC), os.path.getmtime(HDR), os.path.getmtime(HDR2), os.path.getmtime(HDR3), os.path.getmtime(HDR4))
+    newest = max(os.path.getmtime(SRC), os.path.getmtime(HDR), os.path.getmtime(HDR2), os.path.getmtime(HDR3), os.path.getmtime(HDR4), os.path.getmtime(HDR5))
     if not os.path.exists(OUT) or os.path.getmtime(OUT) < newest:
         os.makedirs(os.path.dirname(OUT), exist_ok=True)
         subprocess.check_call(["g++", "-O2", "-std=c++17", "-shared", "-fPIC", "-o", OUT, SRC])
@@ -139,3 +140,22 @@ def loss_terms(pred, target, mask, w=None, gL=None):
     rc = lib().sim_loss_terms(1, _f(pred), _f(target), _f(m), None, None, None, _f(w), _f(gL), _f(gpred), B, h * wd)
     assert rc == 0
     return gpred
+
+
+def layer_seg(img, mask, L, R, H, pts=(48, 48, 64), gout=None, greg=None):
+    """Segment-clamped layer.  Returns dict(out, reg) or, when gout is given, dict(gimg, gL, gR, gH)."""
+    img = _c(img)
+    B, _, h, w = img.shape
+    Kl, Kr, Kh = pts[0] // 3, pts[1] // 3, pts[2] // 4
+    knots = _c(np.concatenate([np.asarray(L)[:, :pts[0]], np.asarray(R)[:, :pts[1]], np.asarray(H)[:, :pts[2]]], axis=1))
+    m = None if mask is None else _c(np.broadcast_to(np.asarray(mask, dtype=np.float32), (B, 1, h, w)))
+    if gout is None:
+        out = np.empty_like(img); reg = np.empty(B, np.float32)
+        rc = lib().sim_layer_seg(0, _f(img), _f(m), _f(knots), Kl, Kr, Kh, _f(out), _f(reg), None, None, None, None, B, h * w)
+        assert rc == 0
+        return dict(out=out, reg=reg)
+    gout = _c(gout); greg = _c(greg)
+    gimg = np.empty_like(img); gk = np.empty_like(knots)
+    rc = lib().sim_layer_seg(1, _f(img), _f(m), _f(knots), Kl, Kr, Kh, None, None, _f(gout), _f(greg), _f(gimg), _f(gk), B, h * w)
+    assert rc == 0
+    return dict(gimg=gimg, gL=gk[:, :pts[0]], gR=gk[:, pts[0]:pts[0] + pts[1]], gH=gk[:, pts[0] + pts[1]:])

@@ -15,6 +15,7 @@
 #include "../../curl_b200/csrc/curl_pixel.cuh"
 #include "../../curl_b200/csrc/curl_poly.cuh"
 #include "../../curl_b200/csrc/curl_loss.cuh"
+#include "../../curl_b200/csrc/curl_seg.cuh"
 
 using namespace curl;
 
@@ -255,6 +256,54 @@ int sim_loss_terms(int do_bwd, const float* pred, const float* target, const flo
       }
     }
     if (!do_bwd) for (int k = 0; k < 5; ++k) sums[b * 5 + k] = (float)acc[k];
+  }
+  return 0;
+}
+
+// Segment-clamped layer (curl_seg.cuh), host instantiation with double bins.  knots: per image the
+// 10 curves' log-domain parameters, concatenated [3*Kl | 3*Kr | 4*Kh]; mask: float or null.
+struct HostBins {
+  double* A; double* B; const int* off;
+  void add(int curve, int j, float a, float b) { A[off[curve] + j] += (double)a; B[off[curve] + j] += (double)b; }
+};
+int sim_layer_seg(int do_bwd, const float* img, const float* mask, const float* knots, int Kl, int Kr, int Kh,
+                  float* out, float* reg, const float* gout, const float* greg, float* gimg, float* gknots, int B, int HW) {
+  const int Ks[10] = {Kl, Kl, Kl, Kr, Kr, Kr, Kh, Kh, Kh, Kh};
+  int off[11]; off[0] = 0;
+  for (int k = 0; k < 10; ++k) off[k + 1] = off[k] + Ks[k];
+  const int NK = off[10];
+  std::vector<float> C(NK);
+  std::vector<double> A(NK), Bv(NK);
+  for (int b = 0; b < B; ++b) {
+    for (int i = 0; i < NK; ++i) C[i] = (float)exp((double)knots[(size_t)b * NK + i]);
+    SegCurve cv[10];
+    for (int k = 0; k < 10; ++k) cv[k] = SegCurve{C.data() + off[k], Ks[k]};
+    std::fill(A.begin(), A.end(), 0.0); std::fill(Bv.begin(), Bv.end(), 0.0);
+    HostBins bins{A.data(), Bv.data(), off};
+    for (int i = 0; i < HW; ++i) {
+      const float x[3] = {img[((size_t)b * 3 + 0) * HW + i], img[((size_t)b * 3 + 1) * HW + i], img[((size_t)b * 3 + 2) * HW + i]};
+      const float m = mask ? mask[(size_t)b * HW + i] : 1.0f;
+      if (!do_bwd) {
+        float y[3];
+        if (mask) seg_layer_fwd<MASK_F32>(x, m, cv, y); else seg_layer_fwd<MASK_NONE>(x, m, cv, y);
+        for (int c = 0; c < 3; ++c) out[((size_t)b * 3 + c) * HW + i] = y[c];
+      } else {
+        const float g[3] = {gout[((size_t)b * 3 + 0) * HW + i], gout[((size_t)b * 3 + 1) * HW + i], gout[((size_t)b * 3 + 2) * HW + i]};
+        float gx[3];
+        if (mask) seg_layer_bwd<MASK_F32, true>(x, m, cv, g, gx, bins); else seg_layer_bwd<MASK_NONE, true>(x, m, cv, g, gx, bins);
+        for (int c = 0; c < 3; ++c) gimg[((size_t)b * 3 + c) * HW + i] = gx[c];
+      }
+    }
+    if (!do_bwd) {
+      double r = 0.0;
+      for (int k = 0; k < 10; ++k) r += curve_regulariser(C.data() + off[k], Ks[k]);
+      reg[b] = (float)r;
+    } else {
+      for (int k = 0; k < 10; ++k)
+        for (int i = 0; i < Ks[k]; ++i)
+          gknots[(size_t)b * NK + off[k] + i] = seg_knot_grad(C.data() + off[k], Ks[k], i, A.data() + off[k], Bv.data() + off[k],
+                                                              greg ? (double)greg[b] : 0.0, true);
+    }
   }
   return 0;
 }

@@ -141,3 +141,27 @@ def test_hostsim_loss_terms_vs_golden(case, loss_golden):
     gp = hostsim.loss_terms(pred, target, mask, w=gs[:, :4].numpy(), gL=gL.numpy())
     r32, r64 = g[f"{case}.f32.gpred"], g[f"{case}.f64.gpred"]
     assert rel_to_max(gp, r64) <= max(1e-4, 3 * rel_to_max(r32, r64)), case
+
+
+@pytest.mark.parametrize("shape,sigma,masked", [((2, 24, 32), 0.1, True), ((1, 17, 19), 0.1, False), ((2, 16, 16), 0.3, True)])
+def test_hostsim_segment_clamp_vs_oracle(shape, sigma, masked):
+    """Per-pixel math of the opt-in segment-clamped layer (curl_seg.cuh: segment lookup, tie
+    semantics at knots, binned knot gradients) against the oracle's restatement of the paper's
+    eq. (1) with autograd.  No reference code exists for this flag (parity unpinned)."""
+    B, H, W = shape
+    gen = torch.Generator().manual_seed(B * H + W)
+    img = torch.rand(B, 3, H, W, generator=gen)
+    mask = (torch.rand(B, 1, H, W, generator=gen) > 0.15) if masked else None
+    L, R, Hk = (sigma * torch.randn(B, n, generator=gen) for n in (48, 48, 64))
+    gout, greg = torch.randn(B, 3, H, W, generator=gen), torch.randn(B, generator=gen)
+    om = mask if masked else torch.ones(B, 1, H, W, dtype=torch.bool)
+    r64 = O.curl_layer_fwd_bwd(img.double(), om, L.double(), R.double(), Hk.double(), gout.double(), greg.double(), segment_clamp=True)
+    r32 = O.curl_layer_fwd_bwd(img, om, L, R, Hk, gout, greg, segment_clamp=True)
+    m_np = None if mask is None else mask.numpy()
+    f = hostsim.layer_seg(img.numpy(), m_np, L.numpy(), R.numpy(), Hk.numpy())
+    b = hostsim.layer_seg(img.numpy(), m_np, L.numpy(), R.numpy(), Hk.numpy(), gout=gout.numpy(), greg=greg.numpy())
+    own = float((r32["out"].double() - r64["out"]).abs().max())
+    assert np.abs(f["out"] - r64["out"].numpy()).max() <= max(2e-5, 3 * own)
+    assert rel_to_max(f["reg"], r64["reg"].numpy()) <= 1e-5
+    for k in ("gimg", "gL", "gR", "gH"):
+        assert rel_to_max(b[k], r64[k].numpy()) <= max(1e-4, 3 * rel_to_max(r32[k].numpy(), r64[k].numpy())), k
