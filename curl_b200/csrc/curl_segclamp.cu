@@ -35,6 +35,7 @@ struct SParams {
   float* partials;       // bwd: [B][gridDim.x][2*NK]
   unsigned* tickets;     // bwd: [B]
   int HW;
+  int rep;               // bwd: histogram copies per warp (lane % rep picks one): divides same-bin conflicts
 };
 
 __host__ __device__ inline int total_knots(const int K[3]) { return 3 * K[0] + 3 * K[1] + 4 * K[2]; }
@@ -98,7 +99,7 @@ __global__ void __launch_bounds__(THREADS) seg_fwd_kernel(const SParams p) {
 }
 
 struct WarpBins {
-  float* A;          // this warp's histogram: A[NK], then B[NK]
+  float* A;          // this lane's copy of its warp's histogram: A[NK], then B[NK]
   float* B;
   const int* off;
   __device__ __forceinline__ void add(int curve, int j, float a, float b) {
@@ -117,13 +118,16 @@ __global__ void __launch_bounds__(THREADS) seg_bwd_kernel(const SParams p) {
   const int NK = total_knots(p.K), NB = 2 * NK;
   double* s_bins = reinterpret_cast<double*>(smem);          // [NB], used by the image's last block
   float* s_C = smem + 2 * NB;                                // [NK]
-  float* s_hist = s_C + NK;                                  // [NWARPS][NB]
+  float* s_hist = s_C + NK;                                  // [NWARPS * rep][NB]
+  const int NH = NWARPS * p.rep;
   const int b = blockIdx.y, HW = p.HW;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   SegCurve cv[LAYER_CURVES];
-  for (int i = threadIdx.x; i < NWARPS * NB; i += THREADS) s_hist[i] = 0.0f;
+  for (int i = threadIdx.x; i < NH * NB; i += THREADS) s_hist[i] = 0.0f;
   stage(p, b, s_C, s_off, cv);                               // ends with a barrier
-  WarpBins bins{s_hist + warp * NB, s_hist + warp * NB + NK, s_off};
+  // smooth images put most lanes of a warp in the same segment; lane % rep spreads them over rep copies
+  float* mine = s_hist + (size_t)(warp * p.rep + lane % p.rep) * NB;
+  WarpBins bins{mine, mine + NK, s_off};
   const float* in = p.img + (size_t)b * 3 * HW;
   const float* go = p.gout + (size_t)b * 3 * HW;
   float* gin = WANT_GIN ? p.gimg + (size_t)b * 3 * HW : nullptr;
@@ -143,8 +147,7 @@ __global__ void __launch_bounds__(THREADS) seg_bwd_kernel(const SParams p) {
   float* row = p.partials + ((size_t)b * gridDim.x + blockIdx.x) * NB;
   for (int k = threadIdx.x; k < NB; k += THREADS) {
     float v = 0.0f;
-#pragma unroll
-    for (int w = 0; w < NWARPS; ++w) v += s_hist[w * NB + k];
+    for (int w = 0; w < NH; ++w) v += s_hist[w * NB + k];
     row[k] = v;
   }
   __threadfence();
@@ -188,7 +191,13 @@ static int grid_x(int B, int HW, int blocks_per_sm) {
 }
 static size_t tick_bytes(int B) { return ((size_t)B * sizeof(unsigned) + 255) / 256 * 256; }
 static size_t fwd_smem(int NK) { return (size_t)NK * sizeof(float); }
-static size_t bwd_smem(int NK) { return ((size_t)4 * NK + NK + (size_t)NWARPS * 2 * NK) * sizeof(float); }
+static size_t bwd_smem(int NK, int rep) { return ((size_t)4 * NK + NK + (size_t)NWARPS * rep * 2 * NK) * sizeof(float); }
+// as many histogram copies per warp as fit in 100 KB per block (two blocks per SM): 8 at the default 160 knots
+static int hist_copies(int NK) {
+  int rep = 8;
+  while (rep > 1 && bwd_smem(NK, rep) > 100 * 1024) rep >>= 1;
+  return rep;
+}
 constexpr int BWD_BLOCKS_PER_SM = 4;
 
 static int fill(SParams& p, const float* img, const void* mask, int mask_kind, const float* L, int64_t ldL,
@@ -212,13 +221,14 @@ static int fill(SParams& p, const float* img, const void* mask, int mask_kind, c
 }
 
 template <int MK>
-static int launch_bwd(const SParams& p, int B, cudaStream_t st) {
+static int launch_bwd(SParams& p, int B, cudaStream_t st) {
   const int NK = total_knots(p.K);
+  p.rep = hist_copies(NK);
   const dim3 grid(grid_x(B, p.HW, BWD_BLOCKS_PER_SM), B);
   auto kern = p.gimg ? seg_bwd_kernel<MK, true> : seg_bwd_kernel<MK, false>;
-  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_smem(NK)) != cudaSuccess)
+  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_smem(NK, p.rep)) != cudaSuccess)
     return CURL_ERR_LAUNCH;
-  kern<<<grid, THREADS, bwd_smem(NK), st>>>(p);
+  kern<<<grid, THREADS, bwd_smem(NK, p.rep), st>>>(p);
   return cudaGetLastError() == cudaSuccess ? CURL_OK : CURL_ERR_LAUNCH;
 }
 
