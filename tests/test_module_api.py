@@ -21,6 +21,9 @@ def test_state_dict_matches_reference_layout():
     assert all(not p.requires_grad for p in layer.parameters())
     assert (layer.num_lab_points, layer.num_rgb_points, layer.num_hsv_points) == (48, 48, 64)
     assert curl_b200.CURLLayer(30, 18, 40).num_hsv_points == 40
+    # the opt-in paper curves are off by default and add no state
+    assert layer.segment_clamp is False and curl_b200.CURLLayer(segment_clamp=True).segment_clamp is True
+    assert list(curl_b200.CURLLayer(segment_clamp=True).state_dict()) == list(layer.state_dict())
 
 
 def test_strict_load_and_legacy_matrix_conversion():
