@@ -159,7 +159,11 @@ CURL_HD void rgb2lab_fwd(const T x[3], T lab[3], LabJac<T>* jac) {
     f[c] = vsel_le(t[c], T(k::F_T), vfma(t[c], T(k::F_SLOPE), T(k::F_OFF)), cr);
     if (JAC) jac->d_f[c] = vsel_le(t[c], T(k::F_T), T(k::F_SLOPE_X3), e);                      // 3 (d f / d t)
   }
-  lab[0] = vfma(f[1], T(k::LN_S), T(k::LN_O));               // colors.py:50,57
+  // colors.py:50,57: (116 fy - 16) / 100 = 1.16 (fy - 4/29).  Written as a difference first so that a black
+  // pixel (fy == 4/29 exactly) gives L == 0 exactly, as the reference's separately rounded 116 fy - 16 does: L = 0
+  // sits on the boundary of every clamp(.., 0, 1) downstream, which passes gradient only on the closed
+  // interval -- a fused 1.16 fy - 0.16 leaves -3e-9 there and silently blocks the L gradient of black pixels.
+  lab[0] = vmul(vsub(f[1], T(k::F_OFF)), T(k::LN_S));
   lab[1] = vfma(vsub(f[0], f[1]), T(k::AN_S), T(0.5f));      // colors.py:50,58
   lab[2] = vfma(vsub(f[1], f[2]), T(k::BN_S), T(0.5f));      // colors.py:50,59
 }

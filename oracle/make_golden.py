@@ -192,7 +192,7 @@ def trispace_golden():
     np.savez_compressed(os.path.join(GOLDEN_DIR, "trispace.npz"), **blob)
 
 
-LOSS_CASES = ["near", "random", "uint8", "odd", "allmasked_image", "floatmask"]
+LOSS_CASES = ["near", "random", "uint8", "odd", "allmasked_image", "floatmask", "saturated"]
 
 
 def loss_golden():
@@ -208,6 +208,10 @@ def loss_golden():
             pred = torch.rand(B, 3, H, W, generator=g)
         else:
             pred = (target + 0.05 * torch.randn(B, 3, H, W, generator=g)).clamp(0.0, 1.0)
+        if case == "saturated":                  # what a clamped prediction looks like: exact 0 / 1, whites, greys, channel ties
+            pred = ((target - 0.5) * 2.2 + 0.5 + 0.05 * torch.randn(B, 3, H, W, generator=g)).clamp(0.0, 1.0)
+            pred[:, :, 4:6] = pred[:, 0:1, 4:6]          # grey rows
+            pred[:, 1, 8:10] = pred[:, 0, 8:10]          # r == g rows
         if case == "uint8":                      # quantised: exact ties pred == target (sign(0) = 0), black pixels
             pred, target = (pred * 255).round() / 255, (target * 255).round() / 255
             pred[:, :, :2] = 0.0

@@ -9,7 +9,7 @@ import torch
 
 import hostsim
 import parity
-from conftest import LAYER_CASES, LOSS_CASES, STAGE_CASES, rel_to_max
+from conftest import LAYER_CASES, LOSS_CASES, STAGE_CASES, frac_mismatch, rel_to_max
 from oracle import curl_oracle as O
 
 
@@ -141,6 +141,9 @@ def test_hostsim_loss_terms_vs_golden(case, loss_golden):
     gp = hostsim.loss_terms(pred, target, mask, w=gs[:, :4].numpy(), gL=gL.numpy())
     r32, r64 = g[f"{case}.f32.gpred"], g[f"{case}.f64.gpred"]
     assert rel_to_max(gp, r64) <= max(1e-4, 3 * rel_to_max(r32, r64)), case
+    # element-wise against the reference's fp32 run: black, white and grey pixels sit exactly on clamp
+    # boundaries and ties (L = 0, L = 1, df = 0) and must take the reference's side of each
+    assert frac_mismatch(gp, r32) == 0.0, (case, frac_mismatch(gp, r32))
 
 
 @pytest.mark.parametrize("shape,sigma,masked", [((2, 24, 32), 0.1, True), ((1, 17, 19), 0.1, False), ((2, 16, 16), 0.3, True)])
