@@ -67,6 +67,13 @@ def test_layer_vs_golden(case, layer_golden):
         if case == "identity":
             continue  # every pixel of this case sits on a tie/clamp bound; see parity.py
         rep[k] = parity.check_knots(case, ours[k], r32[k], r64[k])
+    # element-wise against the reference's fp32 run: pixels on exact boundaries (black, white, grey) must take
+    # the reference's side.  Genuine ties that rounding decides are bounded by the reference's own
+    # fp32-vs-fp64 flip rate (the 'identity' case is made of nothing else).
+    own = frac_mismatch(r64["gimg"], r32["gimg"])
+    rep["gimg_frac_mismatch_vs_ref32"] = frac_mismatch(ours["gimg"], r32["gimg"])
+    rep["gimg_frac_mismatch_ref64_vs_ref32"] = own
+    assert rep["gimg_frac_mismatch_vs_ref32"] <= max(2e-3, 2 * own), rep
     REPORT[f"layer.{case}"] = rep
 
 
@@ -94,6 +101,8 @@ def test_color_modules_vs_golden(case, mod, stage_golden):
     rep = dict(y=parity.check_image(name, y.detach().cpu().numpy(), y32, y64, scale=scale))
     gscale = float(np.abs(gx64).max())
     rep["gx"] = parity.check_image("edges", x.grad.cpu().numpy(), gx32, gx64, scale=gscale, tol=2e-5)
+    rep["gx_frac_mismatch_vs_ref32"] = frac_mismatch(x.grad.cpu().numpy(), gx32)
+    assert rep["gx_frac_mismatch_vs_ref32"] <= max(2e-3, 2 * frac_mismatch(gx64, gx32)), rep
     REPORT[f"color.{mod}.{case}"] = rep
 
 
