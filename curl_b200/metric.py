@@ -23,6 +23,10 @@ class MSSSIMMetric(nn.Module):
         self.window_size = window_size
         self.num_channel = num_channel
         self.gaussian_window = MSSSIMMetric.create_window(window_size, num_channel)
+        # the reference keeps the window as a plain CPU attribute and copies it to the device on every call
+        # (metric.py:131); here the device copy is cached per (device, dtype): no per-call H2D copy, and the
+        # criterion can be captured in a CUDA graph.  Not a buffer, so the state dict is the reference's.
+        self._window_cache = {}
 
     @staticmethod
     def gaussian(window_size, sigma):
@@ -40,7 +44,11 @@ class MSSSIMMetric(nn.Module):
     def _stats(self, img1, img2):
         """mu1, mu2, E[x^2], E[y^2], E[xy] under the window, one grouped conv."""
         C = self.num_channel
-        win = self.gaussian_window.to(device=img1.device, dtype=img1.dtype).repeat(5, 1, 1, 1)
+        key = (img1.device, img1.dtype)
+        win = self._window_cache.get(key)
+        if win is None:
+            win = self.gaussian_window.to(device=img1.device, dtype=img1.dtype).repeat(5, 1, 1, 1)
+            self._window_cache[key] = win
         planes = torch.cat((img1, img2, img1 * img1, img2 * img2, img1 * img2), dim=1)
         s = F.conv2d(planes, win, padding=self.window_size // 2, groups=5 * C)
         return s[:, 0:C], s[:, C:2 * C], s[:, 2 * C:3 * C], s[:, 3 * C:4 * C], s[:, 4 * C:5 * C]
@@ -75,7 +83,13 @@ class MSSSIMMetric(nn.Module):
         ssims = (torch.stack(ssims, dim=1) + 1) / 2
         mcs = (torch.stack(mcs, dim=1) + 1) / 2
         w = self.msssim_weights.reshape(1, -1)
-        return torch.prod((mcs ** w)[:, :-1] * (ssims ** w)[:, -1].reshape(-1, 1), dim=1)
+        terms = (mcs ** w)[:, :-1] * (ssims ** w)[:, -1].reshape(-1, 1)
+        # the reference's torch.prod(terms, dim=1) (metric.py:210), written out: prod's backward inspects its
+        # input for zeros on the host (a device synchronisation, and not capturable in a CUDA graph)
+        out = terms[:, 0]
+        for k in range(1, terms.shape[1]):
+            out = out * terms[:, k]
+        return out
 
     def forward(self, img1, img2):
         return self.compute_msssim(img1, img2)

@@ -767,3 +767,48 @@ def test_segment_clamp_properties_and_errors():
     lib = curl_b200._lib.load()
     assert lib.curl_layer_seg_bwd_workspace_bytes(0, 8, 8, 16, 16, 16) == 0
     assert lib.curl_layer_seg_fwd_f32(None, None, 0, None, 48, None, 48, None, 64, None, None, 1, 8, 8, 16, 16, 16, None) == -1
+
+
+def test_widened_ops_capture_in_cuda_graphs_and_accept_views():
+    """CURLLoss (fused terms + library MS-SSIM), the TriSpace residual and the segment-clamped layer
+    issue no host synchronisation: forward + backward capture into a CUDA graph and replay to the
+    same bits (the loss terms and TriSpace reductions are fixed-order).  Non-contiguous inputs are
+    accepted like the reference accepts them."""
+    import curl_b200
+    import torch.nn as nn
+    dev = _dev()
+    gen = torch.Generator().manual_seed(31)
+    B, H, W = 2, 64, 80
+    target = torch.rand(B, 3, H, W, generator=gen).to(dev)
+    pred = (target + 0.05 * torch.randn(B, 3, H, W, generator=gen).to(dev)).clamp(0, 1).requires_grad_(True)
+    mask = (torch.rand(B, 1, H, W, generator=gen) > 0.1).to(dev)
+    crit = curl_b200.CURLLoss().to(dev)
+    tri = curl_b200.TriSpaceRegNet(spatial=True, backbone=nn.Identity()).to(dev)
+    co = [(0.3 * torch.randn(B, 3, 126, generator=gen)).to(dev).requires_grad_(True) for _ in range(3)]
+
+    def step():
+        out = tri._fused(target, *co, True)
+        loss = crit(pred, target, mask) + (out * target).mean()
+        return torch.autograd.grad(loss, [pred] + co) + (loss.detach(),)
+
+    eager = [t.clone() for t in step()]
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        step()
+    torch.cuda.current_stream().wait_stream(s)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        captured = step()
+    for t in captured:
+        t.zero_()
+    graph.replay()
+    torch.cuda.synchronize()
+    for a, b in zip(eager, captured):
+        assert torch.equal(a, b)
+    # views: channels-last prediction, expanded mask
+    nc = pred.detach().permute(0, 2, 3, 1).contiguous().permute(0, 3, 1, 2)
+    assert not nc.is_contiguous()
+    a = crit(nc, target, mask[:1].expand(B, 1, H, W) | mask)
+    b = crit(pred.detach(), target, mask[:1] | mask)
+    assert torch.equal(a, b)
