@@ -369,6 +369,39 @@ def run_ours(args):
             extras["fwd_u8_4k_b%d" % B]["e2e_mpx_per_s"] = n_px / 1e6 / (ms / 1e3)
             extras["fwd_u8_4k_b%d" % B]["e2e_what"] = "pinned host u8 image + bool mask -> H2D -> kernel -> D2H u8 image (7 B/px over PCIe)"
             del i8, h_i8, h_o8
+        # Training step fed from 8-bit host data (what data.py holds before TF.to_tensor): the host uploads the
+        # uint8 image (3 B/px) + mask, curl_u8_to_unit_f32 makes the fp32 tensor on the device, then the same
+        # forward + backward as the e2e leg above (image gradient included, results read back)
+        from curl_b200.functional import to_tensor_u8
+        h_img8 = torch.empty(img.shape, dtype=torch.uint8, pin_memory=True)
+        h_img8.copy_((img.detach() * 255).to(torch.uint8))
+        d_img8 = torch.empty(img.shape, dtype=torch.uint8, device=dev)
+
+        def u8_train_step():
+            ready = []
+            copy_stream.wait_stream(main_stream)
+            with torch.cuda.stream(copy_stream):
+                for lo, hi in spans:
+                    d_img8[lo:hi].copy_(h_img8[lo:hi], non_blocking=True)
+                    d_mask[lo:hi].copy_(h_mask[lo:hi], non_blocking=True)
+                    ev_c = torch.cuda.Event()
+                    ev_c.record(copy_stream)
+                    ready.append(ev_c)
+            for (lo, hi), ev_c in zip(spans, ready):
+                main_stream.wait_event(ev_c)
+                x = to_tensor_u8(d_img8[lo:hi]).requires_grad_(True)
+                l, r, h = (t[lo:hi].clone().requires_grad_(True) for t in (Ld, Rd, Hd))
+                o, rg = layer(x, d_mask[lo:hi], l, r, h)
+                torch.autograd.backward([o, rg], [gout[lo:hi], greg[lo:hi]])
+                d_res[lo:hi, 0] = rg.detach()
+                d_res[lo:hi, 1:49] = l.grad; d_res[lo:hi, 49:97] = r.grad; d_res[lo:hi, 97:161] = h.grad
+            h_res.copy_(d_res, non_blocking=True)
+        ms = timed(u8_train_step, 3)
+        extras["train_from_u8_4k_b%d" % B] = {
+            "e2e_ms": ms, "e2e_mpx_per_s": n_px / 1e6 / (ms / 1e3), "h2d_bytes_per_step": h_img8.numel() + h_mask.numel(),
+            "what": "pinned host uint8 image + bool mask -> H2D (4 B/px) -> curl_u8_to_unit_f32 -> CURLLayer fwd+bwd "
+                    "-> D2H reg + knot grads; the headline e2e leg uploads the same images as fp32 (13 B/px)"}
+        del h_img8, d_img8
         # TriSpace polynomial residual (TriSpaceRegNet's per-pixel path), spatial=True (126 coefficients),
         # BASELINE configs[2]'s shape: 512 x 512, batch 32; forward incl. generate_image, and backward
         import torch.nn as nn

@@ -15,7 +15,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libcurl_b200.so")
 SOURCES = [os.path.join(CSRC, "curl_kernels.cu"), os.path.join(CSRC, "curl_trispace.cu"),
-           os.path.join(CSRC, "curl_loss.cu"), os.path.join(CSRC, "curl_segclamp.cu")]
+           os.path.join(CSRC, "curl_loss.cu"), os.path.join(CSRC, "curl_segclamp.cu"), os.path.join(CSRC, "curl_convert.cu")]
 DEPS = SOURCES + [os.path.join(CSRC, "curl_pixel.cuh"), os.path.join(CSRC, "curl_vec.cuh"), os.path.join(CSRC, "curl_poly.cuh"),
                   os.path.join(CSRC, "curl_loss.cuh"), os.path.join(CSRC, "curl_seg.cuh"), os.path.join(HERE, "..", "include", "curl_b200.h")]
 

