@@ -577,9 +577,16 @@ __global__ void __launch_bounds__(BWD_THREADS, BWD_MIN_BLOCKS) bwd_tma_kernel(co
   if (NC > 0) stage_curves<NC>(p, b, s_C, s_ab, nullptr, false);
 
   using T = F2;
+#ifdef BWD_SCALAR_MOM
+  // moments as scalars (lo + hi folded every iteration): 20 registers instead of 40 across the loop
+  float mom[NM > 0 ? NM : 1];
+#pragma unroll
+  for (int k = 0; k < NM; ++k) mom[k] = 0.0f;
+#else
   T mom[NM > 0 ? NM : 1];
 #pragma unroll
   for (int k = 0; k < NM; ++k) mom[k] = T(0.0f);
+#endif
 
   // The mask plane is only 4-byte aligned in general, so it cannot ride the bulk copies; it is
   // fetched with an ordinary load one whole iteration ahead (raw bits kept in one register pair).
@@ -626,19 +633,34 @@ __global__ void __launch_bounds__(BWD_THREADS, BWD_MIN_BLOCKS) bwd_tma_kernel(co
     if (threadIdx.x == 0 && it + TMA_STAGES < n_my) issue(it + TMA_STAGES);
     if (!valid) m = T(0.0f);
     T gx[3];
+#ifdef BWD_SCALAR_MOM
+    T momi[NM > 0 ? NM : 1];
+#pragma unroll
+    for (int k = 0; k < NM; ++k) momi[k] = T(0.0f);
+#else
+    T* const momi = mom;
+#endif
     if constexpr (Op::SPILL > 0) {
       const SmemSpill sp{smem_u32(reinterpret_cast<unsigned char*>(s_ring) + TMA_RING_BYTES) + threadIdx.x * 8u};
-      Op::template bwd<MK, WANT_GIN, T>(x, m, s_ab, p.aux, gy, gx, mom, sp);
+      Op::template bwd<MK, WANT_GIN, T>(x, m, s_ab, p.aux, gy, gx, momi, sp);
     } else {
-      Op::template bwd<MK, WANT_GIN, T>(x, m, s_ab, p.aux, gy, gx, mom, KeepInRegisters());
+      Op::template bwd<MK, WANT_GIN, T>(x, m, s_ab, p.aux, gy, gx, momi, KeepInRegisters());
     }
+#ifdef BWD_SCALAR_MOM
+#pragma unroll
+    for (int k = 0; k < NM; ++k) mom[k] += vhsum(momi[k]);
+#endif
     if (WANT_GIN && valid) {
 #pragma unroll
       for (int c = 0; c < 3; ++c)
         __stcs(reinterpret_cast<float2*>(gin + (size_t)c * HW + px), make_float2(gx[c].lo(), gx[c].hi()));
     }
   }
+#ifdef BWD_SCALAR_MOM
+  if (NC > 0) finish_knot_grads<NC, float, BWD_THREADS>(p, b, mom, s_C, s_mom, s_part, &s_ticket);
+#else
   if (NC > 0) finish_knot_grads<NC, T, BWD_THREADS>(p, b, mom, s_C, s_mom, s_part, &s_ticket);
+#endif
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -9,6 +9,8 @@ from curl_b200 import _lib as L
 def bind(path):
     lib = ctypes.CDLL(path)
     for name, (res, args) in L.SIGNATURES.items():
+        if not hasattr(lib, name):
+            continue        # a layer-only experiment build
         fn = getattr(lib, name); fn.restype = res; fn.argtypes = args
     return lib
 
