@@ -1,0 +1,82 @@
+"""GPU: seeded differential sweep of the fused layer against the CPU oracle over shapes, knot counts,
+curve strengths, mask kinds and input kinds (continuous, 8-bit grids with black / white / grey patches).
+Judged ELEMENT-WISE against the oracle's fp32 run (conftest.frac_mismatch: a wrong decision at an exact
+boundary -- L = 0 of black pixels, saturated channels, channel ties -- shows up here even when some
+other element of the tensor is huge), with the reference's own fp32-vs-fp64 disagreement as the
+allowance for ties that rounding decides."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import frac_mismatch, rel_to_max
+from oracle import curl_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+CASES = []
+_rng = np.random.RandomState(20261107)
+for _i in range(18):
+    B = int(_rng.randint(1, 4))
+    H, W = int(_rng.randint(3, 70)), int(_rng.randint(3, 90))
+    K = (int(_rng.randint(3, 22)), int(_rng.randint(3, 22)), int(_rng.randint(3, 22)))
+    sigma = float(_rng.choice([0.03, 0.1, 0.25]))
+    maskkind = str(_rng.choice(["none", "bool", "float"]))
+    inkind = str(_rng.choice(["continuous", "uint8", "patches"]))
+    CASES.append((B, H, W, K, sigma, maskkind, inkind, 1000 + _i))
+
+
+def _inputs(B, H, W, K, sigma, maskkind, inkind, seed):
+    gen = torch.Generator().manual_seed(seed)
+    img = torch.rand(B, 3, H, W, generator=gen)
+    if inkind != "continuous":
+        img = (img * 255).round() / 255
+    if inkind == "patches":          # black, white, mid-grey and two-channel ties, as real images have them
+        h3 = max(1, H // 4)
+        img[:, :, :h3, : W // 2] = 0.0
+        img[:, :, :h3, W // 2:] = 1.0
+        img[:, :, h3:2 * h3] = img[:, 0:1, h3:2 * h3]
+        img[:, 1, 2 * h3:3 * h3] = img[:, 0, 2 * h3:3 * h3]
+    if maskkind == "none":
+        mask, omask = None, torch.ones(B, 1, H, W, dtype=torch.bool)
+    elif maskkind == "bool":
+        mask = torch.rand(B, 1, H, W, generator=gen) > 0.2
+        omask = mask
+    else:
+        mask = (torch.rand(B, 1, H, W, generator=gen) > 0.2).float() * (0.5 + 0.5 * torch.rand(B, 1, H, W, generator=gen))
+        omask = mask
+    pts = (3 * K[0], 3 * K[1], 4 * K[2])
+    L, R, Hk = (sigma * torch.randn(B, n, generator=gen) for n in pts)
+    gout = torch.randn(B, 3, H, W, generator=gen)
+    greg = torch.randn(B, generator=gen)
+    return img, mask, omask, L, R, Hk, gout, greg, pts
+
+
+@pytest.mark.parametrize("case", CASES, ids=lambda c: "B%dx%dx%d-K%s-s%g-%s-%s" % (c[0], c[1], c[2], "_".join(map(str, c[3])), c[4], c[5], c[6]))
+def test_layer_fuzz_vs_oracle(case):
+    import curl_b200
+    dev = torch.device("cuda:0")
+    img, mask, omask, L, R, Hk, gout, greg, pts = _inputs(*case)
+    kw = dict(num_lab_points=pts[0], num_rgb_points=pts[1], num_hsv_points=pts[2])
+    r32 = O.curl_layer_fwd_bwd(img, omask, L, R, Hk, gout, greg, **kw)
+    m64 = omask if omask.dtype == torch.bool else omask.double()
+    r64 = O.curl_layer_fwd_bwd(img.double(), m64, L.double(), R.double(), Hk.double(), gout.double(), greg.double(), **kw)
+    layer = curl_b200.CURLLayer(*pts).to(dev)
+    xi = img.to(dev).requires_grad_(True)
+    kn = [t.to(dev).requires_grad_(True) for t in (L, R, Hk)]
+    out, reg = layer(xi, None if mask is None else mask.to(dev), *kn)
+    torch.autograd.backward([out, reg], [gout.to(dev), greg.to(dev)])
+    got = dict(out=out.detach(), reg=reg.detach(), gimg=xi.grad, gL=kn[0].grad, gR=kn[1].grad, gH=kn[2].grad)
+    got = {k: v.cpu().numpy() for k, v in got.items()}
+    assert rel_to_max(got["reg"], r64["reg"].numpy()) <= 1e-5
+    # forward: absolute, element-wise
+    e32 = np.abs(got["out"] - r32["out"].numpy())
+    own = np.abs(r32["out"].numpy() - r64["out"].numpy())
+    assert (e32 > 1e-5).mean() <= max(2e-3, 2 * (own > 1e-5).mean()), ((e32 > 1e-5).mean(), (own > 1e-5).mean())
+    # image gradient: element-wise against fp32, ties allowed at the reference's own flip rate
+    fm = frac_mismatch(got["gimg"], r32["gimg"].numpy())
+    own_fm = frac_mismatch(r64["gimg"].numpy(), r32["gimg"].numpy())
+    assert fm <= max(3e-3, 2 * own_fm), (fm, own_fm)
+    # knot gradients: sums over pixels; a flipped tie pixel moves them by one pixel's contribution
+    for k in ("gL", "gR", "gH"):
+        e = min(rel_to_max(got[k], r32[k].numpy()), rel_to_max(got[k], r64[k].numpy()))
+        assert e <= max(1e-4, 4 * rel_to_max(r32[k].numpy(), r64[k].numpy())), (k, e)
