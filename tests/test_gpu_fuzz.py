@@ -80,3 +80,52 @@ def test_layer_fuzz_vs_oracle(case):
     for k in ("gL", "gR", "gH"):
         e = min(rel_to_max(got[k], r32[k].numpy()), rel_to_max(got[k], r64[k].numpy()))
         assert e <= max(1e-4, 4 * rel_to_max(r32[k].numpy(), r64[k].numpy())), (k, e)
+
+
+LOSS_FUZZ = []
+for _i in range(10):
+    LOSS_FUZZ.append((int(_rng.randint(1, 4)), int(_rng.randint(32, 90)), int(_rng.randint(32, 100)),
+                      str(_rng.choice(["none", "bool", "float"])), str(_rng.choice(["near", "far", "uint8", "patches"])), 2000 + _i))
+
+
+@pytest.mark.parametrize("case", LOSS_FUZZ, ids=lambda c: "B%dx%dx%d-%s-%s" % c[:5])
+def test_loss_fuzz_vs_oracle(case):
+    """CURLLoss (fused colour terms + library MS-SSIM) against the oracle: value, and gradient element-wise
+    against the oracle's fp32 run with the reference's own fp32-vs-fp64 disagreement as the allowance."""
+    import curl_b200
+    B, H, W, maskkind, inkind, seed = case
+    dev = torch.device("cuda:0")
+    gen = torch.Generator().manual_seed(seed)
+    target = torch.rand(B, 3, H, W, generator=gen)
+    pred = torch.rand(B, 3, H, W, generator=gen) if inkind == "far" else \
+        (target + 0.05 * torch.randn(B, 3, H, W, generator=gen)).clamp(0, 1)
+    if inkind in ("uint8", "patches"):
+        pred, target = (pred * 255).round() / 255, (target * 255).round() / 255
+    if inkind == "patches":
+        h4 = H // 5
+        pred[:, :, :h4, : W // 2] = 0.0
+        pred[:, :, :h4, W // 2:] = 1.0
+        pred[:, :, h4:2 * h4] = pred[:, 0:1, h4:2 * h4]
+        target[:, :, 2 * h4:3 * h4, : W // 3] = 0.0
+        target[:, :, 2 * h4:3 * h4, W // 3:] = 1.0
+        pred[:, :, 3 * h4:4 * h4, : W // 4] = target[:, :, 3 * h4:4 * h4, : W // 4]
+    if maskkind == "none":
+        mask, omask = None, torch.ones(B, 1, H, W, dtype=torch.bool)
+    elif maskkind == "bool":
+        mask = torch.rand(B, 1, H, W, generator=gen) > 0.15
+        omask = mask
+    else:
+        mask = (torch.rand(B, 1, H, W, generator=gen) > 0.15).float()
+        omask = mask
+    r32 = O.curl_loss_fwd_bwd(pred, target, omask)
+    r64 = O.curl_loss_fwd_bwd(pred.double(), target.double(), omask)
+    crit = curl_b200.CURLLoss().to(dev)
+    p = pred.to(dev).requires_grad_(True)
+    loss = crit(p, target.to(dev), None if mask is None else mask.to(dev))
+    loss.backward()
+    tol = max(1e-5, 3 * abs(float(r32["loss"]) - float(r64["loss"])))
+    assert abs(float(loss.detach()) - float(r64["loss"])) <= tol, (float(loss.detach()), float(r32["loss"]), float(r64["loss"]))
+    gp = p.grad.cpu().numpy()
+    fm = frac_mismatch(gp, r32["gpred"].numpy())
+    own = frac_mismatch(r64["gpred"].numpy(), r32["gpred"].numpy())
+    assert fm <= max(2e-3, 2 * own), (fm, own)
