@@ -129,3 +129,44 @@ def test_loss_fuzz_vs_oracle(case):
     fm = frac_mismatch(gp, r32["gpred"].numpy())
     own = frac_mismatch(r64["gpred"].numpy(), r32["gpred"].numpy())
     assert fm <= max(2e-3, 2 * own), (fm, own)
+
+
+TRI_FUZZ = [(int(_rng.randint(1, 4)), int(_rng.randint(2, 80)), int(_rng.randint(2, 100)), bool(_rng.randint(0, 2)),
+             bool(_rng.randint(0, 2)), str(_rng.choice(["continuous", "uint8", "patches"])), bool(_rng.randint(0, 2)), 3000 + _i)
+            for _i in range(10)]
+
+
+@pytest.mark.parametrize("case", TRI_FUZZ, ids=lambda c: "B%dx%dx%d-sp%d-cl%d-%s-save%d" % c[:7])
+def test_trispace_fuzz_vs_oracle(case):
+    """Fused TriSpace residual / image and its coefficient gradients against the oracle over shapes
+    (odd and tiny included), spatial on/off, with/without the final clamp, saved or recomputed backward."""
+    import curl_b200
+    import torch.nn as nn
+    B, H, W, spatial, clamp, inkind, save, seed = case
+    dev = torch.device("cuda:0")
+    gen = torch.Generator().manual_seed(seed)
+    img = torch.rand(B, 3, H, W, generator=gen)
+    if inkind != "continuous":
+        img = (img * 255).round() / 255
+    if inkind == "patches":
+        h3 = max(1, H // 3)
+        img[:, :, :h3, : W // 2] = 0.0
+        img[:, :, :h3, W // 2:] = 1.0
+        img[:, :, h3:2 * h3] = img[:, 0:1, h3:2 * h3]
+    nc = 126 if spatial else 35
+    co = [0.3 * torch.randn(B, 3, nc, generator=gen) for _ in range(3)]
+    gout = torch.randn(B, 3, H, W, generator=gen)
+    r32 = O.trispace_fwd_bwd(img, *co, gout, 4, spatial, clamp)
+    r64 = O.trispace_fwd_bwd(img.double(), *[c.double() for c in co], gout.double(), 4, spatial, clamp)
+    net = curl_b200.TriSpaceRegNet(spatial=spatial, backbone=nn.Identity()).to(dev)
+    net.save_activations = save
+    cg = [c.to(dev).requires_grad_(True) for c in co]
+    out = net._fused(img.to(dev), *cg, clamp)
+    out.backward(gout.to(dev))
+    o = out.detach().cpu().numpy()
+    own = float(np.abs(r32["out"].numpy() - r64["out"].numpy()).max())
+    assert np.abs(o - r64["out"].numpy()).max() <= max(3e-5, 3 * own)
+    assert (np.abs(o - r32["out"].numpy()) > 2e-5).mean() <= 2e-3
+    for k, c in zip(("gR", "gL", "gH"), cg):
+        e = rel_to_max(c.grad.cpu().numpy(), r64[k].numpy())
+        assert e <= max(1e-4, 4 * rel_to_max(r32[k].numpy(), r64[k].numpy())), (k, e)
