@@ -170,6 +170,28 @@ CURL_F2_MAP2(vgate_le) CURL_F2_MAP2(vgate_lt) CURL_F2_MAP2(vgate_eq) CURL_F2_MAP
 #endif
 CURL_F2_MAP4(vsel_le) CURL_F2_MAP4(vsel_lt) CURL_F2_MAP4(vsel_eq)
 CURL_D float vhsum(F2 a) { return a.lo() + a.hi(); }
+
+// ------------------------------------------------------------------------------------------------
+// F4: two F2 side by side (four pixels per value).  For kernels whose inner loop is bound by
+// per-pixel-group shared-memory reads of broadcast operands (the TriSpace coefficients): one read then
+// feeds four pixels instead of two.  Every operation is the F2 one on both halves.
+// ------------------------------------------------------------------------------------------------
+struct F4 {
+  F2 a, b;
+  F4() = default;
+  CURL_D F4(float c) : a(c), b(c) {}
+  CURL_D F4(F2 x, F2 y) : a(x), b(y) {}
+};
+#define CURL_F4_MAP1(name) CURL_D F4 name(F4 x) { return F4(name(x.a), name(x.b)); }
+#define CURL_F4_MAP2(name) CURL_D F4 name(F4 x, F4 y) { return F4(name(x.a, y.a), name(x.b, y.b)); }
+#define CURL_F4_MAP3(name) CURL_D F4 name(F4 x, F4 y, F4 z) { return F4(name(x.a, y.a, z.a), name(x.b, y.b, z.b)); }
+#define CURL_F4_MAP4(name) CURL_D F4 name(F4 x, F4 y, F4 z, F4 w) { return F4(name(x.a, y.a, z.a, w.a), name(x.b, y.b, z.b, w.b)); }
+CURL_F4_MAP2(vadd) CURL_F4_MAP2(vsub) CURL_F4_MAP2(vmul) CURL_F4_MAP3(vfma) CURL_F4_MAP1(vneg)
+CURL_F4_MAP1(vlg2) CURL_F4_MAP1(vex2) CURL_F4_MAP1(vrcp) CURL_F4_MAP1(vsat)
+CURL_F4_MAP2(vmul_sat) CURL_F4_MAP2(vadd_sat) CURL_F4_MAP3(vfma_sat) CURL_F4_MAP2(vmax) CURL_F4_MAP2(vmin)
+CURL_F4_MAP2(vgate_le) CURL_F4_MAP2(vgate_lt) CURL_F4_MAP2(vgate_eq) CURL_F4_MAP2(vgate_ne)
+CURL_F4_MAP4(vsel_le) CURL_F4_MAP4(vsel_lt) CURL_F4_MAP4(vsel_eq)
+CURL_D float vhsum(F4 x) { return vhsum(x.a) + vhsum(x.b); }
 #endif  // __CUDACC__
 
 }  // namespace curl
