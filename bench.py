@@ -16,7 +16,8 @@ Printed JSON (rank 0, one line):
   roofline  the dominant kernel (fused backward, 37 algorithmic B/px) against the measured HBM peak
   gpu_eager_baseline  the same op sequence run eagerly by PyTorch on this GPU (the reference's own
             way of using a GPU), one 1080p tile
-  extras    non-headline measurements: BASELINE configs[1] (1080p x16 forward) and the 8-bit inference path
+  extras    non-headline measurements: BASELINE configs[1] (1080p x16 forward), configs[2] / configs[4]
+            (GCURLNet optimiser step at 512x512x32, under DDP when N > 1), the 8-bit paths, TriSpace, CURLLoss
   cpu_baseline  the CPU oracle (the reference's ATen op sequence, restated; kind "port") on this
             box's host cores over a bounded sample of the same workload
 `--impl reference` times only that CPU path (the reference has no native code and /root/reference
@@ -197,6 +198,63 @@ WORKLOAD = "4K (3840x2160) synthetic RGB fp32, batch 64 per GPU, curve-layer fwd
 
 # ------------------------------------------------------------------------------------------------
 # GPU arm
+def net_training_step_extra(dev, world, local, timed):
+    """BASELINE.json configs[2] (N = 1) and the training half of configs[4] (N > 1): one optimiser step of
+    the layer's caller, GCURLNet (reference model.py:179-203), at 512 x 512 x 32 per GPU.  The backbone is
+    library code on PyTorch/cuDNN (north_star); the reference's timm EfficientNetV2 is absent from this
+    image, so torchvision's efficientnet_v2_s with a 160-wide head stands in.  Loss =
+    L1 + 1e-6 * regulariser, Adam as in main.py:236-237.  At N > 1 the net is wrapped in
+    DistributedDataParallel exactly as main.py:224-225 does: the only collective is DDP's NCCL gradient
+    all-reduce of the backbone weights; the curve layer adds none.  Runs on every rank."""
+    import torch.nn as nn
+    import torch.nn.functional as F
+    import curl_b200
+    from curl_b200.parallel import max_over_ranks
+    try:
+        from torchvision.models import efficientnet_v2_s
+    except Exception as e:
+        return {"unavailable": "torchvision: %s" % e}
+    Bn, Hn, Wn = 32, 512, 512
+    torch.manual_seed(99)                                    # same initial weights on every rank
+    net = curl_b200.GCURLNet(backbone=efficientnet_v2_s(weights=None, num_classes=160)).to(dev)
+    net.train()
+    model = nn.parallel.DistributedDataParallel(net, device_ids=[local], output_device=local) if world > 1 else net
+    opt = torch.optim.Adam(net.parameters(), lr=5e-7, betas=(0.5, 0.999))
+    g = torch.Generator(device=dev).manual_seed(555 + local)
+    x = torch.rand(Bn, 3, Hn, Wn, generator=g, device=dev)
+    y = (x * 0.9 + 0.05).contiguous()
+    m = torch.rand(Bn, 1, Hn, Wn, generator=g, device=dev) > 0.1
+
+    def step():
+        opt.zero_grad(set_to_none=True)
+        out, reg = model(x, m)
+        loss = F.l1_loss(out, y) + 1e-6 * reg.mean()
+        loss.backward()
+        opt.step()
+    ms = max_over_ranks(timed(step, 10), dev)
+    # the curve layer's own share of that step: forward + backward without image gradient (25 + 25 B/px)
+    layer = net.curllayer
+    k = [(0.1 * torch.randn(Bn, n, generator=g, device=dev)).requires_grad_(True) for n in (48, 48, 64)]
+    go = torch.randn(Bn, 3, Hn, Wn, generator=g, device=dev)
+    gr = torch.ones(Bn, device=dev)
+
+    def layer_step():
+        o, r = layer(x, m, *k)
+        torch.autograd.backward([o, r], [go, gr])
+    ms_layer = max_over_ranks(timed(layer_step, 20), dev)
+    mpx = world * Bn * Hn * Wn / 1e6
+    res = {"step_ms": ms, "images_per_s": world * Bn / (ms / 1e3), "mpx_per_s": mpx / (ms / 1e3),
+           "curve_layer_fwd_bwd_ms": ms_layer, "curve_layer_share": ms_layer / ms,
+           "backbone": "torchvision efficientnet_v2_s (random init, fp32, cuDNN), %.1f M parameters"
+                       % (sum(p.numel() for p in net.backbone.parameters()) / 1e6),
+           "what": "GCURLNet optimiser step, 512x512 batch 32 per GPU: backbone -> [L|R|H] -> CURLLayer -> "
+                   "L1 + 1e-6*reg -> backward -> Adam; " +
+                   ("DistributedDataParallel over NCCL (gradient all-reduce of the backbone only), max over ranks"
+                    if world > 1 else "single GPU")}
+    del model, net, opt, x, y, m, go
+    return res
+
+
 # ------------------------------------------------------------------------------------------------
 def run_ours(args):
     import torch.distributed as dist
@@ -212,7 +270,8 @@ def run_ours(args):
     dev = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # keep stdout to the one JSON line
-        dist.init_process_group("nccl", device_id=dev)
+        import datetime
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=180))
     _lib.load()
 
     B, H, W = args.batch, args.height, args.width
@@ -455,6 +514,13 @@ def run_ours(args):
             "what": "fused colour terms: 33 B/px forward (pred, target, mask in; 2 L planes out), 41 B/px backward; "
                     "criterion = terms + MS-SSIM of the L planes on the library convolution path"}
         del l_pred, l_target, l_gl, crit
+
+    if not args.no_extras:
+        try:
+            extras["gcurlnet_train_512_b32" if world == 1 else "gcurlnet_ddp_train_512_b32"] = \
+                net_training_step_extra(dev, world, local, timed)
+        except Exception as e:   # an extra never fails the headline line (every rank reaches the barrier below)
+            extras["gcurlnet_train_512_b32"] = {"unavailable": "%s: %s" % (type(e).__name__, str(e)[:200])}
 
     if rank == 0:
         peak, peak_src = measured_peak()
