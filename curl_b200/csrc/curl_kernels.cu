@@ -15,14 +15,20 @@
 namespace curl {
 
 constexpr int THREADS = 256;
+// Backward (aligned path) launch shape: three independent 128-thread blocks per SM (144 registers
+// each) instead of one 384-thread block.  Same 12 warps per SM, but each scheduler holds one warp of
+// each block, the per-stage barrier spans 4 warps instead of 12 and the blocks drift apart, so their
+// MUFU / gate / FMA phases interleave: 4K x 16 backward 2.357 -> 2.165 ms; with two sub-tiles per
+// stage (BWD_PAIRS, one barrier + one refill per 512 px) 2.131 ms.  Measured alternatives, ms:
+// 192x2 2.343, 96x4 2.377, 64x6 2.234, 32x12 2.317, 128x4 at 128 registers (BWD_SCALAR_MOM) 2.121.
 #ifndef BWD_THREADS
-#define BWD_THREADS 384
+#define BWD_THREADS 128
 #endif
 #ifndef BWD_SPILL
 #define BWD_SPILL 24
 #endif
 #ifndef BWD_MIN_BLOCKS
-#define BWD_MIN_BLOCKS 1
+#define BWD_MIN_BLOCKS 3
 #endif
 constexpr int MAX_SEGS = 3;
 constexpr int MAX_CURVES = 10;
@@ -425,7 +431,7 @@ __device__ __forceinline__ void finish_knot_grads(const KParams& p, int b, const
 // image folds all partial rows in a fixed order (in double) and writes the knot gradients.
 // ---------------------------------------------------------------------------------------------
 template <class Op, int MK, int VEC, bool WANT_GIN>
-__global__ void __launch_bounds__(THREADS, BWD_MIN_BLOCKS) bwd_kernel(const KParams p) {
+__global__ void __launch_bounds__(THREADS) bwd_kernel(const KParams p) {
   constexpr int NC = Op::NC;
   constexpr int NM = 2 * NC;
   constexpr int NWARPS = THREADS / 32;
@@ -468,9 +474,10 @@ __global__ void __launch_bounds__(THREADS, BWD_MIN_BLOCKS) bwd_kernel(const KPar
 }
 
 // ---------------------------------------------------------------------------------------------
-// TMA (bulk async copy) helpers.  The backward kernel needs ~230 registers per thread, so only 8
-// warps fit on an SM: far too few to hide HBM latency with ordinary loads.  Instead one elected
-// thread streams each tile's six input planes into a shared-memory ring with cp.async.bulk
+// TMA (bulk async copy) helpers.  The backward kernel needs 144 registers per thread even with its
+// Jac records parked in shared memory, so only 12 warps fit on an SM: too few to hide HBM latency
+// with ordinary loads.  Instead one elected thread per block streams each tile's six input planes
+// into a shared-memory ring with cp.async.bulk
 // (SASS UBLKCP), completion tracked by an mbarrier per stage; the loads of the next STAGES-1 tiles
 // are always in flight and cost no registers.
 // ---------------------------------------------------------------------------------------------
@@ -500,9 +507,13 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned by
                : "memory");
 }
 
-constexpr int TMA_TILE = BWD_THREADS * 2;   // pixels per tile: one packed pair per thread
+#ifndef BWD_PAIRS
+#define BWD_PAIRS 2
+#endif
+constexpr int TMA_SUB = BWD_THREADS * 2;        // pixels per sub-tile: one packed pair per thread
+constexpr int TMA_TILE = TMA_SUB * BWD_PAIRS;   // pixels per stage: BWD_PAIRS sub-tiles, one barrier + one refill per stage
 #ifndef TMA_STAGES_N
-#define TMA_STAGES_N 4
+#define TMA_STAGES_N 3
 #endif
 constexpr int TMA_STAGES = TMA_STAGES_N;
 constexpr int TMA_PLANES = 6;           // x0 x1 x2 g0 g1 g2
@@ -590,8 +601,9 @@ __global__ void __launch_bounds__(BWD_THREADS, BWD_MIN_BLOCKS) bwd_tma_kernel(co
 
   // The mask plane is only 4-byte aligned in general, so it cannot ride the bulk copies; it is
   // fetched with an ordinary load one whole iteration ahead (raw bits kept in one register pair).
-  auto mask_raw = [&](int it) -> float2 {
-    const int px = (blockIdx.x + it * gridDim.x) * TMA_TILE + threadIdx.x * 2;
+  auto mask_raw = [&](int j) -> float2 {   // j: sub-tile counter of this block, BWD_PAIRS per stage
+    const int it = j / BWD_PAIRS, q = j % BWD_PAIRS;
+    const int px = (blockIdx.x + it * gridDim.x) * TMA_TILE + q * TMA_SUB + threadIdx.x * 2;
     float2 r = make_float2(1.0f, 1.0f);
     if (MK == MASK_NONE || it >= n_my || px >= HW) return r;
     if (MK == MASK_U8) {
@@ -605,12 +617,14 @@ __global__ void __launch_bounds__(BWD_THREADS, BWD_MIN_BLOCKS) bwd_tma_kernel(co
   };
   float2 m_next = mask_raw(0);
 
-  for (int it = 0; it < n_my; ++it) {
+#pragma unroll 1
+  for (int j = 0; j < n_my * BWD_PAIRS; ++j) {
+    const int it = j / BWD_PAIRS, q = j % BWD_PAIRS;
     const int s = it % TMA_STAGES;
-    const int px = (blockIdx.x + it * gridDim.x) * TMA_TILE + threadIdx.x * 2;
+    const int px = (blockIdx.x + it * gridDim.x) * TMA_TILE + q * TMA_SUB + threadIdx.x * 2;
     const bool valid = px < HW;     // HW is even: a pair is either fully inside or fully outside
     const float2 m_raw = m_next;
-    m_next = mask_raw(it + 1);
+    m_next = mask_raw(j + 1);
     T m = T(1.0f);
     if (MK == MASK_U8) {
       const unsigned u = __float_as_uint(m_raw.x);
@@ -618,8 +632,8 @@ __global__ void __launch_bounds__(BWD_THREADS, BWD_MIN_BLOCKS) bwd_tma_kernel(co
     } else if (MK == MASK_F32) {
       m = F2(m_raw.x, m_raw.y);
     }
-    mbar_wait(&s_full[s], (unsigned)(it / TMA_STAGES) & 1u);
-    const float* src = s_ring + (size_t)s * TMA_PLANES * TMA_TILE + threadIdx.x * 2;
+    if (q == 0) mbar_wait(&s_full[s], (unsigned)(it / TMA_STAGES) & 1u);
+    const float* src = s_ring + (size_t)s * TMA_PLANES * TMA_TILE + q * TMA_SUB + threadIdx.x * 2;
     T x[3], gy[3];
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
@@ -629,8 +643,10 @@ __global__ void __launch_bounds__(BWD_THREADS, BWD_MIN_BLOCKS) bwd_tma_kernel(co
       // a tail pair's gradient is switched off through m (= 0) where a mask multiplies it anyway
       gy[c] = (MK == MASK_NONE && !valid) ? F2(0.0f) : F2(g.x, g.y);
     }
-    __syncthreads();                                    // every thread has read stage s
-    if (threadIdx.x == 0 && it + TMA_STAGES < n_my) issue(it + TMA_STAGES);
+    if (q == BWD_PAIRS - 1) {
+      __syncthreads();                                  // every thread has read all of stage s
+      if (threadIdx.x == 0 && it + TMA_STAGES < n_my) issue(it + TMA_STAGES);
+    }
     if (!valid) m = T(0.0f);
     T gx[3];
 #ifdef BWD_SCALAR_MOM
@@ -717,14 +733,16 @@ static int launch_fwd(const KParams& p, int B, bool vec4, cudaStream_t st) {
 // (B * grid.x a multiple of the SM count) whenever some wave count in [W, 2W] allows it; a partial
 // last wave costs up to one full wave of time.
 static int bwd_grid_x(int B, int HW, int vec) {
-  const int px_per_tile = (vec == 1 ? THREADS : BWD_THREADS * vec);
+  const int px_per_tile = (vec == 1 ? THREADS : TMA_TILE);
   const long long tiles = ((long long)HW + px_per_tile - 1) / px_per_tile;
   const int sms = sm_count();
-  for (int w = BWD_GRID_BLOCKS_PER_SM; w <= 2 * BWD_GRID_BLOCKS_PER_SM; ++w) {
+  // R blocks are resident per SM (BWD_MIN_BLOCKS): a wave is sms * R blocks, so w steps in multiples of R
+  constexpr int R = BWD_MIN_BLOCKS;
+  for (int w = BWD_GRID_BLOCKS_PER_SM * R; w <= 2 * BWD_GRID_BLOCKS_PER_SM * R; w += R) {
     const long long total = (long long)sms * w;
     if (total % B == 0 && total / B <= tiles) return (int)(total / B);
   }
-  long long cap = ((long long)sms * BWD_GRID_BLOCKS_PER_SM + B - 1) / B;
+  long long cap = ((long long)sms * BWD_GRID_BLOCKS_PER_SM * R + B - 1) / B;
   long long n = tiles < cap ? tiles : cap;
   return (int)(n < 1 ? 1 : n);
 }
