@@ -25,7 +25,7 @@ constexpr int THREADS = 256;
 #define BWD_THREADS 128
 #endif
 #ifndef BWD_SPILL
-#define BWD_SPILL 24
+#define BWD_SPILL (6 * CURL_PARK_STAGES)
 #endif
 #ifndef BWD_MIN_BLOCKS
 #define BWD_MIN_BLOCKS 3

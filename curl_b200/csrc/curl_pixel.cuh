@@ -234,14 +234,19 @@ CURL_HD void lab2rgb_bwd(const RgbJac<T>& jac, const T grgb[3], T glab[3]) {
 // Hue uses ADDITIVE selectors: on ties the per-channel terms add (colors.py:221-224).
 // max/min route their gradient to the FIRST index attaining them (torch CPU semantics).
 // Backward, with gh/gs/gv the upstream gradients:
-//   gdf = gh kdf_h + gs kdf_s ;  gmx = gv + gs kmx_s + gdf ;  gx_c = gh hc_c + gmx amax_c - gdf amin_c
+//   -gdf = gh nkdf_h + gs nkdf_s ;  gmx = gv + gs kmx_s + gdf ;
+//   gx_c = pin_c ((gh A) sd_c + gmx amax_c - gdf amin_c)
+// The input-clamp pass pin_c and the common hue factor A are applied once in the reverse sweep rather than
+// being multiplied into nine record entries in the forward one (11 packed multiplies fewer per pixel pair).
 // ------------------------------------------------------------------------------------------------
 template <class T>
 struct HsvJac {
-  T hc[3];      // direct hue terms: pass_h/6 * (1/df) * (selector difference) * pass_in_c
-  T amax[3];    // one-hot first argmax  * pass_in_c
-  T amin[3];    // one-hot first argmin  * pass_in_c
-  T kdf_h, kdf_s, kmx_s;
+  T sd[3];      // direct hue terms: selector differences (-1, 0, 1)
+  T amax[3];    // one-hot first argmax
+  T amin[3];    // one-hot first argmin
+  T pin[3];     // input clamp passes
+  T A;          // pass_h/6 * (1/df)
+  T nkdf_h, nkdf_s, kmx_s;
 };
 
 template <class T, bool JAC, bool IN_UNIT>
@@ -280,44 +285,51 @@ CURL_HD void rgb2hsv_fwd(const T x[3], T hsv[3], HsvJac<T>* jac) {
     const T pass_s = vgate_eq(hsv[1], s);
     const T pin0 = vgate_eq(xc[0], x[0]), pin1 = vgate_eq(xc[1], x[1]), pin2 = vgate_eq(xc[2], x[2]);
     const T A = vmul(pass_h6, dinv);      // dinv == 0 on grey pixels blocks the hue gradient
-    jac->hc[0] = vmul(vmul(A, vsub(s2, s1)), pin0);
-    jac->hc[1] = vmul(vmul(A, vsub(s0, s2)), pin1);
-    jac->hc[2] = vmul(vmul(A, vsub(s1, s0)), pin2);
+    jac->A = A;
+    jac->sd[0] = vsub(s2, s1); jac->sd[1] = vsub(s0, s2); jac->sd[2] = vsub(s1, s0);
+    jac->pin[0] = pin0; jac->pin[1] = pin1; jac->pin[2] = pin2;
     const T num = vfma(s2, d01, vfma(s1, d20, vmul(s0, d12)));
-    jac->kdf_h = vneg(vmul(vmul(A, num), dinv));               // d(1/df) = -1/df^2
-    jac->kdf_s = vmul(pass_s, minv);                           // s = df / mx
-    jac->kmx_s = vneg(vmul(jac->kdf_s, s));
+    jac->nkdf_h = vmul(vmul(A, num), dinv);                    // -(d h / d df): d(1/df) = -1/df^2
+    jac->nkdf_s = vneg(vmul(pass_s, minv));                    // -(d s / d df), s = df / mx
+    jac->kmx_s = vmul(jac->nkdf_s, s);                         // d s / d mx = -s / mx
     const T e0 = vgate_eq(xc[0], mn), e1 = vgate_eq(xc[1], mn);
     const T ns0 = vsub(T(1.0f), s0), ne0 = vsub(T(1.0f), e0);
-    jac->amax[0] = vmul(s0, pin0);
-    jac->amax[1] = vmul(vmul(s1, ns0), pin1);
-    jac->amax[2] = vmul(vmul(ns0, vsub(T(1.0f), s1)), pin2);
-    jac->amin[0] = vmul(e0, pin0);
-    jac->amin[1] = vmul(vmul(e1, ne0), pin1);
-    jac->amin[2] = vmul(vmul(ne0, vsub(T(1.0f), e1)), pin2);
+    jac->amax[0] = s0;
+    jac->amax[1] = vmul(s1, ns0);
+    jac->amax[2] = vmul(ns0, vsub(T(1.0f), s1));
+    jac->amin[0] = e0;
+    jac->amin[1] = vmul(e1, ne0);
+    jac->amin[2] = vmul(ne0, vsub(T(1.0f), e1));
   }
 }
 
 template <class T>
 CURL_HD void rgb2hsv_bwd(const HsvJac<T>& j, const T ghsv[3], T gx[3]) {
-  const T gdf = vfma(ghsv[0], j.kdf_h, vmul(ghsv[1], j.kdf_s));
-  const T gmx = vadd(vfma(ghsv[1], j.kmx_s, ghsv[2]), gdf);
+  const T ngdf = vfma(ghsv[0], j.nkdf_h, vmul(ghsv[1], j.nkdf_s));
+  const T gmx = vsub(vfma(ghsv[1], j.kmx_s, ghsv[2]), ngdf);
+  const T ghA = vmul(ghsv[0], j.A);
 #pragma unroll
   for (int c = 0; c < 3; ++c)
-    gx[c] = vfma(ghsv[0], j.hc[c], vsub(vmul(gmx, j.amax[c]), vmul(gdf, j.amin[c])));
+    gx[c] = vmul(j.pin[c], vfma(ghA, j.sd[c], vfma(ngdf, j.amin[c], vmul(gmx, j.amax[c]))));
 }
 
 // ------------------------------------------------------------------------------------------------
 // Stage: HSV -> RGB                             (reference colors.py:131-177)
-//   p = v(1-s), w = v - p ;  ramp_k = clamp(360 h - k, 0, 60)/60 = sat(6h - k/60)
-//   r = v + w (ramp240 - ramp60) ; g = p + w (ramp0 - ramp180) ; b = p + w (ramp120 - ramp300)
+//   p = v(1-s), w = v - p, k = 6h.  The reference's pairs of 60-degree ramps are one trapezoid each:
+//     r = v - w (ramp60 - ramp240)   = p + w sat(|k-3| - 1)
+//     g = p + w (ramp0  - ramp180)   = p + w sat(2 - |k-2|)
+//     b = p + w (ramp120 - ramp300)  = p + w sat(2 - |k-4|)
+//   (one FFMA2 + one FADD.SAT with |.| per half and channel instead of two of each), with
+//   d/dk = +-[the trapezoid is on a slope, ends included] exactly where the reference's clamp gates pass.
+//   The output clamp of colors.py:175 is inert here and is not evaluated: 0 <= p <= v <= 1, 0 <= w = fl(v - p) <= v
+//   and 0 <= ramp <= 1, so every channel is fl(p + w ramp) with p + w ramp in [0, v + 2^-25] -- it
+//   rounds into [0, 1] and the clamp's gradient gate is 1.
 // ------------------------------------------------------------------------------------------------
 template <class T>
 struct Hsv2RgbJac {
-  T po[3];          // output clamp passes
-  T dr, dg, db;     // ramp differences
-  T hr, hg, hb;     // 6 w (gate differences) pass_in_h
-  T oms, vs;        // (1 - s) * pass_in_v ... see bwd ; v * pass_in_s
+  T ramp[3];        // r, g, b = p + w ramp_c
+  T hk[3];          // 6 w (d ramp_c / d k) pass_in_h
+  T oms, vs;        // 1 - s ; v * pass_in_s
   T pin_v;
 };
 
@@ -329,41 +341,35 @@ CURL_HD void hsv2rgb_fwd(const T in[3], T rgb[3], Hsv2RgbJac<T>* jac) {
   const T oms = vsub(T(1.0f), s);
   const T p = vmul(v, oms);
   const T w = vsub(v, p);
-  T t[6], u[6];
-#pragma unroll
-  for (int i = 0; i < 6; ++i) {
-    if (JAC) { t[i] = vfma(h, T(6.0f), T(-(float)i)); u[i] = vsat(t[i]); }
-    else u[i] = vfma_sat(h, T(6.0f), T(-(float)i));
-  }
-  const T dr = vsub(u[4], u[1]), dg = vsub(u[0], u[3]), db = vsub(u[2], u[5]);
-  const T r = vfma(w, dr, v);                                   // colors.py:143-150
-  const T g = vfma(w, dg, p);                                   // colors.py:153-159
-  const T b = vfma(w, db, p);                                   // colors.py:162-168
-  rgb[0] = vsat(r); rgb[1] = vsat(g); rgb[2] = vsat(b);         // colors.py:175
-  if (JAC) {
-    T gate[6];
-#pragma unroll
-    for (int i = 0; i < 6; ++i) gate[i] = vgate_eq(u[i], t[i]);   // ramp unsaturated, inclusive ends
-    jac->po[0] = vgate_eq(rgb[0], r); jac->po[1] = vgate_eq(rgb[1], g); jac->po[2] = vgate_eq(rgb[2], b);
-    jac->dr = dr; jac->dg = dg; jac->db = db;
+  const T tr = vfma(h, T(6.0f), T(-3.0f)), tg = vfma(h, T(6.0f), T(-2.0f)), tb = vfma(h, T(6.0f), T(-4.0f));
+  T ramp[3];
+  if (!JAC) {
+    ramp[0] = vabs_add_sat(tr, -1.0f); ramp[1] = vnabs_add_sat(tg, 2.0f); ramp[2] = vnabs_add_sat(tb, 2.0f);
+  } else {
+    const T yr = vabs_add(tr, -1.0f), yg = vnabs_add(tg, 2.0f), yb = vnabs_add(tb, 2.0f);
+    ramp[0] = vsat(yr); ramp[1] = vsat(yg); ramp[2] = vsat(yb);
     T w6 = vmul(w, T(6.0f));
     if (!IN_UNIT) w6 = vmul(w6, vgate_eq(h, in[0]));
-    jac->hr = vmul(w6, vsub(gate[4], gate[1]));
-    jac->hg = vmul(w6, vsub(gate[0], gate[3]));
-    jac->hb = vmul(w6, vsub(gate[2], gate[5]));
+    // on a slope (ends included, as torch.clamp passes gradient on the closed interval): +-1, else 0
+    jac->hk[0] = vmul(w6, vcopysign(vgate_eq(ramp[0], yr), tr));
+    jac->hk[1] = vmul(w6, vcopysign_neg(vgate_eq(ramp[1], yg), tg));
+    jac->hk[2] = vmul(w6, vcopysign_neg(vgate_eq(ramp[2], yb), tb));
+    jac->ramp[0] = ramp[0]; jac->ramp[1] = ramp[1]; jac->ramp[2] = ramp[2];
     jac->oms = oms;
     jac->vs = IN_UNIT ? v : vmul(v, vgate_eq(s, in[1]));
     jac->pin_v = IN_UNIT ? T(1.0f) : vgate_eq(v, in[2]);
   }
+  rgb[0] = vfma(w, ramp[0], p);                                 // colors.py:143-150
+  rgb[1] = vfma(w, ramp[1], p);                                 // colors.py:153-159
+  rgb[2] = vfma(w, ramp[2], p);                                 // colors.py:162-168 ; colors.py:175 inert (above)
 }
 
 template <class T, bool IN_UNIT>
 CURL_HD void hsv2rgb_bwd(const Hsv2RgbJac<T>& j, const T grgb[3], T ghsv[3]) {
-  const T gr = vmul(grgb[0], j.po[0]), gg = vmul(grgb[1], j.po[1]), gb = vmul(grgb[2], j.po[2]);
-  const T gw = vfma(gr, j.dr, vfma(gg, j.dg, vmul(gb, j.db)));
-  ghsv[0] = vfma(gr, j.hr, vfma(gg, j.hg, vmul(gb, j.hb)));
-  const T gp = vsub(vadd(gg, gb), gw);          // p enters g, b directly and w = v - p
-  const T gv = vfma(gp, j.oms, vadd(gr, gw));
+  const T gw = vfma(grgb[0], j.ramp[0], vfma(grgb[1], j.ramp[1], vmul(grgb[2], j.ramp[2])));
+  ghsv[0] = vfma(grgb[0], j.hk[0], vfma(grgb[1], j.hk[1], vmul(grgb[2], j.hk[2])));
+  const T gp = vsub(vadd(vadd(grgb[0], grgb[1]), grgb[2]), gw);   // p enters r, g, b directly and w = v - p
+  const T gv = vfma(gp, j.oms, gw);                               // v enters through w and p = v (1 - s)
   ghsv[1] = vneg(vmul(gp, j.vs));
   ghsv[2] = IN_UNIT ? gv : vmul(gv, j.pin_v);
 }
@@ -546,7 +552,11 @@ CURL_HD void layer_fwd(const T x[3], T m, const float* ab, T out[3]) {
 struct KeepInRegisters {
   static constexpr bool kActive = false;
 };
-constexpr int SPILL_SLOTS = 24;   // LabJac 6 + Self3Jac 6 + RgbJac 6 + Self3Jac 6
+#ifndef CURL_PARK_STAGES
+#define CURL_PARK_STAGES 4         // how many of the first four stages' records are parked (6 slots each)
+#endif
+constexpr int PARK_STAGES = CURL_PARK_STAGES;
+constexpr int SPILL_SLOTS = 6 * PARK_STAGES;   // LabJac 6 + Self3Jac 6 + RgbJac 6 + Self3Jac 6
 
 template <class T, class S> CURL_HD void spill_save(const S& sp, int o, const LabJac<T>& j) {
 #pragma unroll
@@ -581,14 +591,14 @@ CURL_HD void layer_bwd(const T x[3], T m, const float* ab, const T gout[3], T gx
   T lab[3], lab2[3], rgb[3], rgb2[3], hsv[3], hsv2[3], res[3];
   LabJac<T> j1; Self3Jac<T> j2; RgbJac<T> j3; Self3Jac<T> j4; HsvJac<T> j5; HsvCurveJac<T> j6; Hsv2RgbJac<T> j7;
   rgb2lab_fwd<T, WANT_GX>(x, lab, &j1);
-  if constexpr (kSpill && WANT_GX) spill_save<T>(sp, 0, j1);
+  if constexpr (kSpill && WANT_GX && PARK_STAGES >= 1) spill_save<T>(sp, 0, j1);
   adjust_self3_fwd<T, true>(lab, ab, lab2, &j2);
-  if constexpr (kSpill) spill_save<T>(sp, 6, j2);
+  if constexpr (kSpill && PARK_STAGES >= 2) spill_save<T>(sp, 6, j2);
   if (MK == MASK_F32) vscale3(lab2, m);
   lab2rgb_fwd<T, true>(lab2, rgb, &j3);
-  if constexpr (kSpill) spill_save<T>(sp, 12, j3);
+  if constexpr (kSpill && PARK_STAGES >= 3) spill_save<T>(sp, 12, j3);
   adjust_self3_fwd<T, true>(rgb, ab + 6, rgb2, &j4);
-  if constexpr (kSpill) spill_save<T>(sp, 18, j4);
+  if constexpr (kSpill && PARK_STAGES >= 4) spill_save<T>(sp, 18, j4);
   if (MK == MASK_F32) vscale3(rgb2, m);
   rgb2hsv_fwd<T, true, MK != MASK_F32>(rgb2, hsv, &j5);
   adjust_hsv_fwd<T, true, true>(hsv, ab + 12, hsv2, &j6);
@@ -611,15 +621,15 @@ CURL_HD void layer_bwd(const T x[3], T m, const float* ab, const T gout[3], T gx
   adjust_hsv_bwd(j6, ab + 12, a, b, mom + 12);
   rgb2hsv_bwd(j5, b, a);
   if (MK == MASK_F32) vscale3(a, m);
-  if constexpr (kSpill) spill_load<T>(sp, 18, j4);
+  if constexpr (kSpill && PARK_STAGES >= 4) spill_load<T>(sp, 18, j4);
   adjust_self3_bwd(j4, a, b, mom + 6);
-  if constexpr (kSpill) spill_load<T>(sp, 12, j3);
+  if constexpr (kSpill && PARK_STAGES >= 3) spill_load<T>(sp, 12, j3);
   lab2rgb_bwd(j3, b, a);
   if (MK == MASK_F32) vscale3(a, m);
-  if constexpr (kSpill) spill_load<T>(sp, 6, j2);
+  if constexpr (kSpill && PARK_STAGES >= 2) spill_load<T>(sp, 6, j2);
   adjust_self3_bwd(j2, a, b, mom + 0);
   if (WANT_GX) {
-    if constexpr (kSpill) spill_load<T>(sp, 0, j1);
+    if constexpr (kSpill && PARK_STAGES >= 1) spill_load<T>(sp, 0, j1);
     rgb2lab_bwd(j1, b, a);
     gx[0] = vadd(g[0], a[0]); gx[1] = vadd(g[1], a[1]); gx[2] = vadd(g[2], a[2]);
   }

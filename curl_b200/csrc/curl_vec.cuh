@@ -67,6 +67,14 @@ CURL_HD float vsat(float x) {
 CURL_HD float vmul_sat(float a, float b) { return vsat(a * b); }
 CURL_HD float vadd_sat(float a, float b) { return vsat(a + b); }
 CURL_HD float vfma_sat(float a, float b, float c) { return vsat(fmaf(a, b, c)); }
+// |a| + c and its clamp: one FADD / FADD.SAT with the |.| operand modifier
+CURL_HD float vabs_add(float a, float c) { return fabsf(a) + c; }
+CURL_HD float vabs_add_sat(float a, float c) { return vsat(fabsf(a) + c); }
+CURL_HD float vnabs_add(float a, float c) { return c - fabsf(a); }
+CURL_HD float vnabs_add_sat(float a, float c) { return vsat(c - fabsf(a)); }
+// magnitude of g with the sign of t / of -t (one LOP3)
+CURL_HD float vcopysign(float g, float t) { return copysignf(g, t); }
+CURL_HD float vcopysign_neg(float g, float t) { return copysignf(g, -t); }
 CURL_HD float vmax(float a, float b) {
 #if defined(__CUDA_ARCH__)
   return fmaxf(a, b);
@@ -160,6 +168,11 @@ CURL_F2_MAP1(vsat)
 #endif
 CURL_F2_MAP2(vmul_sat) CURL_F2_MAP2(vadd_sat) CURL_F2_MAP3(vfma_sat)
 CURL_F2_MAP2(vmax) CURL_F2_MAP2(vmin)
+CURL_D F2 vabs_add(F2 a, float c) { return F2(vabs_add(a.lo(), c), vabs_add(a.hi(), c)); }
+CURL_D F2 vabs_add_sat(F2 a, float c) { return F2(vabs_add_sat(a.lo(), c), vabs_add_sat(a.hi(), c)); }
+CURL_D F2 vnabs_add(F2 a, float c) { return F2(vnabs_add(a.lo(), c), vnabs_add(a.hi(), c)); }
+CURL_D F2 vnabs_add_sat(F2 a, float c) { return F2(vnabs_add_sat(a.lo(), c), vnabs_add_sat(a.hi(), c)); }
+CURL_F2_MAP2(vcopysign) CURL_F2_MAP2(vcopysign_neg)
 #ifdef ABL_NOGATE
 CURL_D F2 vgate_le(F2 a, F2 b) { return F2(1.0f); }
 CURL_D F2 vgate_lt(F2 a, F2 b) { return F2(1.0f); }
@@ -190,6 +203,11 @@ CURL_F4_MAP2(vadd) CURL_F4_MAP2(vsub) CURL_F4_MAP2(vmul) CURL_F4_MAP3(vfma) CURL
 CURL_F4_MAP1(vlg2) CURL_F4_MAP1(vex2) CURL_F4_MAP1(vrcp) CURL_F4_MAP1(vsat)
 CURL_F4_MAP2(vmul_sat) CURL_F4_MAP2(vadd_sat) CURL_F4_MAP3(vfma_sat) CURL_F4_MAP2(vmax) CURL_F4_MAP2(vmin)
 CURL_F4_MAP2(vgate_le) CURL_F4_MAP2(vgate_lt) CURL_F4_MAP2(vgate_eq) CURL_F4_MAP2(vgate_ne)
+CURL_D F4 vabs_add(F4 x, float c) { return F4(vabs_add(x.a, c), vabs_add(x.b, c)); }
+CURL_D F4 vabs_add_sat(F4 x, float c) { return F4(vabs_add_sat(x.a, c), vabs_add_sat(x.b, c)); }
+CURL_D F4 vnabs_add(F4 x, float c) { return F4(vnabs_add(x.a, c), vnabs_add(x.b, c)); }
+CURL_D F4 vnabs_add_sat(F4 x, float c) { return F4(vnabs_add_sat(x.a, c), vnabs_add_sat(x.b, c)); }
+CURL_F4_MAP2(vcopysign) CURL_F4_MAP2(vcopysign_neg)
 CURL_F4_MAP4(vsel_le) CURL_F4_MAP4(vsel_lt) CURL_F4_MAP4(vsel_eq)
 CURL_D float vhsum(F4 x) { return vhsum(x.a) + vhsum(x.b); }
 #endif  // __CUDACC__
