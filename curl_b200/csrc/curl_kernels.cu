@@ -522,18 +522,19 @@ template <class Op> constexpr size_t tma_smem_bytes() {
   return TMA_RING_BYTES + (size_t)Op::SPILL * BWD_THREADS * sizeof(F2);
 }
 
-// Shared-memory parking space for Jac records (curl_pixel.cuh "Spill policies"): slot-major, one
-// 8-byte column per thread, so a warp's STS.64/LDS.64 touches 256 consecutive bytes.
+// Shared-memory parking space for Jac records (curl_pixel.cuh "Spill policies"): slot-pair-major, one
+// 16-byte column per thread and pair of slots, so a warp's STS.128/LDS.128 touches 512 consecutive bytes
+// (conflict-free) and one instruction parks or fetches two packed values.
 struct SmemSpill {
   static constexpr bool kActive = true;
-  unsigned base;   // shared-space byte address, already offset by threadIdx.x
+  unsigned base;   // shared-space byte address, already offset by threadIdx.x * 16
   // asm volatile: the compiler must not forward the stored value to the later load (that would keep
   // the value live in a register, which is exactly what parking is meant to avoid)
-  __device__ __forceinline__ void put(int slot, F2 v) const {
-    asm volatile("st.shared.b64 [%0], %1;" ::"r"(base + slot * (BWD_THREADS * 8)), "l"(v.u) : "memory");
+  __device__ __forceinline__ void put2(int slot, F2 a, F2 b) const {   // slot even: slots slot, slot + 1
+    asm volatile("st.shared.v2.b64 [%0], {%1, %2};" ::"r"(base + (slot >> 1) * (BWD_THREADS * 16)), "l"(a.u), "l"(b.u) : "memory");
   }
-  __device__ __forceinline__ F2 get(int slot) const {
-    F2 r; asm volatile("ld.shared.b64 %0, [%1];" : "=l"(r.u) : "r"(base + slot * (BWD_THREADS * 8)) : "memory"); return r;
+  __device__ __forceinline__ void get2(int slot, F2& a, F2& b) const {
+    asm volatile("ld.shared.v2.b64 {%0, %1}, [%2];" : "=l"(a.u), "=l"(b.u) : "r"(base + (slot >> 1) * (BWD_THREADS * 16)) : "memory");
   }
 };
 
@@ -657,7 +658,7 @@ __global__ void __launch_bounds__(BWD_THREADS, BWD_MIN_BLOCKS) bwd_tma_kernel(co
     T* const momi = mom;
 #endif
     if constexpr (Op::SPILL > 0) {
-      const SmemSpill sp{smem_u32(reinterpret_cast<unsigned char*>(s_ring) + TMA_RING_BYTES) + threadIdx.x * 8u};
+      const SmemSpill sp{smem_u32(reinterpret_cast<unsigned char*>(s_ring) + TMA_RING_BYTES) + threadIdx.x * 16u};
       Op::template bwd<MK, WANT_GIN, T>(x, m, s_ab, p.aux, gy, gx, momi, sp);
     } else {
       Op::template bwd<MK, WANT_GIN, T>(x, m, s_ab, p.aux, gy, gx, momi, KeepInRegisters());

@@ -546,7 +546,7 @@ CURL_HD void layer_fwd(const T x[3], T m, const float* ab, T out[3]) {
 // Spill policies for the backward pass.  At the turning point of the reverse sweep every stage's
 // Jac record is live (66 values of T), which is what limits the kernel to 8 warps per SM.  The
 // records of the first four stages are not needed again until the very end, so the sm_100a kernel
-// parks them in shared memory (one 8-byte column per thread: conflict-free) and gets them back
+// parks them in shared memory (one 16-byte column per thread and pair of values: conflict-free) and gets them back
 // when the reverse sweep reaches their stage.  KeepInRegisters is the no-op policy (host check,
 // scalar tail path).
 struct KeepInRegisters {
@@ -558,33 +558,30 @@ struct KeepInRegisters {
 constexpr int PARK_STAGES = CURL_PARK_STAGES;
 constexpr int SPILL_SLOTS = 6 * PARK_STAGES;   // LabJac 6 + Self3Jac 6 + RgbJac 6 + Self3Jac 6
 
+// Six values per record, parked and fetched two at a time (put2 / get2 on an even slot).
 template <class T, class S> CURL_HD void spill_save(const S& sp, int o, const LabJac<T>& j) {
-#pragma unroll
-  for (int c = 0; c < 3; ++c) { sp.put(o + c, j.d_lin[c]); sp.put(o + 3 + c, j.d_f[c]); }
+  sp.put2(o, j.d_lin[0], j.d_lin[1]); sp.put2(o + 2, j.d_lin[2], j.d_f[0]); sp.put2(o + 4, j.d_f[1], j.d_f[2]);
 }
 template <class T, class S> CURL_HD void spill_load(const S& sp, int o, LabJac<T>& j) {
-#pragma unroll
-  for (int c = 0; c < 3; ++c) { j.d_lin[c] = sp.get(o + c); j.d_f[c] = sp.get(o + 3 + c); }
+  sp.get2(o, j.d_lin[0], j.d_lin[1]); sp.get2(o + 2, j.d_lin[2], j.d_f[0]); sp.get2(o + 4, j.d_f[1], j.d_f[2]);
 }
 template <class T, class S> CURL_HD void spill_save(const S& sp, int o, const RgbJac<T>& j) {
-#pragma unroll
-  for (int c = 0; c < 3; ++c) { sp.put(o + c, j.d_finv[c]); sp.put(o + 3 + c, j.d_gam[c]); }
+  sp.put2(o, j.d_finv[0], j.d_finv[1]); sp.put2(o + 2, j.d_finv[2], j.d_gam[0]); sp.put2(o + 4, j.d_gam[1], j.d_gam[2]);
 }
 template <class T, class S> CURL_HD void spill_load(const S& sp, int o, RgbJac<T>& j) {
-#pragma unroll
-  for (int c = 0; c < 3; ++c) { j.d_finv[c] = sp.get(o + c); j.d_gam[c] = sp.get(o + 3 + c); }
+  sp.get2(o, j.d_finv[0], j.d_finv[1]); sp.get2(o + 2, j.d_finv[2], j.d_gam[0]); sp.get2(o + 4, j.d_gam[1], j.d_gam[2]);
 }
 template <class T, class S> CURL_HD void spill_save(const S& sp, int o, const Self3Jac<T>& j) {
 #pragma unroll
-  for (int c = 0; c < 3; ++c) { sp.put(o + 2 * c, j.c[c].a); sp.put(o + 2 * c + 1, j.c[c].d); }
+  for (int c = 0; c < 3; ++c) sp.put2(o + 2 * c, j.c[c].a, j.c[c].d);
 }
 template <class T, class S> CURL_HD void spill_load(const S& sp, int o, Self3Jac<T>& j) {
 #pragma unroll
-  for (int c = 0; c < 3; ++c) { j.c[c].a = sp.get(o + 2 * c); j.c[c].d = sp.get(o + 2 * c + 1); }
+  for (int c = 0; c < 3; ++c) sp.get2(o + 2 * c, j.c[c].a, j.c[c].d);
 }
 
 // Recompute-forward + reverse.  mom: 20 accumulators (S0,S1 per curve), accumulated in place.
-// SPILL: a policy with put(slot, T) / get(slot) (see above) or KeepInRegisters.
+// SPILL: a policy with put2(slot, T, T) / get2(slot, T&, T&) (see above) or KeepInRegisters.
 template <class T, int MK, bool WANT_GX, class SPILL>
 CURL_HD void layer_bwd(const T x[3], T m, const float* ab, const T gout[3], T gx[3], T* mom, const SPILL& sp) {
   constexpr bool kSpill = SPILL::kActive;
