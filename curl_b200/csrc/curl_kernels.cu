@@ -14,12 +14,15 @@
 
 namespace curl {
 
-constexpr int THREADS = 256;
+#ifndef CURL_THREADS
+#define CURL_THREADS 256
+#endif
+constexpr int THREADS = CURL_THREADS;
 // Backward (aligned path) launch shape: three independent 128-thread blocks per SM (144 registers
 // each) instead of one 384-thread block.  Same 12 warps per SM, but each scheduler holds one warp of
 // each block, the per-stage barrier spans 4 warps instead of 12 and the blocks drift apart, so their
-// MUFU / gate / FMA phases interleave: 4K x 16 backward 2.357 -> 2.165 ms; with two sub-tiles per
-// stage (BWD_PAIRS, one barrier + one refill per 512 px) 2.131 ms.  Measured alternatives, ms:
+// MUFU / gate / FMA phases interleave: 4K x 16 backward 2.357 -> 2.165 ms; with several sub-tiles per
+// stage (BWD_PAIRS, one barrier + one refill per 768 px, two stages) 2.13 ms.  Measured alternatives, ms:
 // 192x2 2.343, 96x4 2.377, 64x6 2.234, 32x12 2.317, 128x4 at 128 registers (BWD_SCALAR_MOM) 2.121.
 #ifndef BWD_THREADS
 #define BWD_THREADS 128
@@ -508,12 +511,12 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned by
 }
 
 #ifndef BWD_PAIRS
-#define BWD_PAIRS 2
+#define BWD_PAIRS 3
 #endif
 constexpr int TMA_SUB = BWD_THREADS * 2;        // pixels per sub-tile: one packed pair per thread
 constexpr int TMA_TILE = TMA_SUB * BWD_PAIRS;   // pixels per stage: BWD_PAIRS sub-tiles, one barrier + one refill per stage
 #ifndef TMA_STAGES_N
-#define TMA_STAGES_N 3
+#define TMA_STAGES_N 2
 #endif
 constexpr int TMA_STAGES = TMA_STAGES_N;
 constexpr int TMA_PLANES = 6;           // x0 x1 x2 g0 g1 g2
@@ -633,7 +636,18 @@ __global__ void __launch_bounds__(BWD_THREADS, BWD_MIN_BLOCKS) bwd_tma_kernel(co
     } else if (MK == MASK_F32) {
       m = F2(m_raw.x, m_raw.y);
     }
-    if (q == 0) mbar_wait(&s_full[s], (unsigned)(it / TMA_STAGES) & 1u);
+    if (q == 0) {
+      // Refill of the stage the block finished with its previous tile.  The barrier sits here, after that
+      // tile's arithmetic, and not right behind its shared-memory reads: BAR.SYNC does not wait for a
+      // warp's outstanding LDS, so a refill issued straight after such a barrier can land before a
+      // congested warp's reads of the old tile are served (seen as rare run-to-run differences of whole
+      // warps' pixels with three blocks per SM).  Here every read of the old tile has been consumed.
+      if (it > 0) {
+        __syncthreads();
+        if (threadIdx.x == 0 && it - 1 + TMA_STAGES < n_my) issue(it - 1 + TMA_STAGES);
+      }
+      mbar_wait(&s_full[s], (unsigned)(it / TMA_STAGES) & 1u);
+    }
     const float* src = s_ring + (size_t)s * TMA_PLANES * TMA_TILE + q * TMA_SUB + threadIdx.x * 2;
     T x[3], gy[3];
 #pragma unroll
@@ -643,10 +657,6 @@ __global__ void __launch_bounds__(BWD_THREADS, BWD_MIN_BLOCKS) bwd_tma_kernel(co
       x[c] = F2(a.x, a.y);
       // a tail pair's gradient is switched off through m (= 0) where a mask multiplies it anyway
       gy[c] = (MK == MASK_NONE && !valid) ? F2(0.0f) : F2(g.x, g.y);
-    }
-    if (q == BWD_PAIRS - 1) {
-      __syncthreads();                                  // every thread has read all of stage s
-      if (threadIdx.x == 0 && it + TMA_STAGES < n_my) issue(it + TMA_STAGES);
     }
     if (!valid) m = T(0.0f);
     T gx[3];

@@ -218,6 +218,38 @@ def test_masked_pixels_are_zero_and_inputs_untouched():
     assert out.min().item() >= 0.0 and out.max().item() <= 1.0
 
 
+def test_backward_run_to_run_determinism():
+    """The backward is bitwise reproducible run to run, with and without the image gradient, over many repeats
+    at shapes that keep every SM's three resident blocks busy.  Guards the shared-memory ring of the backward
+    kernel: a stage may only be refilled once every warp's reads of it have been consumed (a refill issued
+    right behind a barrier that does not wait for outstanding LDS showed up as rare differences of whole
+    warps' pixels)."""
+    import curl_b200
+    dev = torch.device("cuda:0")
+    gen = torch.Generator(device=dev).manual_seed(11)
+    layer = curl_b200.CURLLayer().to(dev)
+    for B, H, W, reps in ((4, 2160, 3840, 12), (3, 1080, 1920, 40), (32, 512, 512, 40)):
+        img0 = torch.rand(B, 3, H, W, generator=gen, device=dev)
+        mask = torch.rand(B, 1, H, W, generator=gen, device=dev) > 0.1
+        Ls = [(0.1 * torch.randn(B, n, generator=gen, device=dev)).requires_grad_(True) for n in (48, 48, 64)]
+        gout = torch.randn(B, 3, H, W, generator=gen, device=dev)
+        for want_gimg in (True, False):
+            first = None
+            for _ in range(reps):
+                img = img0.clone().requires_grad_(want_gimg)
+                for t in Ls:
+                    t.grad = None
+                o, r = layer(img, mask, *Ls)
+                torch.autograd.backward([o, r], [gout, torch.ones_like(r)])
+                cur = [t.grad.clone() for t in Ls] + ([img.grad] if want_gimg else [])
+                if first is None:
+                    first = cur
+                else:
+                    for a, b in zip(cur, first):
+                        assert torch.equal(a, b)
+        del img0, mask, gout, first, cur
+
+
 def test_full_size_properties():
     """BASELINE config sizes (1080p batch 16 forward; 4K batch 4 fwd+bwd): size-independent checks --
     range, mask zeros, determinism, batch-shard equality (no cross-image coupling), knot-gradient
