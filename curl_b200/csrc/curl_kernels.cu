@@ -605,11 +605,9 @@ __global__ void __launch_bounds__(BWD_THREADS, BWD_MIN_BLOCKS) bwd_tma_kernel(co
 
   // The mask plane is only 4-byte aligned in general, so it cannot ride the bulk copies; it is
   // fetched with an ordinary load one whole iteration ahead (raw bits kept in one register pair).
-  auto mask_raw = [&](int j) -> float2 {   // j: sub-tile counter of this block, BWD_PAIRS per stage
-    const int it = j / BWD_PAIRS, q = j % BWD_PAIRS;
-    const int px = (blockIdx.x + it * gridDim.x) * TMA_TILE + q * TMA_SUB + threadIdx.x * 2;
+  auto mask_raw = [&](int px) -> float2 {   // px: this thread's first pixel of a sub-tile (>= HW past the block's work)
     float2 r = make_float2(1.0f, 1.0f);
-    if (MK == MASK_NONE || it >= n_my || px >= HW) return r;
+    if (MK == MASK_NONE || px >= HW) return r;
     if (MK == MASK_U8) {
       const unsigned short u = __ldcs(reinterpret_cast<const unsigned short*>(
           reinterpret_cast<const unsigned char*>(p.mask) + (size_t)b * HW + px));
@@ -619,69 +617,77 @@ __global__ void __launch_bounds__(BWD_THREADS, BWD_MIN_BLOCKS) bwd_tma_kernel(co
     }
     return r;
   };
-  float2 m_next = mask_raw(0);
+  // Indices advance by addition only (tile by tile, sub-tile by sub-tile): the flat "sub-tile counter" form
+  // cost ~40 integer instructions per sub-tile in divisions by the sub-tile and stage counts.
+  const int tile_stride = (int)gridDim.x * TMA_TILE;
+  int px_tile = (int)blockIdx.x * TMA_TILE + (int)threadIdx.x * 2;   // a block's tile indices never reach n_tiles + gridDim.x: no overflow
+  float2 m_next = (n_my > 0) ? mask_raw(px_tile) : make_float2(1.0f, 1.0f);
+  int s = 0;
+  unsigned parity = 0u;
 
 #pragma unroll 1
-  for (int j = 0; j < n_my * BWD_PAIRS; ++j) {
-    const int it = j / BWD_PAIRS, q = j % BWD_PAIRS;
-    const int s = it % TMA_STAGES;
-    const int px = (blockIdx.x + it * gridDim.x) * TMA_TILE + q * TMA_SUB + threadIdx.x * 2;
-    const bool valid = px < HW;     // HW is even: a pair is either fully inside or fully outside
-    const float2 m_raw = m_next;
-    m_next = mask_raw(j + 1);
-    T m = T(1.0f);
-    if (MK == MASK_U8) {
-      const unsigned u = __float_as_uint(m_raw.x);
-      m = F2((u & 0xffu) ? 1.0f : 0.0f, (u & 0xff00u) ? 1.0f : 0.0f);
-    } else if (MK == MASK_F32) {
-      m = F2(m_raw.x, m_raw.y);
+  for (int it = 0; it < n_my; ++it, px_tile += tile_stride) {
+    // Refill of the stage the block finished with its previous tile.  The barrier sits here, after that
+    // tile's arithmetic, and not right behind its shared-memory reads: BAR.SYNC does not wait for a
+    // warp's outstanding LDS, so a refill issued straight after such a barrier can land before a
+    // congested warp's reads of the old tile are served (seen as rare run-to-run differences of whole
+    // warps' pixels with three blocks per SM).  Here every read of the old tile has been consumed.
+    if (it > 0) {
+      __syncthreads();
+      if (threadIdx.x == 0 && it - 1 + TMA_STAGES < n_my) issue(it - 1 + TMA_STAGES);
     }
-    if (q == 0) {
-      // Refill of the stage the block finished with its previous tile.  The barrier sits here, after that
-      // tile's arithmetic, and not right behind its shared-memory reads: BAR.SYNC does not wait for a
-      // warp's outstanding LDS, so a refill issued straight after such a barrier can land before a
-      // congested warp's reads of the old tile are served (seen as rare run-to-run differences of whole
-      // warps' pixels with three blocks per SM).  Here every read of the old tile has been consumed.
-      if (it > 0) {
-        __syncthreads();
-        if (threadIdx.x == 0 && it - 1 + TMA_STAGES < n_my) issue(it - 1 + TMA_STAGES);
+    mbar_wait(&s_full[s], parity);
+    const float* stage = s_ring + (size_t)s * TMA_PLANES * TMA_TILE + threadIdx.x * 2;
+    if (++s == TMA_STAGES) { s = 0; parity ^= 1u; }
+#pragma unroll 1
+    for (int q = 0; q < BWD_PAIRS; ++q) {
+      const int px = px_tile + q * TMA_SUB;
+      const bool valid = px < HW;     // HW is even: a pair is either fully inside or fully outside
+      const float2 m_raw = m_next;
+      // next sub-tile of this tile, or the first of the block's next tile (past the image once the block is done)
+      m_next = mask_raw(q + 1 < BWD_PAIRS ? px + TMA_SUB : px_tile + tile_stride);
+      T m = T(1.0f);
+      if (MK == MASK_U8) {
+        const unsigned u = __float_as_uint(m_raw.x);
+        m = F2((u & 0xffu) ? 1.0f : 0.0f, (u & 0xff00u) ? 1.0f : 0.0f);
+      } else if (MK == MASK_F32) {
+        m = F2(m_raw.x, m_raw.y);
       }
-      mbar_wait(&s_full[s], (unsigned)(it / TMA_STAGES) & 1u);
-    }
-    const float* src = s_ring + (size_t)s * TMA_PLANES * TMA_TILE + q * TMA_SUB + threadIdx.x * 2;
-    T x[3], gy[3];
+      const float* src = stage + q * TMA_SUB;
+      T x[3], gy[3];
 #pragma unroll
-    for (int c = 0; c < 3; ++c) {
-      const float2 a = *reinterpret_cast<const float2*>(src + c * TMA_TILE);
-      const float2 g = *reinterpret_cast<const float2*>(src + (3 + c) * TMA_TILE);
-      x[c] = F2(a.x, a.y);
-      // a tail pair's gradient is switched off through m (= 0) where a mask multiplies it anyway
-      gy[c] = (MK == MASK_NONE && !valid) ? F2(0.0f) : F2(g.x, g.y);
-    }
-    if (!valid) m = T(0.0f);
-    T gx[3];
+      for (int c = 0; c < 3; ++c) {
+        const float2 a = *reinterpret_cast<const float2*>(src + c * TMA_TILE);
+        const float2 g = *reinterpret_cast<const float2*>(src + (3 + c) * TMA_TILE);
+        x[c] = F2(a.x, a.y);
+        // a tail pair's gradient is switched off through m (= 0) where a mask multiplies it anyway
+        gy[c] = (MK == MASK_NONE && !valid) ? F2(0.0f) : F2(g.x, g.y);
+      }
+      if (!valid) m = T(0.0f);
+      T gx[3];
 #ifdef BWD_SCALAR_MOM
-    T momi[NM > 0 ? NM : 1];
+      T momi[NM > 0 ? NM : 1];
 #pragma unroll
-    for (int k = 0; k < NM; ++k) momi[k] = T(0.0f);
+      for (int k = 0; k < NM; ++k) momi[k] = T(0.0f);
 #else
-    T* const momi = mom;
+      T* const momi = mom;
 #endif
-    if constexpr (Op::SPILL > 0) {
-      const SmemSpill sp{smem_u32(reinterpret_cast<unsigned char*>(s_ring) + TMA_RING_BYTES) + threadIdx.x * 16u};
-      Op::template bwd<MK, WANT_GIN, T>(x, m, s_ab, p.aux, gy, gx, momi, sp);
-    } else {
-      Op::template bwd<MK, WANT_GIN, T>(x, m, s_ab, p.aux, gy, gx, momi, KeepInRegisters());
-    }
+      if constexpr (Op::SPILL > 0) {
+        const SmemSpill sp{smem_u32(reinterpret_cast<unsigned char*>(s_ring) + TMA_RING_BYTES) + threadIdx.x * 16u};
+        Op::template bwd<MK, WANT_GIN, T>(x, m, s_ab, p.aux, gy, gx, momi, sp);
+      } else {
+        Op::template bwd<MK, WANT_GIN, T>(x, m, s_ab, p.aux, gy, gx, momi, KeepInRegisters());
+      }
 #ifdef BWD_SCALAR_MOM
 #pragma unroll
-    for (int k = 0; k < NM; ++k) mom[k] += vhsum(momi[k]);
+      for (int k = 0; k < NM; ++k) mom[k] += vhsum(momi[k]);
 #endif
-    if (WANT_GIN && valid) {
+      if (WANT_GIN && valid) {
 #pragma unroll
-      for (int c = 0; c < 3; ++c)
-        __stcs(reinterpret_cast<float2*>(gin + (size_t)c * HW + px), make_float2(gx[c].lo(), gx[c].hi()));
-    }
+        for (int c = 0; c < 3; ++c)
+          __stcs(reinterpret_cast<float2*>(gin + (size_t)c * HW + px), make_float2(gx[c].lo(), gx[c].hi()));
+      }
+    }   // sub-tiles
   }
 #ifdef BWD_SCALAR_MOM
   if (NC > 0) finish_knot_grads<NC, float, BWD_THREADS>(p, b, mom, s_C, s_mom, s_part, &s_ticket);
