@@ -341,7 +341,8 @@ CURL_HD void hsv2rgb_fwd(const T in[3], T rgb[3], Hsv2RgbJac<T>* jac) {
   const T oms = vsub(T(1.0f), s);
   const T p = vmul(v, oms);
   const T w = vsub(v, p);
-  const T tr = vfma(h, T(6.0f), T(-3.0f)), tg = vfma(h, T(6.0f), T(-2.0f)), tb = vfma(h, T(6.0f), T(-4.0f));
+  // tg, tb carry the sign of the falling-side convention (2 - k, 4 - k): |.| is the same and the slope sign is theirs
+  const T tr = vfma(h, T(6.0f), T(-3.0f)), tg = vfma(h, T(-6.0f), T(2.0f)), tb = vfma(h, T(-6.0f), T(4.0f));
   T ramp[3];
   if (!JAC) {
     ramp[0] = vabs_add_sat(tr, -1.0f); ramp[1] = vnabs_add_sat(tg, 2.0f); ramp[2] = vnabs_add_sat(tb, 2.0f);
@@ -352,8 +353,8 @@ CURL_HD void hsv2rgb_fwd(const T in[3], T rgb[3], Hsv2RgbJac<T>* jac) {
     if (!IN_UNIT) w6 = vmul(w6, vgate_eq(h, in[0]));
     // on a slope (ends included, as torch.clamp passes gradient on the closed interval): +-1, else 0
     jac->hk[0] = vmul(w6, vcopysign(vgate_eq(ramp[0], yr), tr));
-    jac->hk[1] = vmul(w6, vcopysign_neg(vgate_eq(ramp[1], yg), tg));
-    jac->hk[2] = vmul(w6, vcopysign_neg(vgate_eq(ramp[2], yb), tb));
+    jac->hk[1] = vmul(w6, vcopysign(vgate_eq(ramp[1], yg), tg));
+    jac->hk[2] = vmul(w6, vcopysign(vgate_eq(ramp[2], yb), tb));
     jac->ramp[0] = ramp[0]; jac->ramp[1] = ramp[1]; jac->ramp[2] = ramp[2];
     jac->oms = oms;
     jac->vs = IN_UNIT ? v : vmul(v, vgate_eq(s, in[1]));
