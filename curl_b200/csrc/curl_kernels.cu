@@ -15,7 +15,7 @@
 namespace curl {
 
 #ifndef CURL_THREADS
-#define CURL_THREADS 256
+#define CURL_THREADS 128   // forward: 128 x 64 blocks per SM measured 1.7-2 % faster than 256 x 16 at 4K (3.215 -> 3.160 ms at batch 64)
 #endif
 constexpr int THREADS = CURL_THREADS;
 // Backward (aligned path) launch shape: three independent 128-thread blocks per SM (144 registers
@@ -733,7 +733,7 @@ static int blocks_per_image(int B, int HW, int vec, int blocks_per_sm) {
 constexpr int BWD_GRID_BLOCKS_PER_SM = BWD_GRID_BPS;
 constexpr int BWD_VEC = 2;   // pixels per thread per iteration on the aligned backward path
 #ifndef FWD_GRID_BPS
-#define FWD_GRID_BPS 16
+#define FWD_GRID_BPS 64
 #endif
 constexpr int FWD_GRID_BLOCKS_PER_SM = FWD_GRID_BPS;
 
