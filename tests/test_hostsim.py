@@ -168,3 +168,41 @@ def test_hostsim_segment_clamp_vs_oracle(shape, sigma, masked):
     assert rel_to_max(f["reg"], r64["reg"].numpy()) <= 1e-5
     for k in ("gimg", "gL", "gR", "gH"):
         assert rel_to_max(b[k], r64[k].numpy()) <= max(1e-4, 3 * rel_to_max(r32[k].numpy(), r64[k].numpy())), k
+
+
+def test_hsv2rgb_unclamped_output_stays_in_unit_range_and_matches_reference():
+    """HSV->RGB is evaluated as one trapezoid per channel and without the reference's output clamp
+    (colors.py:175), which is inert for that form: every channel is fl(p + w ramp) with 0 <= p <= v <= 1,
+    0 <= w <= v, 0 <= ramp <= 1.  Dense random inputs, inputs outside [0, 1] and every ramp end (hue = n/6,
+    their float neighbours, 0, 1, 1e-9; s, v in {0, 1e-9, 1/3, 1 - 2^-24, 1}) stay inside [0, 1] and agree with the
+    reference's two-ramp form; at the ramp ends the hue gradient is the reference's (closed clamp intervals)."""
+    import torch
+    from oracle import curl_oracle as O
+    rng = np.random.default_rng(3)
+    hues = [0.0, 1e-9, 1.0]
+    for n in range(1, 6):
+        h = np.float32(n / 6.0)
+        hues += [float(h), float(np.nextafter(h, np.float32(0))), float(np.nextafter(h, np.float32(1)))]
+    sv = [0.0, 1e-9, 1.0 / 3.0, float(np.float32(1) - np.float32(2.0 ** -24)), 1.0]
+    grid = np.array([(h, s, v) for h in hues for s in sv for v in sv], np.float32)          # [n, 3]
+    dense = rng.random((200000, 3), dtype=np.float32)
+    wild = (rng.random((20000, 3), dtype=np.float32) * 3.0 - 1.0)                           # outside [0, 1] too
+    x = np.concatenate([grid, dense, wild]).T.reshape(1, 3, 1, -1).copy()
+    y = hostsim.color(3, x)
+    assert y.min() >= 0.0 and y.max() <= 1.0
+    ref = O.hsv2rgb(torch.from_numpy(x).double()).numpy()
+    assert np.abs(y - ref).max() <= 2e-6
+    # gradients on the grid of ramp ends and on generic points against the fp64 reference
+    xg = np.concatenate([grid, dense[:20000]]).T.reshape(1, 3, 1, -1).copy()
+    gy = rng.standard_normal(xg.shape).astype(np.float32)
+    gx = hostsim.color(3, xg, gy)
+    t = torch.from_numpy(xg).double().requires_grad_(True)
+    O.hsv2rgb(t).backward(torch.from_numpy(gy).double())
+    gref = t.grad.numpy()
+    bad = np.abs(gx - gref) > 1e-4 * max(1.0, np.abs(gref).max())
+    # a hue within one float step of a ramp end may take the neighbouring slope in fp32 (the reference's own
+    # fp32 run does too); exact ends and generic points must agree
+    near_end = np.zeros(xg.shape[-1], bool)
+    k6 = xg[0, 0, 0].astype(np.float64) * 6.0
+    near_end |= (np.abs(k6 - np.round(k6)) < 1e-6) & (np.abs(k6 - np.round(k6)) > 0)
+    assert not bad[:, :, :, ~near_end].any()
