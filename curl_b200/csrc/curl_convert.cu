@@ -7,6 +7,7 @@
 
 #include "../../include/curl_b200.h"
 #include "curl_vec.cuh"
+#include "curl_host.cuh"
 
 namespace curl {
 namespace cvt {
@@ -61,12 +62,7 @@ __global__ void __launch_bounds__(THREADS) u8_to_unit_kernel(const unsigned char
   }
 }
 
-static int sm_count() {
-  int dev = 0, n = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess) return 148;
-  if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) return 148;
-  return n;
-}
+using host::sm_count;
 
 }  // namespace cvt
 }  // namespace curl

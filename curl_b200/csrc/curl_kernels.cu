@@ -11,6 +11,7 @@
 
 #include "../../include/curl_b200.h"
 #include "curl_pixel.cuh"
+#include "curl_host.cuh"
 
 namespace curl {
 
@@ -704,27 +705,25 @@ __global__ void __launch_bounds__(BWD_THREADS, BWD_MIN_BLOCKS) bwd_tma_kernel(co
 // ---------------------------------------------------------------------------------------------
 // Host side
 // ---------------------------------------------------------------------------------------------
-static int sm_count() {
-  static int cached[64] = {0};
-  int dev = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
-  if (cached[dev] == 0) {
-    int n = 0;
-    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
-    cached[dev] = n;
-  }
-  return cached[dev];
+using host::sm_count;
+using host::ensure_dyn_smem;
+
+// Test hook (curl_test_set_grid_cap): when > 0, no kernel of this translation unit is launched with more
+// than this many blocks per image, so that SMALL test images drive every block through several loop
+// iterations (ring-stage reuse, mbarrier parity flips, grid-stride steps) -- the code paths the large
+// benchmark shapes run.  0 (the default) leaves the launch shapes alone.
+static int g_grid_cap = 0;
+static int apply_grid_cap(long long n) {
+  if (g_grid_cap > 0 && n > g_grid_cap) n = g_grid_cap;
+  return (int)(n < 1 ? 1 : n);
 }
 
-// Blocks along x for one image: enough tiles to cover it, capped so the whole grid is about
-// `waves` resident waves of the machine (each block then loops over its share of the image).
 static int blocks_per_image(int B, int HW, int vec, int blocks_per_sm) {
   const long long tiles = ((long long)HW + (long long)THREADS * vec - 1) / ((long long)THREADS * vec);
   long long cap = ((long long)sm_count() * blocks_per_sm + B - 1) / B;
   if (cap < 1) cap = 1;
   long long n = tiles < cap ? tiles : cap;
-  if (n < 1) n = 1;
-  return (int)n;
+  return apply_grid_cap(n);
 }
 
 #ifndef BWD_GRID_BPS
@@ -751,9 +750,9 @@ static int launch_fwd(const KParams& p, int B, bool vec4, cudaStream_t st) {
   return check_launch();
 }
 
-// Backward grid: one block is resident per SM, so the grid is sized to a whole number of waves
-// (B * grid.x a multiple of the SM count) whenever some wave count in [W, 2W] allows it; a partial
-// last wave costs up to one full wave of time.
+// Backward grid: BWD_MIN_BLOCKS blocks are resident per SM, so the grid is sized to a whole number of waves
+// (B * grid.x a multiple of SM count x resident blocks) whenever some wave count in [W, 2W] allows it; a
+// partial last wave costs up to one full wave of time.
 static int bwd_grid_x(int B, int HW, int vec) {
   const int px_per_tile = (vec == 1 ? THREADS : TMA_TILE);
   const long long tiles = ((long long)HW + px_per_tile - 1) / px_per_tile;
@@ -762,11 +761,11 @@ static int bwd_grid_x(int B, int HW, int vec) {
   constexpr int R = BWD_MIN_BLOCKS;
   for (int w = BWD_GRID_BLOCKS_PER_SM * R; w <= 2 * BWD_GRID_BLOCKS_PER_SM * R; w += R) {
     const long long total = (long long)sms * w;
-    if (total % B == 0 && total / B <= tiles) return (int)(total / B);
+    if (total % B == 0 && total / B <= tiles) return apply_grid_cap(total / B);
   }
   long long cap = ((long long)sms * BWD_GRID_BLOCKS_PER_SM * R + B - 1) / B;
   long long n = tiles < cap ? tiles : cap;
-  return (int)(n < 1 ? 1 : n);
+  return apply_grid_cap(n);
 }
 
 template <class Op, int MK>
@@ -784,12 +783,10 @@ static int launch_bwd(KParams& p, int B, bool vec4, void* ws, size_t ws_bytes, c
   const bool want = p.out != nullptr;
   if (vec4) {
     if (want) {
-      if (cudaFuncSetAttribute(bwd_tma_kernel<Op, MK, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                               (int)tma_smem_bytes<Op>()) != cudaSuccess) return CURL_ERR_LAUNCH;
+      if (!ensure_dyn_smem<bwd_tma_kernel<Op, MK, true>>(tma_smem_bytes<Op>())) return CURL_ERR_LAUNCH;
       bwd_tma_kernel<Op, MK, true><<<grid, BWD_THREADS, tma_smem_bytes<Op>(), st>>>(p);
     } else {
-      if (cudaFuncSetAttribute(bwd_tma_kernel<Op, MK, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                               (int)tma_smem_bytes<Op>()) != cudaSuccess) return CURL_ERR_LAUNCH;
+      if (!ensure_dyn_smem<bwd_tma_kernel<Op, MK, false>>(tma_smem_bytes<Op>())) return CURL_ERR_LAUNCH;
       bwd_tma_kernel<Op, MK, false><<<grid, BWD_THREADS, tma_smem_bytes<Op>(), st>>>(p);
     }
   } else {
@@ -820,6 +817,12 @@ using namespace curl;
 extern "C" {
 
 int curl_abi_version(void) { return CURL_ABI_VERSION; }
+
+int curl_test_set_grid_cap(int max_blocks_per_image) {
+  const int old = g_grid_cap;
+  g_grid_cap = max_blocks_per_image > 0 ? max_blocks_per_image : 0;
+  return old;
+}
 
 const char* curl_strerror(int code) {
   switch (code) {

@@ -6,6 +6,7 @@
 
 #include "../../include/curl_b200.h"
 #include "curl_loss.cuh"
+#include "curl_host.cuh"
 
 namespace curl {
 namespace loss {
@@ -28,12 +29,7 @@ struct LParams {
   int HW;
 };
 
-static int sm_count() {
-  int dev = 0, n = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess) return 148;
-  if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) return 148;
-  return n;
-}
+using host::sm_count;
 
 template <int MK>
 __device__ __forceinline__ float mask1(const void* mask, size_t i) {

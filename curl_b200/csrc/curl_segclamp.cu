@@ -13,6 +13,7 @@
 
 #include "../../include/curl_b200.h"
 #include "curl_seg.cuh"
+#include "curl_host.cuh"
 
 namespace curl {
 namespace seg {
@@ -40,12 +41,7 @@ struct SParams {
 
 __host__ __device__ inline int total_knots(const int K[3]) { return 3 * K[0] + 3 * K[1] + 4 * K[2]; }
 
-static int sm_count() {
-  int dev = 0, n = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess) return 148;
-  if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) return 148;
-  return n;
-}
+using host::sm_count;
 
 template <int MK>
 __device__ __forceinline__ float mask1(const void* mask, size_t i) {
@@ -226,8 +222,9 @@ static int launch_bwd(SParams& p, int B, cudaStream_t st) {
   p.rep = hist_copies(NK);
   const dim3 grid(grid_x(B, p.HW, BWD_BLOCKS_PER_SM), B);
   auto kern = p.gimg ? seg_bwd_kernel<MK, true> : seg_bwd_kernel<MK, false>;
-  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_smem(NK, p.rep)) != cudaSuccess)
-    return CURL_ERR_LAUNCH;
+  const bool ok = p.gimg ? host::ensure_dyn_smem<seg_bwd_kernel<MK, true>>(bwd_smem(NK, p.rep))
+                         : host::ensure_dyn_smem<seg_bwd_kernel<MK, false>>(bwd_smem(NK, p.rep));
+  if (!ok) return CURL_ERR_LAUNCH;
   kern<<<grid, THREADS, bwd_smem(NK, p.rep), st>>>(p);
   return cudaGetLastError() == cudaSuccess ? CURL_OK : CURL_ERR_LAUNCH;
 }

@@ -11,6 +11,7 @@
 
 #include "../../include/curl_b200.h"
 #include "curl_poly.cuh"
+#include "curl_host.cuh"
 
 namespace curl {
 namespace tri {
@@ -38,12 +39,7 @@ struct TParams {
   int clamp;             // apply generate_image: clamp(img + residual, 0, 1)
 };
 
-static int sm_count() {
-  int dev = 0, n = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess) return 148;
-  if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) return 148;
-  return n;
-}
+using host::sm_count;
 
 // coefficients of image b -> shared memory as [space][monomial] Coef4 records {c0, c1, c2, 0}
 template <int NC>
@@ -362,8 +358,9 @@ static int launch_fwd(const TParams& p, int B, int vec, cudaStream_t st) {
 template <int NV>
 static int launch_bwd(const TParams& p, int B, cudaStream_t st) {
   auto kern = p.sig ? trispace_bwd_kernel<NV, true> : trispace_bwd_kernel<NV, false>;
-  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_smem_bytes<NV>()) != cudaSuccess)
-    return CURL_ERR_LAUNCH;
+  const bool ok = p.sig ? host::ensure_dyn_smem<trispace_bwd_kernel<NV, true>>(bwd_smem_bytes<NV>())
+                        : host::ensure_dyn_smem<trispace_bwd_kernel<NV, false>>(bwd_smem_bytes<NV>());
+  if (!ok) return CURL_ERR_LAUNCH;
   dim3 grid(bwd_grid_x(B, p.HW), B);
   kern<<<grid, BT, bwd_smem_bytes<NV>(), st>>>(p);
   return cudaGetLastError() == cudaSuccess ? CURL_OK : CURL_ERR_LAUNCH;

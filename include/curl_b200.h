@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define CURL_ABI_VERSION 7
+#define CURL_ABI_VERSION 8
 
 /* error codes */
 #define CURL_OK 0
@@ -56,6 +56,17 @@ extern "C" {
 
 int curl_abi_version(void);
 const char* curl_strerror(int code);
+
+/*
+ * TEST HOOK, not part of the reference-facing surface (the reference has nothing like it): caps the
+ * number of blocks per image every layer / colour / curve kernel is launched with (0 = no cap, the
+ * default) and returns the previous cap.  With a small cap a SMALL image drives each block through
+ * many tiles -- shared-memory ring reuse, mbarrier parity flips, grid-stride steps -- so the parity
+ * tests can compare exactly the loop structure the 4K benchmark shapes run against the CPU oracle.
+ * Process-global and not thread-safe: set it, run the test, restore it.  Results do not depend on
+ * the cap except for the summation order of the knot-gradient partials.
+ */
+int curl_test_set_grid_cap(int max_blocks_per_image);
 
 /*
  * Fused forward of the whole layer.  Replaces CURLLayer.forward (model.py:137-176):

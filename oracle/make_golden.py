@@ -145,7 +145,8 @@ def main():
     np.savez_compressed(os.path.join(GOLDEN_DIR, "stages.npz"), **blob)
     trispace_golden()
     loss_golden()
-    for f in ("layer.npz", "stages.npz", "trispace.npz", "loss.npz"):
+    real_golden()
+    for f in ("layer.npz", "stages.npz", "trispace.npz", "loss.npz", "real.npz"):
         print(f, os.path.getsize(os.path.join(GOLDEN_DIR, f)), "bytes")
 
 
@@ -232,8 +233,72 @@ def loss_golden():
     np.savez_compressed(os.path.join(GOLDEN_DIR, "loss.npz"), **blob)
 
 
+REAL_DIR = "/root/reference/adobe5k_dpe/curl_example_test_input"
+REAL_CROP = (48, 64)      # rows, columns of the window whose reference outputs are stored
+
+
+def real_images():
+    """The nine 8-bit example photographs the reference ships (512 x 340/341 RGBA, alpha == 255), as
+    uint8 [H, W, 3] arrays in file-name order -- BASELINE.md section 4(i)'s substitute for config 1."""
+    from PIL import Image
+    out = []
+    for name in sorted(os.listdir(REAL_DIR)):
+        if not name.lower().endswith(".png"):
+            continue
+        a = np.array(Image.open(os.path.join(REAL_DIR, name)))
+        assert a.dtype == np.uint8 and a.ndim == 3 and a.shape[2] == 4 and (a[..., 3] == 255).all(), name
+        out.append((name, np.ascontiguousarray(a[..., :3])))
+    assert len(out) == 9
+    return out
+
+
+def real_golden():
+    """tests/golden/real.npz: the nine real photographs (whole, uint8) and, for one window of each, the
+    reference CURLLayer's forward + backward in fp32 and fp64 (x = u8 / 255 as TF.to_tensor does,
+    data.py:152-158; knots 0.1 * randn seed 1234; mask == 1 on even images, a random bool mask on odd
+    ones).  The whole images travel so that the GPU box can (a) run the CUDA path on real saturation /
+    smooth-region statistics against the oracle and (b) time the CPU arm on them one at a time."""
+    _, _, CURLLayer = ref_loader.load()
+    g = torch.Generator().manual_seed(1234)
+    blob = {"n": np.array(9), "crop": np.array(REAL_CROP)}
+    ch, cw = REAL_CROP
+    for i, (name, a) in enumerate(real_images()):
+        H, W, _ = a.shape
+        blob[f"{i}.name"] = np.array(name)
+        blob[f"{i}.u8"] = a
+        L, R, Hk = (0.1 * torch.randn(1, n, generator=g) for n in (48, 48, 64))
+        for k, t in zip("LRH", (L, R, Hk)):
+            blob[f"{i}.{k}"] = t.numpy()
+        # the window whose reference OUTPUT is closest to 30 % saturated (exact 0 / 1: the clamp ties of
+        # SURVEY.md 8a) -- a window that is all white or all black carries no gradient information
+        full = torch.from_numpy(a).permute(2, 0, 1)[None].float() / 255.0
+        with torch.no_grad():
+            o_full, _ = CURLLayer(48, 48, 64)(full.contiguous(), torch.ones(1, 1, H, W, dtype=torch.bool), L, R, Hk)
+        sat = ((o_full[0] == 0) | (o_full[0] == 1)).float().mean(0).numpy()
+        best, by, bx = 9.0, (H - ch) // 2, (W - cw) // 2
+        for y0 in range(0, H - ch + 1, ch // 2):
+            for x0 in range(0, W - cw + 1, cw // 2):
+                v = abs(float(sat[y0:y0 + ch, x0:x0 + cw].mean()) - 0.3)
+                if v < best:
+                    best, by, bx = v, y0, x0
+        blob[f"{i}.win"] = np.array([by, bx])
+        x = torch.from_numpy(a[by:by + ch, bx:bx + cw]).permute(2, 0, 1)[None].float() / 255.0   # TF.to_tensor
+        mask = torch.ones(1, 1, ch, cw, dtype=torch.bool) if i % 2 == 0 else torch.rand(1, 1, ch, cw, generator=g) > 0.1
+        case = dict(img=x.contiguous(), mask=mask, knots=(L, R, Hk), pts=(48, 48, 64),
+                    gout=torch.randn(1, 3, ch, cw, generator=g), greg=torch.ones(1))
+        blob[f"{i}.mask"] = mask.numpy()
+        blob[f"{i}.gout"] = case["gout"].numpy()
+        for tag, dtype in (("f32", torch.float32), ("f64", torch.float64)):
+            for k, t in run_layer(CURLLayer, case, dtype).items():
+                blob[f"{i}.{tag}.{k}"] = t.numpy()
+    np.savez_compressed(os.path.join(GOLDEN_DIR, "real.npz"), **blob)
+
+
 if __name__ == "__main__":
     if "--loss-only" in sys.argv:
         loss_golden()
+    elif "--real-only" in sys.argv:
+        real_golden()
+        print("real.npz", os.path.getsize(os.path.join(GOLDEN_DIR, "real.npz")), "bytes")
     else:
         main()
