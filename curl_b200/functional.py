@@ -49,8 +49,10 @@ def _knots(P, n, name, dev):
 
 
 def _mask(mask, img):
-    """Returns (mask_tensor_or_None, mask_kind).  bool/uint8 -> 1 byte per pixel; anything else is
-    converted to fp32 and multiplied in at every stage like the reference (model.py:154,160,166,170)."""
+    """Returns (mask_tensor_or_None, mask_kind).  torch.bool -> 1 byte per pixel (zero / non-zero); every
+    other dtype -- torch.uint8 included: the reference MULTIPLIES by the mask's value, so a 0/255 byte mask
+    scales by 255 there -- is converted to fp32 and multiplied in at every stage like the reference
+    (model.py:154,160,166,170)."""
     if mask is None:
         return None, _lib.MASK_NONE
     B, _, H, W = img.shape
@@ -66,7 +68,7 @@ def _mask(mask, img):
         raise ValueError("curl_b200: mask must have shape [B, 1, H, W], got %s" % (tuple(mask.shape),))
     if mask.shape[0] != B:
         mask = mask.expand(B, 1, H, W)
-    if mask.dtype in (torch.bool, torch.uint8):
+    if mask.dtype == torch.bool:
         return mask.contiguous(), _lib.MASK_U8
     return mask.to(torch.float32).contiguous(), _lib.MASK_F32
 
@@ -354,8 +356,10 @@ class TriSpaceFn(torch.autograd.Function):
                                            int(spatial), int(final_clamp), _ptr(out), _ptr(saved), B, h, w, _stream(dev))
         _lib.check(rc, "curl_trispace_fwd_f32")
         _lib.count_launch()
-        ctx.save_for_backward(img, *coefs)
-        ctx.sig = saved
+        # `saved` goes through save_for_backward like the inputs: autograd frees it with the graph, a second
+        # backward under retain_graph=True sees the same tensor, and saved-tensor hooks (checkpointing,
+        # CPU offload) and the in-place/version checks apply to it
+        ctx.save_for_backward(img, *coefs, saved)
         ctx.cfg = (degree, int(spatial), int(final_clamp))
         return out
 
@@ -366,7 +370,7 @@ class TriSpaceFn(torch.autograd.Function):
             raise RuntimeError("curl_b200: the TriSpace residual has no image gradient (the image is data on this "
                                "path, reference model.py:517-519); detach the image")
         lib = _lib.load()
-        img, R, L, H = ctx.saved_tensors
+        img, R, L, H, saved = ctx.saved_tensors
         degree, spatial, final_clamp = ctx.cfg
         dev = img.device
         B, _, h, w = img.shape
@@ -376,11 +380,10 @@ class TriSpaceFn(torch.autograd.Function):
         ws = torch.empty(n, dtype=torch.uint8, device=dev)
         with torch.cuda.device(dev):
             rc = lib.curl_trispace_bwd_f32(_ptr(img), _ptr(R), _ptr(L), _ptr(H), degree, spatial, final_clamp,
-                                           _ptr(gout), _ptr(ctx.sig), _ptr(gR), _ptr(gL), _ptr(gH), _ptr(ws), n, B, h, w,
+                                           _ptr(gout), _ptr(saved), _ptr(gR), _ptr(gL), _ptr(gH), _ptr(ws), n, B, h, w,
                                            _stream(dev))
         _lib.check(rc, "curl_trispace_bwd_f32")
         _lib.count_launch(2)
-        ctx.sig = None
         return None, gR, gL, gH, None, None, None, None
 
 

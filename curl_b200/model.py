@@ -142,6 +142,31 @@ class ChannelPolyLayer(nn.Module):
                                   "generate_residual (curl_trispace_fwd_f32); there is no stand-alone kernel")
 
 
+class Deg4MobilePolyLayer(nn.Module):
+    """Holder of the reference's Deg4MobilePolyLayer state (model.py:336-343): `num_coeffs` = 126 and the
+    frozen `powers` parameter of a degree-4, 5-variable polynomial, so that `infer.py:22-23` /
+    `coreml_conversion.py:19-20` -- `TriSpaceRegNet(polynomial_order=4, spatial=True, is_train=False,
+    polylayer=model.Deg4MobilePolyLayer())` -- construct unchanged and checkpoints written with either
+    polynomial layer load into the other (the reference keeps `powers` for exactly that reason).  In the
+    reference the class exists because Core ML cannot trace torch.pow; its products-written-out form and
+    ChannelPolyLayer's differ by ~1e-5 in fp32 (tests/test_oracle_pins.py).  Here both run the same fused
+    kernel (nested evaluation), which sits inside that spread of either."""
+
+    degree = 4
+    num_variables = 5
+    num_out = 3
+
+    def __init__(self):
+        super().__init__()
+        powers = list(ChannelPolyLayer.generate_powers(4, 5))
+        self.num_coeffs = len(powers)           # 126
+        self.powers = nn.Parameter(torch.tensor(powers, dtype=torch.float32), requires_grad=False)
+
+    def forward(self, img, coeffs):
+        raise NotImplementedError("curl_b200: Deg4MobilePolyLayer runs only fused inside TriSpaceRegNet."
+                                  "generate_residual (curl_trispace_fwd_f32); there is no stand-alone kernel")
+
+
 class TriSpaceRegNet(nn.Module):
     """The reference's TriSpaceRegNet (model.py:411-520) with its per-pixel part -- colour
     conversions, three polynomials, sigmoids, inverse conversions, residual sum, final clamp -- as one
@@ -165,6 +190,10 @@ class TriSpaceRegNet(nn.Module):
         self.polylayer = polylayer if polylayer is not None else ChannelPolyLayer(
             degree=self.order, num_variables=self.num_in, num_out=self.num_channels)
         self.num_coeffs = self.polylayer.num_coeffs
+        want = len(list(ChannelPolyLayer.generate_powers(self.order, self.num_in)))
+        if self.num_coeffs != want:
+            raise ValueError("TriSpaceRegNet: polylayer has %d coefficients, a degree-%d polynomial in %d variables "
+                             "(spatial=%s) has %d" % (self.num_coeffs, self.order, self.num_in, self.spatial, want))
         if backbone is None:
             try:
                 import timm
@@ -256,13 +285,22 @@ class CURLLoss(nn.Module):
         from .functional import loss_terms
         for m in (self.rgb2lab, self.rgb2hsv):
             m._check_constants()
-        sums, L_pred, L_target = loss_terms(predicted_img_batch, target_img_batch, mask)
         B, C, H, W = predicted_img_batch.shape
+        if isinstance(mask, torch.Tensor):
+            # model.py:90 divides by `mask.sum()` of the tensor as passed: a broadcast [1,1,H,W] mask would make
+            # the reference's terms B times larger than one mask row per image gives, so it is refused rather
+            # than silently expanded; [B,H,W] is what data.py's loader yields before its unsqueeze
+            if mask.dim() == 3:
+                mask = mask.unsqueeze(1)
+            if tuple(mask.shape) != (B, 1, H, W):
+                raise ValueError("curl_b200: CURLLoss needs a mask of shape [%d, 1, %d, %d] (one row per image), got %s"
+                                 % (B, H, W, tuple(mask.shape)))
+        sums, L_pred, L_target = loss_terms(predicted_img_batch, target_img_batch, mask)
         tot = sums.sum(dim=0)
         n_px = float(B * H * W)
         if mask is None:
             n_masked = 0.0
-        elif mask.dtype in (torch.bool, torch.uint8):
+        elif mask.dtype == torch.bool:
             n_masked = n_px - tot[4]
         else:
             n_masked = torch.logical_not(mask).expand(B, 1, H, W).sum()

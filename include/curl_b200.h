@@ -40,7 +40,8 @@ extern "C" {
 
 /* mask_kind: how `mask` is to be read (reference: data.py:190 gives bool, infer.py:41 gives float) */
 #define CURL_MASK_NONE 0 /* mask == NULL, treated as all ones                              */
-#define CURL_MASK_U8 1   /* 1 byte per pixel, zero / non-zero (torch.bool or torch.uint8)    */
+#define CURL_MASK_U8 1   /* 1 byte per pixel, zero / non-zero (torch.bool; the Python layer sends a  */
+                         /* torch.uint8 mask as F32 because the reference multiplies by its VALUE)  */
 #define CURL_MASK_F32 2  /* fp32 per pixel, arbitrary values, multiplied in at every stage   */
 
 /* colour conversions (reference colors.py) */

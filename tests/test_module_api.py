@@ -128,6 +128,16 @@ def test_trispace_api():
         flat.generate_residual(torch.rand(1, 3, 4, 4), *[torch.zeros(1, 3, 35)] * 3)
     x = torch.rand(1, 3, 4, 4)
     assert torch.equal(flat.generate_image(x, x), torch.clamp(x + x, 0, 1))
+    # infer.py:22-23 / coreml_conversion.py:19-20 build the net around model.Deg4MobilePolyLayer()
+    mob = curl_b200.model.Deg4MobilePolyLayer()
+    assert mob.num_coeffs == 126 and list(mob.state_dict()) == ["powers"]
+    assert torch.equal(mob.powers, net.polylayer.powers)
+    inf = curl_b200.model.TriSpaceRegNet(polynomial_order=4, spatial=True, is_train=False, polylayer=mob,
+                                         backbone=nn.Identity())
+    assert inf.polylayer is mob and inf.num_coeffs == 126
+    assert inf.load_state_dict(net.state_dict(), strict=True).missing_keys == []      # checkpoints are interchangeable
+    with pytest.raises(ValueError, match="coefficients"):
+        curl_b200.TriSpaceRegNet(spatial=False, polylayer=mob, backbone=nn.Identity())
 
 
 def test_curlloss_api():
@@ -156,4 +166,8 @@ def test_curlloss_api():
         ms(a[0], b[0])
     with pytest.raises(RuntimeError, match="CUDA"):
         crit(torch.rand(1, 3, 32, 32), torch.rand(1, 3, 32, 32), torch.ones(1, 1, 32, 32, dtype=torch.bool))
+    # a mask that is not one row per image is refused before anything runs (model.py:90 sums the mask as passed)
+    for bad in (torch.ones(1, 1, 32, 32, dtype=torch.bool), torch.ones(2, 3, 32, 32)):
+        with pytest.raises(ValueError, match="one row per image"):
+            crit(torch.rand(2, 3, 32, 32), torch.rand(2, 3, 32, 32), bad)
     assert torch.equal(crit.batch_L_ssim_convert(torch.arange(24.).reshape(1, 3, 2, 4)), torch.arange(8.).reshape(1, 1, 2, 4))
