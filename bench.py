@@ -13,9 +13,16 @@ Printed JSON (rank 0, one line):
   e2e       the same step driven from pinned HOST buffers through the public module API: per step the
             image + mask are copied host->device, forward+backward run, and the regulariser and knot
             gradients are read back device->host
-  roofline  the dominant kernel (fused backward, 37 algorithmic B/px) against the measured HBM peak
+  roofline  the dominant kernel (fused backward, 37 algorithmic B/px) against the measured HBM peak;
+            roofline_fwd / roofline_step / roofline_bwd_no_gimg (25 B/px: the GCURLNet case, img is data) beside it
+  fwd_only  forward-only (inference) legs at every N: resident-input rate, and host round trips with the
+            output copied back (fp32: 13 B/px up + 12 down; 8-bit: 4 up + 3 down)
+  e2e_u8    the training step fed from 8-bit host data (4 B/px up instead of 13), at every N
+  e2e.h2d_peak_gbs / frac_of_h2d_peak   a plain pinned host->device copy of the same chunks on all ranks at once
   gpu_eager_baseline  the same op sequence run eagerly by PyTorch on this GPU (the reference's own
             way of using a GPU), one 1080p tile
+  gpu_compile_baseline  the same op sequence under torch.compile (inductor) on this GPU, 1080p x 4
+            (dev/compile_baseline.py in a subprocess): the strongest "reference on B200" there is
   extras    non-headline measurements: BASELINE configs[1] (1080p x16 forward), configs[2] / configs[4]
             (GCURLNet optimiser step at 512x512x32, under DDP when N > 1), the 8-bit paths, TriSpace, CURLLoss
   cpu_baseline  the CPU oracle (the reference's ATen op sequence, restated; kind "port") on this
@@ -151,6 +158,62 @@ def time_cpu(steps, warmup, h=1080, w=1920):
                       "(bit-identical to the patched reference on CPU)" % (h, w, mpx, steps, dt)}, dt
 
 
+def time_cpu_real_images(reps=2):
+    """the reference's CPU path on the nine real photographs it ships (512 x 340/341,
+    8-bit; tests/golden/real.npz carries them to the GPU box), one image at a time, batch 1 -- forward under
+    no_grad (what infer.py would do with this layer) and forward + backward."""
+    import numpy as np
+    from oracle import curl_oracle as O
+    path = os.path.join(ROOT, "tests", "golden", "real.npz")
+    if not os.path.exists(path):
+        return {"unavailable": "tests/golden/real.npz missing"}
+    g = np.load(path)
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    items = []
+    gen = torch.Generator().manual_seed(4)
+    for i in range(int(g["n"])):
+        x = O.u8_to_unit(torch.from_numpy(np.ascontiguousarray(g["%d.u8" % i])).permute(2, 0, 1)[None]).contiguous()
+        L, R, Hk = (torch.from_numpy(g["%d.%s" % (i, k)]) for k in "LRH")
+        m = torch.ones(1, 1, x.shape[2], x.shape[3], dtype=torch.bool)
+        items.append((x, m, L, R, Hk, torch.randn(x.shape, generator=gen), torch.ones(1)))
+    mpx = sum(it[0].shape[2] * it[0].shape[3] for it in items) / 1e6
+    with torch.no_grad():
+        for it in items[:2]:
+            O.curl_layer(*it[:5])
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            for it in items:
+                O.curl_layer(*it[:5])
+        dt_f = (time.perf_counter() - t0) / reps
+    O.curl_layer_fwd_bwd(*items[0])
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        for it in items:
+            O.curl_layer_fwd_bwd(*it)
+    dt_fb = (time.perf_counter() - t0) / reps
+    return {"fwd_mpx_per_s": mpx / dt_f, "fwd_bwd_mpx_per_s": mpx / dt_fb, "cores": cores, "images": len(items),
+            "mpx_total": mpx, "fwd_ms_per_image": dt_f / len(items) * 1e3, "fwd_bwd_ms_per_image": dt_fb / len(items) * 1e3,
+            "what": "the 9 example photographs of the reference (adobe5k_dpe/curl_example_test_input, 512x340/341, "
+                    "u8/255), one at a time, batch 1, mask == 1, knots 0.1*randn seed 1234; oracle on the host cores"}
+
+
+def time_gpu_compile(timeout_s=420):
+    """dev/compile_baseline.py in a subprocess (a failed or hung compile must not take the bench line with it)."""
+    cmd = [sys.executable, os.path.join(ROOT, "dev", "compile_baseline.py"), "4", "1080", "1920"]
+    try:
+        proc = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=timeout_s, cwd=ROOT)
+    except subprocess.TimeoutExpired:
+        return {"unavailable": "timed out after %d s" % timeout_s}
+    for ln in reversed(proc.stdout.strip().splitlines()):
+        if ln.startswith("{"):
+            try:
+                return json.loads(ln)
+            except ValueError:
+                break
+    return {"unavailable": "rc %d: %s" % (proc.returncode, proc.stderr.strip()[-300:])}
+
+
 def time_gpu_eager(dev, steps=3, warmup=2, h=1080, w=1920):
     """The reference's own way of running this path on a GPU: the same ATen op sequence, eagerly, on
     the B200.  ~650 launches per forward and every intermediate kept for autograd
@@ -181,6 +244,7 @@ def run_reference(args):
     steps = max(1, min(args.steps, 5))
     warmup = max(1, min(args.warmup, 1))
     base, dt = time_cpu(steps, warmup)
+    base["real_images"] = time_cpu_real_images()
     line = {
         "impl": "reference", "metric": METRIC, "value": base["value"], "unit": UNIT, "n_gpus": args.gpus,
         "steps": steps, "warmup": warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
@@ -326,11 +390,59 @@ def run_ours(args):
     bwd_ms = statistics.mean(e[1].elapsed_time(e[2]) for e in ev)
     del out, reg
 
-    tt = torch.tensor([ms_total], device=dev, dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-    ms_step = tt.item() / args.steps
+    def max_ranks(x):
+        t = torch.tensor([x], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item()
+
+    ms_step = max_ranks(ms_total) / args.steps
     value = world * n_px / 1e6 / (ms_step / 1e3)
+
+    def timed_all(fn, reps, warm=2):
+        """ms per call of fn on every rank at once: barrier + sync on both sides, CUDA events, max over ranks."""
+        for _ in range(warm):
+            fn()
+        barrier()
+        a = torch.cuda.Event(enable_timing=True); b_ = torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(reps):
+            fn()
+        b_.record()
+        barrier()
+        return max_ranks(a.elapsed_time(b_)) / reps
+
+    # ---- forward only (inference; north_star states the multi-GPU target on batch-sharded inference) -------
+    launches_before_legs = _lib.launches
+
+    def fwd_only():
+        with torch.no_grad():
+            return layer(img, mask, L, R, Hk)
+    fwd_only_ms = timed_all(fwd_only, args.steps)
+    fwd_only_value = world * n_px / 1e6 / (fwd_only_ms / 1e3)
+
+    # ---- backward without the image gradient (the GCURLNet case: img is data; 25 B/px) ----------------------
+    img_data = img.detach()
+    ev2 = [[torch.cuda.Event(enable_timing=True) for _ in range(2)] for _ in range(args.steps)]
+
+    def step_no_gimg(k=None):
+        for t in (L, R, Hk):
+            t.grad = None
+        o, r = layer(img_data, mask, L, R, Hk)
+        if k is not None:
+            ev2[k][0].record()
+        torch.autograd.backward([o, r], [gout, greg])
+        if k is not None:
+            ev2[k][1].record()
+    for _ in range(2):
+        step_no_gimg()
+    barrier()
+    for k in range(args.steps):
+        step_no_gimg(k)
+    barrier()
+    bwd_nog_ms = max_ranks(statistics.mean(e[0].elapsed_time(e[1]) for e in ev2))
+    for t in (L, R, Hk):
+        t.grad = None
 
     # ---- e2e: pinned host buffers -> H2D -> fwd+bwd -> D2H of the step's results -------------------
     # The public module API is driven from HOST data the way the reference's training loop does
@@ -389,6 +501,98 @@ def run_ours(args):
     h2d = h_img.numel() * 4 + h_mask.numel()
     d2h = h_res.numel() * 4
 
+    # ---- what the host->device path can do: the same pinned chunks, plain copies, all ranks at once ---------
+    def h2d_probe():
+        with torch.cuda.stream(copy_stream):
+            for lo, hi in spans:
+                d_img[lo:hi].copy_(h_img[lo:hi], non_blocking=True)
+                d_mask[lo:hi].copy_(h_mask[lo:hi], non_blocking=True)
+        main_stream.wait_stream(copy_stream)
+    h2d_ms = timed_all(h2d_probe, 3, warm=1)
+    h2d_peak_gbs = h2d / (h2d_ms / 1e3) / 1e9                 # per rank, measured with every rank copying
+
+    # ---- forward-only host round trips (inference e2e), fp32 and 8-bit, at every N ---------------------------
+    out_stream = torch.cuda.Stream(device=dev)
+    h_out = torch.empty(img.shape, dtype=torch.float32, pin_memory=True)
+    d_out = torch.empty_like(d_img)
+
+    def infer_f32():
+        ready = []
+        copy_stream.wait_stream(main_stream)
+        with torch.cuda.stream(copy_stream):
+            for lo, hi in spans:
+                d_img[lo:hi].copy_(h_img[lo:hi], non_blocking=True)
+                d_mask[lo:hi].copy_(h_mask[lo:hi], non_blocking=True)
+                ev_c = torch.cuda.Event(); ev_c.record(copy_stream); ready.append(ev_c)
+        with torch.no_grad():
+            for (lo, hi), ev_c in zip(spans, ready):
+                main_stream.wait_event(ev_c)
+                o, _ = layer(d_img[lo:hi], d_mask[lo:hi], Ld[lo:hi], Rd[lo:hi], Hd[lo:hi])
+                d_out[lo:hi] = o
+                ev_k = torch.cuda.Event(); ev_k.record(main_stream)
+                out_stream.wait_event(ev_k)
+                with torch.cuda.stream(out_stream):
+                    h_out[lo:hi].copy_(d_out[lo:hi], non_blocking=True)
+        main_stream.wait_stream(out_stream)
+    infer_f32_ms = timed_all(infer_f32, 3, warm=1)
+    del h_out, d_out
+
+    d_img8 = torch.empty(img.shape, dtype=torch.uint8, device=dev)
+    d_out8 = torch.empty(img.shape, dtype=torch.uint8, device=dev)
+    h_img8 = torch.empty(img.shape, dtype=torch.uint8, pin_memory=True)
+    h_img8.copy_((img.detach() * 255).to(torch.uint8))
+    h_out8 = torch.empty(img.shape, dtype=torch.uint8, pin_memory=True)
+
+    def infer_u8():
+        ready = []
+        copy_stream.wait_stream(main_stream)
+        with torch.cuda.stream(copy_stream):
+            for lo, hi in spans:
+                d_img8[lo:hi].copy_(h_img8[lo:hi], non_blocking=True)
+                d_mask[lo:hi].copy_(h_mask[lo:hi], non_blocking=True)
+                ev_c = torch.cuda.Event(); ev_c.record(copy_stream); ready.append(ev_c)
+        with torch.no_grad():
+            for (lo, hi), ev_c in zip(spans, ready):
+                main_stream.wait_event(ev_c)
+                o8, _ = layer.forward_u8(d_img8[lo:hi], d_mask[lo:hi], Ld[lo:hi], Rd[lo:hi], Hd[lo:hi])
+                d_out8[lo:hi] = o8
+                ev_k = torch.cuda.Event(); ev_k.record(main_stream)
+                out_stream.wait_event(ev_k)
+                with torch.cuda.stream(out_stream):
+                    h_out8[lo:hi].copy_(d_out8[lo:hi], non_blocking=True)
+        main_stream.wait_stream(out_stream)
+    infer_u8_ms = timed_all(infer_u8, 3, warm=1)
+    with torch.no_grad():
+        fwd_u8_ms = timed_all(lambda: layer.forward_u8(d_img8, d_mask, Ld, Rd, Hd), 5, warm=2)
+    del d_out8, h_out8
+
+    # ---- the training step fed from 8-bit host data (what data.py holds before TF.to_tensor), at every N -----
+    from curl_b200.functional import to_tensor_u8
+
+    def u8_train_step():
+        ready = []
+        copy_stream.wait_stream(main_stream)
+        with torch.cuda.stream(copy_stream):
+            for lo, hi in spans:
+                d_img8[lo:hi].copy_(h_img8[lo:hi], non_blocking=True)
+                d_mask[lo:hi].copy_(h_mask[lo:hi], non_blocking=True)
+                ev_c = torch.cuda.Event()
+                ev_c.record(copy_stream)
+                ready.append(ev_c)
+        for (lo, hi), ev_c in zip(spans, ready):
+            main_stream.wait_event(ev_c)
+            x = to_tensor_u8(d_img8[lo:hi]).requires_grad_(True)
+            l, r, h = (t[lo:hi].clone().requires_grad_(True) for t in (Ld, Rd, Hd))
+            o, rg = layer(x, d_mask[lo:hi], l, r, h)
+            torch.autograd.backward([o, rg], [gout[lo:hi], greg[lo:hi]])
+            d_res[lo:hi, 0] = rg.detach()
+            d_res[lo:hi, 1:49] = l.grad; d_res[lo:hi, 49:97] = r.grad; d_res[lo:hi, 97:161] = h.grad
+        h_res.copy_(d_res, non_blocking=True)
+    e2e_u8_ms = timed_all(u8_train_step, 3, warm=1)
+    h2d_u8 = h_img8.numel() + h_mask.numel()
+    del d_img8, h_img8
+    launches_legs = _lib.launches - launches_before_legs
+
     # ---- extras (reported beside the headline, never part of it) -----------------------------------
     def timed(fn, reps=10):
         for _ in range(3):
@@ -411,56 +615,6 @@ def run_ours(args):
             extras["config1_fwd_1080p_b16"] = {"ms": ms, "mpx_per_s": 16 * 1080 * 1920 / 1e6 / (ms / 1e3),
                                                "gbs": 16 * 1080 * 1920 * FWD_BYTES_PER_PX / (ms / 1e3) / 1e9}
             del gi, gm, gl, gr, gh
-            # 8-bit inference (curl_layer_fwd_u8): 3 B/px in + 1 mask + 3 B/px out
-            i8 = (img.detach() * 255).to(torch.uint8)
-            ms = timed(lambda: layer.forward_u8(i8, mask, Ld, Rd, Hd), 5)
-            extras["fwd_u8_4k_b%d" % B] = {"ms": ms, "mpx_per_s": n_px / 1e6 / (ms / 1e3), "bytes_per_px": 7,
-                                           "gbs": n_px * 7 / (ms / 1e3) / 1e9}
-            h_i8 = torch.empty(i8.shape, dtype=torch.uint8, pin_memory=True); h_i8.copy_(i8)
-            h_o8 = torch.empty(i8.shape, dtype=torch.uint8, pin_memory=True)
-
-            def u8_e2e():
-                i8.copy_(h_i8, non_blocking=True); d_mask.copy_(h_mask, non_blocking=True)
-                o8, _ = layer.forward_u8(i8, d_mask, Ld, Rd, Hd)
-                h_o8.copy_(o8, non_blocking=True)
-            ms = timed(u8_e2e, 3)
-            extras["fwd_u8_4k_b%d" % B]["e2e_ms"] = ms
-            extras["fwd_u8_4k_b%d" % B]["e2e_mpx_per_s"] = n_px / 1e6 / (ms / 1e3)
-            extras["fwd_u8_4k_b%d" % B]["e2e_what"] = "pinned host u8 image + bool mask -> H2D -> kernel -> D2H u8 image (7 B/px over PCIe)"
-            del i8, h_i8, h_o8
-        # Training step fed from 8-bit host data (what data.py holds before TF.to_tensor): the host uploads the
-        # uint8 image (3 B/px) + mask, curl_u8_to_unit_f32 makes the fp32 tensor on the device, then the same
-        # forward + backward as the e2e leg above (image gradient included, results read back)
-        from curl_b200.functional import to_tensor_u8
-        h_img8 = torch.empty(img.shape, dtype=torch.uint8, pin_memory=True)
-        h_img8.copy_((img.detach() * 255).to(torch.uint8))
-        d_img8 = torch.empty(img.shape, dtype=torch.uint8, device=dev)
-
-        def u8_train_step():
-            ready = []
-            copy_stream.wait_stream(main_stream)
-            with torch.cuda.stream(copy_stream):
-                for lo, hi in spans:
-                    d_img8[lo:hi].copy_(h_img8[lo:hi], non_blocking=True)
-                    d_mask[lo:hi].copy_(h_mask[lo:hi], non_blocking=True)
-                    ev_c = torch.cuda.Event()
-                    ev_c.record(copy_stream)
-                    ready.append(ev_c)
-            for (lo, hi), ev_c in zip(spans, ready):
-                main_stream.wait_event(ev_c)
-                x = to_tensor_u8(d_img8[lo:hi]).requires_grad_(True)
-                l, r, h = (t[lo:hi].clone().requires_grad_(True) for t in (Ld, Rd, Hd))
-                o, rg = layer(x, d_mask[lo:hi], l, r, h)
-                torch.autograd.backward([o, rg], [gout[lo:hi], greg[lo:hi]])
-                d_res[lo:hi, 0] = rg.detach()
-                d_res[lo:hi, 1:49] = l.grad; d_res[lo:hi, 49:97] = r.grad; d_res[lo:hi, 97:161] = h.grad
-            h_res.copy_(d_res, non_blocking=True)
-        ms = timed(u8_train_step, 3)
-        extras["train_from_u8_4k_b%d" % B] = {
-            "e2e_ms": ms, "e2e_mpx_per_s": n_px / 1e6 / (ms / 1e3), "h2d_bytes_per_step": h_img8.numel() + h_mask.numel(),
-            "what": "pinned host uint8 image + bool mask -> H2D (4 B/px) -> curl_u8_to_unit_f32 -> CURLLayer fwd+bwd "
-                    "-> D2H reg + knot grads; the headline e2e leg uploads the same images as fp32 (13 B/px)"}
-        del h_img8, d_img8
         # TriSpace polynomial residual (TriSpaceRegNet's per-pixel path), spatial=True (126 coefficients),
         # BASELINE configs[2]'s shape: 512 x 512, batch 32; forward incl. generate_image, and backward
         import torch.nn as nn
@@ -544,17 +698,48 @@ def run_ours(args):
                        "parallelism": "batch-sharded, no collective" if world > 1 else "single GPU"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": e2e_ms, "steps": e2e_steps, "chunk_images": chunk,
+                    "h2d_gbs_achieved": h2d / (e2e_ms / 1e3) / 1e9, "h2d_peak_gbs": h2d_peak_gbs,
+                    "frac_of_h2d_peak": (h2d / (e2e_ms / 1e3) / 1e9) / h2d_peak_gbs,
+                    "h2d_peak_what": "the same pinned chunks copied host->device with nothing else running, on all %d "
+                                     "rank(s) at once; GB/s per rank, slowest rank" % world,
                     "what": "pinned host img+mask -> H2D (copy stream, chunked) -> CURLLayer fwd+bwd -> D2H reg + knot grads"},
+            "e2e_u8": {"value": world * n_px / 1e6 / (e2e_u8_ms / 1e3), "unit": UNIT, "ms_per_step": e2e_u8_ms,
+                       "h2d_bytes_per_step": h2d_u8, "d2h_bytes_per_step": d2h,
+                       "h2d_gbs_achieved": h2d_u8 / (e2e_u8_ms / 1e3) / 1e9,
+                       "what": "the same training step fed from 8-bit host data: pinned uint8 image + bool mask -> H2D "
+                               "(4 B/px instead of 13) -> curl_u8_to_unit_f32 (device-side TF.to_tensor, exact) -> "
+                               "CURLLayer fwd+bwd with image gradient -> D2H reg + knot grads"},
+            "fwd_only": {"value": fwd_only_value, "unit": UNIT, "ms_per_step": fwd_only_ms,
+                         "achieved_gbs_per_gpu": n_px * FWD_BYTES_PER_PX / (fwd_only_ms / 1e3) / 1e9,
+                         "frac": n_px * FWD_BYTES_PER_PX / (fwd_only_ms / 1e3) / 1e9 / peak,
+                         "u8_kernel_ms": fwd_u8_ms, "u8_kernel_value": world * n_px / 1e6 / (fwd_u8_ms / 1e3),
+                         "e2e_f32": {"value": world * n_px / 1e6 / (infer_f32_ms / 1e3), "ms_per_step": infer_f32_ms,
+                                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": n_px * 12,
+                                     "what": "pinned host fp32 img + mask -> H2D -> forward -> fp32 output copied back "
+                                             "(three streams, chunked)"},
+                         "e2e_u8": {"value": world * n_px / 1e6 / (infer_u8_ms / 1e3), "ms_per_step": infer_u8_ms,
+                                    "h2d_bytes_per_step": h2d_u8, "d2h_bytes_per_step": n_px * 3,
+                                    "what": "pinned host uint8 img + mask -> H2D -> curl_layer_fwd_u8 -> uint8 output "
+                                            "copied back (7 B/px over PCIe)"},
+                         "what": "forward only (inference), whole batch per launch, resident inputs; max over ranks"},
             "gpu_launches": launches,
+            "gpu_launches_other_legs": launches_legs,
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": "bwd_tma_kernel<OpLayer> (fused recompute backward, 37 B/px)",
                          "achieved": bwd_gbs, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
                          "frac": bwd_gbs / peak, "frac_of_8TBps": bwd_gbs / 8000.0, "traffic": traffic,
-                         "traffic_unit": "GB per launch (ncu dram read+write, profiles/traffic.json)",
+                         "traffic_unit": "GB per launch",
+                         "traffic_source": "NOT measured in this run: the committed ncu constant of profiles/traffic.json "
+                                           "(dram read+write bytes per pixel of one --set full capture) x pixels per launch",
                          "algorithmic_gb_per_launch": n_px * BWD_BYTES_PER_PX / 1e9,
                          "ms_per_launch": bwd_ms},
             "roofline_fwd": {"kernel": "fwd_kernel<OpLayer> (fused forward, 25 B/px)", "achieved": fwd_gbs,
                              "frac": fwd_gbs / peak, "ms_per_launch": fwd_ms},
+            "roofline_bwd_no_gimg": {"kernel": "bwd_tma_kernel<OpLayer, .., false> (no image gradient: the GCURLNet "
+                                               "case, 25 B/px)",
+                                     "achieved": n_px * FWD_BYTES_PER_PX / (bwd_nog_ms / 1e3) / 1e9,
+                                     "frac": n_px * FWD_BYTES_PER_PX / (bwd_nog_ms / 1e3) / 1e9 / peak,
+                                     "ms_per_launch": bwd_nog_ms},
             "roofline_step": {"bytes_per_px": FWD_BYTES_PER_PX + BWD_BYTES_PER_PX, "achieved": step_gbs,
                               "frac": step_gbs / peak, "frac_of_8TBps": step_gbs / 8000.0},
         }
@@ -562,6 +747,7 @@ def run_ours(args):
             line["extras"] = extras
         if world == 1 and not args.no_cpu:
             base, _ = time_cpu(3, 1)
+            base["real_images"] = time_cpu_real_images()
             line["cpu_baseline"] = base
             try:
                 del img, gout, h_img, d_img
@@ -570,6 +756,9 @@ def run_ours(args):
                 line["gpu_eager_baseline"] = time_gpu_eager(dev)
             except Exception as e:   # reported baseline only: never fail the bench line for it
                 line["gpu_eager_baseline"] = {"unavailable": "%s: %s" % (type(e).__name__, str(e)[:200])}
+            if not args.no_compile:
+                torch.cuda.empty_cache()
+                line["gpu_compile_baseline"] = time_gpu_compile()
         print(json.dumps(line))
     if world > 1:
         dist.barrier()
@@ -587,6 +776,7 @@ def main():
     ap.add_argument("--width", type=int, default=W4K)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline and gpu_eager_baseline legs")
     ap.add_argument("--no-extras", action="store_true", help="skip the extra (non-headline) measurements")
+    ap.add_argument("--no-compile", action="store_true", help="skip the torch.compile baseline (a subprocess, ~1-2 min)")
     ap.add_argument("--e2e-chunk", type=int, default=8, help="images per host->device chunk in the e2e leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

@@ -10,13 +10,13 @@ namespace host {
 
 constexpr int MAX_DEVICES = 64;
 
-inline int current_device() {
+static inline int current_device() {
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= MAX_DEVICES) return -1;
   return dev;
 }
 
-inline int sm_count() {
+static inline int sm_count() {
   static int cached[MAX_DEVICES] = {0};
   const int dev = current_device();
   if (dev < 0) return 148;
@@ -32,7 +32,7 @@ inline int sm_count() {
 // static (a function-pointer *type* would be shared by all kernels of one signature).  `bytes` may grow
 // between calls of the same kernel (segment-clamp histograms), so the largest value set so far is kept.
 template <auto kernel>
-inline bool ensure_dyn_smem(size_t bytes) {
+static inline bool ensure_dyn_smem(size_t bytes) {
   static size_t set_to[MAX_DEVICES] = {0};
   const int dev = current_device();
   if (dev < 0) return false;

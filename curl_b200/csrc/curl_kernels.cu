@@ -66,8 +66,11 @@ struct KParams {
 // Ops.  T is the lane type: F2 (two pixels per value, packed FFMA2/FMUL2/FADD2) on the aligned
 // path, float on the unaligned tail path.
 // ---------------------------------------------------------------------------------------------
+// FOLD: the op's reverse sweep works in the scaled units of curl_pixel.cuh ("Units of the fused layer's reverse
+// sweep"): the moments are rescaled after the reduction (curve_fold_m) and s_ab[2 NC] holds layer_beta1.
 struct OpLayer {
   static constexpr int NC = LAYER_CURVES;
+  static constexpr bool FOLD = true;
   template <int MK, class T>
   static __device__ __forceinline__ void fwd(const T x[3], T m, const float* ab, int, T y[3]) {
     layer_fwd<T, MK>(x, m, ab, y);
@@ -85,6 +88,7 @@ struct OpLayer {
 template <int CONV>
 struct OpColor {
   static constexpr int NC = 0;
+  static constexpr bool FOLD = false;
   template <int MK, class T>
   static __device__ __forceinline__ void fwd(const T x[3], T, const float*, int, T y[3]) {
     if (CONV == CURL_RGB2LAB) rgb2lab_fwd<T, false>(x, y, nullptr);
@@ -105,6 +109,7 @@ struct OpColor {
 
 struct OpAdjustSelf3 {  // adjust_lab, adjust_rgb
   static constexpr int NC = 3;
+  static constexpr bool FOLD = false;
   template <int MK, class T>
   static __device__ __forceinline__ void fwd(const T x[3], T, const float* ab, int, T y[3]) {
     adjust_self3_fwd<T, false>(x, ab, y, nullptr);
@@ -121,6 +126,7 @@ struct OpAdjustSelf3 {  // adjust_lab, adjust_rgb
 
 struct OpAdjustHsv {
   static constexpr int NC = 4;
+  static constexpr bool FOLD = false;
   template <int MK, class T>
   static __device__ __forceinline__ void fwd(const T x[3], T, const float* ab, int, T y[3]) {
     adjust_hsv_fwd<T, false, false>(x, ab, y, nullptr);
@@ -131,12 +137,13 @@ struct OpAdjustHsv {
                                              const SP&) {
     T y[3]; HsvCurveJac<T> j;
     adjust_hsv_fwd<T, true, false>(x, ab, y, &j);
-    adjust_hsv_bwd(j, ab, gy, gx, mom);
+    adjust_hsv_bwd(j, ab[3], gy, gx, mom);
   }
 };
 
 struct OpCurve1 {  // curves.apply_curve: one curve channel_in -> channel_out, knots given as C
   static constexpr int NC = 1;
+  static constexpr bool FOLD = false;
   template <int MK, class T>
   static __device__ __forceinline__ void fwd(const T x[3], T, const float* ab, int aux, T y[3]) {
     single_curve_fwd<T>(x, aux & 3, (aux >> 2) & 3, ab[0], ab[1], y);
@@ -214,9 +221,11 @@ __device__ __forceinline__ Group<VEC> load_mask(const void* mask, size_t idx) {
 // Block prologue: exp() the knots of image b into shared memory, derive (alpha, beta) per curve
 // (and, for the block that owns it, the regulariser).  curves.py:19-24,53-54,105-106,152-153.
 // ---------------------------------------------------------------------------------------------
-template <int NC>
+// BWD (backward kernels of a FOLD op): s_ab[2 NC] = layer_beta1(beta of the hue -> sat curve, curve 7).
+template <class Op, bool BWD>
 __device__ __forceinline__ void stage_curves(const KParams& p, int b, float* s_C, float* s_ab, double* s_reg,
                                              bool want_reg) {
+  constexpr int NC = Op::NC;
   int off = 0;
   for (int s = 0; s < p.nseg; ++s) {
     const int n = p.seg[s].nc * p.seg[s].K;
@@ -235,6 +244,7 @@ __device__ __forceinline__ void stage_curves(const KParams& p, int b, float* s_C
       o += p.seg[s].nc * K;
     }
     curve_alpha_beta(s_C + o, K, &s_ab[2 * threadIdx.x], &s_ab[2 * threadIdx.x + 1]);
+    if (BWD && Op::FOLD && threadIdx.x == 7) s_ab[2 * NC] = layer_beta1(s_ab[2 * 7 + 1]);
     if (want_reg) s_reg[threadIdx.x] = curve_regulariser(s_C + o, K);
   }
   __syncthreads();
@@ -257,7 +267,7 @@ __global__ void FWD_BOUNDS fwd_kernel(const KParams p) {
   const int b = blockIdx.y;
   if (NC > 0) {
     const bool owner = (blockIdx.x == 0) && (p.reg != nullptr);
-    stage_curves<NC>(p, b, s_C, s_ab, s_reg, owner);
+    stage_curves<Op, false>(p, b, s_C, s_ab, s_reg, owner);
     if (owner && threadIdx.x == 0) {
       double r = 0.0;
       for (int j = 0; j < NC; ++j) r += s_reg[j];
@@ -306,7 +316,7 @@ __global__ void __launch_bounds__(THREADS) fwd_u8_kernel(const KParams p) {
   const int b = blockIdx.y;
   {
     const bool owner = (blockIdx.x == 0) && (p.reg != nullptr);
-    stage_curves<NC>(p, b, s_C, s_ab, s_reg, owner);
+    stage_curves<OpLayer, false>(p, b, s_C, s_ab, s_reg, owner);
     if (owner && threadIdx.x == 0) {
       double r = 0.0;
       for (int j = 0; j < NC; ++j) r += s_reg[j];
@@ -377,9 +387,10 @@ __global__ void __launch_bounds__(THREADS) fwd_u8_kernel(const KParams p) {
 // image folds all partial rows in a fixed order (in double, bitwise deterministic) and expands the
 // 2 moments per curve into the knot gradients (curve_knot_grad).
 // ---------------------------------------------------------------------------------------------
-template <int NC, class T, int NT>
+template <class Op, class T, int NT>
 __device__ __forceinline__ void finish_knot_grads(const KParams& p, int b, const T* mom, const float* s_C,
                                                   double* s_mom, float* s_part, unsigned* s_ticket_p) {
+  constexpr int NC = Op::NC;
   constexpr int NM = 2 * NC;
   constexpr int NWARPS = NT / 32;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -411,7 +422,7 @@ __device__ __forceinline__ void finish_knot_grads(const KParams& p, int b, const
     for (unsigned r = lane; r < gridDim.x; r += 32) acc += (double)__ldcg(rows + (size_t)r * NM + k);
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-    if (lane == 0) s_mom[k] = acc;
+    if (lane == 0) s_mom[k] = acc * curve_fold_m(Op::FOLD, k >> 1);   // back from the folded units of the reverse sweep
   }
   __syncthreads();
   const double greg = p.greg ? (double)p.greg[b] : 0.0;
@@ -440,12 +451,12 @@ __global__ void __launch_bounds__(THREADS) bwd_kernel(const KParams p) {
   constexpr int NM = 2 * NC;
   constexpr int NWARPS = THREADS / 32;
   __shared__ float s_C[NC > 0 ? CURL_MAX_KNOTS : 1];
-  __shared__ float s_ab[NC > 0 ? 2 * NC : 1];
+  __shared__ float s_ab[NC > 0 ? 2 * NC + 1 : 1];
   __shared__ double s_mom[NC > 0 ? NM : 1];
   __shared__ float s_part[NC > 0 ? NWARPS * NM : 1];
   __shared__ unsigned s_ticket;
   const int b = blockIdx.y;
-  if (NC > 0) stage_curves<NC>(p, b, s_C, s_ab, nullptr, false);
+  if (NC > 0) stage_curves<Op, true>(p, b, s_C, s_ab, nullptr, false);
 
   using G = Group<VEC>;
   using T = typename G::T;
@@ -461,7 +472,9 @@ __global__ void __launch_bounds__(THREADS) bwd_kernel(const KParams p) {
   for (int i = (blockIdx.x * THREADS + threadIdx.x) * VEC; i < HW; i += stride) {
     const G c0 = G::ld(in + i), c1 = G::ld(in + HW + i), c2 = G::ld(in + 2 * (size_t)HW + i);
     const G g0 = G::ld(go + i), g1 = G::ld(go + HW + i), g2 = G::ld(go + 2 * (size_t)HW + i);
-    const G m = load_mask<MK, VEC>(p.mask, (size_t)b * HW + i);
+    G m = load_mask<MK, VEC>(p.mask, (size_t)b * HW + i);
+    if constexpr (MK == MASK_U8 && VEC == 1) m.v[0] = bwd_mask_lane_u8(m.v[0] != 0.0f);   // gate offset (layer_bwd)
+    static_assert(MK != MASK_U8 || VEC == 1, "the vector backward with a byte mask is bwd_tma_kernel");
     G o0, o1, o2;
 #pragma unroll
     for (int v = 0; v < G::LANES; ++v) {
@@ -474,7 +487,7 @@ __global__ void __launch_bounds__(THREADS) bwd_kernel(const KParams p) {
     if (WANT_GIN) { o0.st(gin + i); o1.st(gin + HW + i); o2.st(gin + 2 * (size_t)HW + i); }
   }
 
-  if (NC > 0) finish_knot_grads<NC, T, THREADS>(p, b, mom, s_C, s_mom, s_part, &s_ticket);
+  if (NC > 0) finish_knot_grads<Op, T, THREADS>(p, b, mom, s_C, s_mom, s_part, &s_ticket);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -522,8 +535,13 @@ constexpr int TMA_TILE = TMA_SUB * BWD_PAIRS;   // pixels per stage: BWD_PAIRS s
 constexpr int TMA_STAGES = TMA_STAGES_N;
 constexpr int TMA_PLANES = 6;           // x0 x1 x2 g0 g1 g2
 constexpr size_t TMA_RING_BYTES = (size_t)TMA_STAGES * TMA_PLANES * TMA_TILE * sizeof(float);
+#ifdef CURL_PARK_TMEM
+constexpr bool PARK_IN_TMEM = true;
+#else
+constexpr bool PARK_IN_TMEM = false;
+#endif
 template <class Op> constexpr size_t tma_smem_bytes() {
-  return TMA_RING_BYTES + (size_t)Op::SPILL * BWD_THREADS * sizeof(F2);
+  return TMA_RING_BYTES + (PARK_IN_TMEM ? 0 : (size_t)Op::SPILL * BWD_THREADS * sizeof(F2));
 }
 
 // Shared-memory parking space for Jac records (curl_pixel.cuh "Spill policies"): slot-pair-major, one
@@ -545,7 +563,74 @@ struct SmemSpill {
     asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(x), "=f"(y), "=f"(z), "=f"(w) : "r"(base + (slot >> 1) * (BWD_THREADS * 16)) : "memory");
     a = F2(x, y); b = F2(z, w);
   }
+  __device__ __forceinline__ void before_loads() const {}     // a thread's own STS -> LDS are ordered
+  template <class... A> __device__ __forceinline__ void put8(int, A...) const {}      // (tensor-memory parking only)
+  template <class... A> __device__ __forceinline__ void get8(int, A&...) const {}
+  __device__ __forceinline__ void put6(int o, F2 a, F2 b, F2 c, F2 d, F2 e, F2 f) const {
+    put2(o, a, b); put2(o + 2, c, d); put2(o + 4, e, f);
+  }
+  __device__ __forceinline__ void get6(int o, F2& a, F2& b, F2& c, F2& d, F2& e, F2& f) const {
+    get2(o, a, b); get2(o + 2, c, d); get2(o + 4, e, f);
+  }
 };
+
+// The same parking space in TENSOR MEMORY (-DCURL_PARK_TMEM): each thread owns one TMEM lane (shape 32x32b: lane
+// i of a warp addresses TMEM lane 32 (warp % 4) + i) and parks a record of six packed values = 12 consecutive
+// 32-bit columns with tcgen05.st (x8 + x4), fetching it with tcgen05.ld + tcgen05.wait::ld.  No shared memory, no
+// LSU instructions, no bank conflicts; the block allocates TMEM_COLS columns for its lifetime.
+#ifdef CURL_PARK_J5
+constexpr int TMEM_COLS = 128;      // 24 + 14 slots of two columns, a power of two >= 32
+#else
+constexpr int TMEM_COLS = 64;       // >= 2 * Op::SPILL (48), a power of two >= 32
+#endif
+struct TmemSpill {
+  static constexpr bool kActive = true;
+  unsigned base;   // TMEM address: this warp's lane quarter in bits 31..16, the block's first column in bits 15..0
+  // tcgen05.st is asynchronous: the stores of this pixel pair must have completed before they are read back
+  __device__ __forceinline__ void before_loads() const { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+  __device__ __forceinline__ void put6(int o, F2 a, F2 b, F2 c, F2 d, F2 e, F2 f) const {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};\n"
+        "tcgen05.st.sync.aligned.32x32b.x4.b32 [%0 + 8], {%9, %10, %11, %12};" ::"r"(base + 2 * o),
+        "f"(a.lo()), "f"(a.hi()), "f"(b.lo()), "f"(b.hi()), "f"(c.lo()), "f"(c.hi()), "f"(d.lo()), "f"(d.hi()),
+        "f"(e.lo()), "f"(e.hi()), "f"(f.lo()), "f"(f.hi()) : "memory");
+  }
+  __device__ __forceinline__ void put8(int o, F2 a, F2 b, F2 c, F2 d, F2 e, F2 f, F2 g, F2 h) const {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+        ::"r"(base + 2 * o), "f"(a.lo()), "f"(a.hi()), "f"(b.lo()), "f"(b.hi()), "f"(c.lo()), "f"(c.hi()), "f"(d.lo()), "f"(d.hi()),
+        "f"(e.lo()), "f"(e.hi()), "f"(f.lo()), "f"(f.hi()), "f"(g.lo()), "f"(g.hi()), "f"(h.lo()), "f"(h.hi()) : "memory");
+  }
+  __device__ __forceinline__ void get8(int o, F2& a, F2& b, F2& c, F2& d, F2& e, F2& f, F2& g, F2& h) const {
+    float v[16];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];\n"
+        "tcgen05.wait::ld.sync.aligned;"
+        : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7]), "=f"(v[8]),
+          "=f"(v[9]), "=f"(v[10]), "=f"(v[11]), "=f"(v[12]), "=f"(v[13]), "=f"(v[14]), "=f"(v[15])
+        : "r"(base + 2 * o) : "memory");
+    a = F2(v[0], v[1]); b = F2(v[2], v[3]); c = F2(v[4], v[5]); d = F2(v[6], v[7]);
+    e = F2(v[8], v[9]); f = F2(v[10], v[11]); g = F2(v[12], v[13]); h = F2(v[14], v[15]);
+  }
+  __device__ __forceinline__ void get6(int o, F2& a, F2& b, F2& c, F2& d, F2& e, F2& f) const {
+    float v[12];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%12];\n"
+        "tcgen05.ld.sync.aligned.32x32b.x4.b32 {%8, %9, %10, %11}, [%12 + 8];\n"
+        "tcgen05.wait::ld.sync.aligned;"
+        : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7]), "=f"(v[8]),
+          "=f"(v[9]), "=f"(v[10]), "=f"(v[11])
+        : "r"(base + 2 * o) : "memory");
+    a = F2(v[0], v[1]); b = F2(v[2], v[3]); c = F2(v[4], v[5]); d = F2(v[6], v[7]); e = F2(v[8], v[9]); f = F2(v[10], v[11]);
+  }
+};
+__device__ __forceinline__ void tmem_alloc(unsigned* smem_slot, unsigned cols) {   // one whole warp
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_slot)), "r"(cols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(unsigned taddr, unsigned cols) {      // the same warp
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
 
 // Backward, aligned path (HW % 4 == 0, 16-byte aligned bases).  Same math as bwd_kernel<.., 2, ..>.
 template <class Op, int MK, bool WANT_GIN>
@@ -556,10 +641,14 @@ __global__ void __launch_bounds__(BWD_THREADS, BWD_MIN_BLOCKS) bwd_tma_kernel(co
   extern __shared__ __align__(128) float s_ring[];   // [STAGES][PLANES][TILE]
   __shared__ __align__(8) unsigned long long s_full[TMA_STAGES];
   __shared__ float s_C[NC > 0 ? CURL_MAX_KNOTS : 1];
-  __shared__ float s_ab[NC > 0 ? 2 * NC : 1];
+  __shared__ float s_ab[NC > 0 ? 2 * NC + 1 : 1];
   __shared__ double s_mom[NC > 0 ? NM : 1];
   __shared__ float s_part[NC > 0 ? NWARPS * NM : 1];
   __shared__ unsigned s_ticket;
+  __shared__ unsigned s_tmem;
+  constexpr bool USE_TMEM = PARK_IN_TMEM && Op::SPILL > 0;
+  static_assert(!USE_TMEM || (2 * Op::SPILL <= TMEM_COLS && BWD_THREADS == 128), "TMEM parking: 4 warps, 2 columns per slot");
+  static_assert(!PARK_J5 || PARK_IN_TMEM, "-DCURL_PARK_J5 needs -DCURL_PARK_TMEM");
   const int b = blockIdx.y;
   const int HW = p.HW;
   const float* in = p.in + (size_t)b * 3 * HW;
@@ -592,10 +681,19 @@ __global__ void __launch_bounds__(BWD_THREADS, BWD_MIN_BLOCKS) bwd_tma_kernel(co
   for (int i = threadIdx.x; i < (int)(TMA_RING_BYTES / sizeof(float4)); i += BWD_THREADS)
     reinterpret_cast<float4*>(s_ring)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  if constexpr (USE_TMEM) {
+    if (threadIdx.x < 32) tmem_alloc(&s_tmem, TMEM_COLS);
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  }
   __syncthreads();
+  unsigned tmem_base = 0;
+  if constexpr (USE_TMEM) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    tmem_base = s_tmem + (((threadIdx.x >> 5) & 3u) << 21);     // lane quarter of this warp: 32 (warp % 4) << 16
+  }
   if (threadIdx.x == 0)
     for (int it = 0; it < TMA_STAGES && it < n_my; ++it) issue(it);
-  if (NC > 0) stage_curves<NC>(p, b, s_C, s_ab, nullptr, false);
+  if (NC > 0) stage_curves<Op, true>(p, b, s_C, s_ab, nullptr, false);
 
   using T = F2;
 #ifdef BWD_SCALAR_MOM
@@ -645,7 +743,11 @@ __global__ void __launch_bounds__(BWD_THREADS, BWD_MIN_BLOCKS) bwd_tma_kernel(co
     mbar_wait(&s_full[s], parity);
     const float* stage = s_ring + (size_t)s * TMA_PLANES * TMA_TILE + threadIdx.x * 2;
     if (++s == TMA_STAGES) { s = 0; parity ^= 1u; }
+#ifdef BWD_UNROLL_Q
+#pragma unroll
+#else
 #pragma unroll 1
+#endif
     for (int q = 0; q < BWD_PAIRS; ++q) {
       const int px = px_tile + q * TMA_SUB;
       const bool valid = px < HW;     // HW is even: a pair is either fully inside or fully outside
@@ -653,9 +755,9 @@ __global__ void __launch_bounds__(BWD_THREADS, BWD_MIN_BLOCKS) bwd_tma_kernel(co
       // next sub-tile of this tile, or the first of the block's next tile (past the image once the block is done)
       m_next = mask_raw(q + 1 < BWD_PAIRS ? px + TMA_SUB : px_tile + tile_stride);
       T m = T(1.0f);
-      if (MK == MASK_U8) {
+      if (MK == MASK_U8) {     // the backward takes a {0,1} mask as a gate offset: 0 keeps, NaN masks (bwd_mask_lane_u8)
         const unsigned u = __float_as_uint(m_raw.x);
-        m = F2((u & 0xffu) ? 1.0f : 0.0f, (u & 0xff00u) ? 1.0f : 0.0f);
+        m = F2(bwd_mask_lane_u8((u & 0xffu) != 0), bwd_mask_lane_u8((u & 0xff00u) != 0));
       } else if (MK == MASK_F32) {
         m = F2(m_raw.x, m_raw.y);
       }
@@ -669,7 +771,7 @@ __global__ void __launch_bounds__(BWD_THREADS, BWD_MIN_BLOCKS) bwd_tma_kernel(co
         // a tail pair's gradient is switched off through m (= 0) where a mask multiplies it anyway
         gy[c] = (MK == MASK_NONE && !valid) ? F2(0.0f) : F2(g.x, g.y);
       }
-      if (!valid) m = T(0.0f);
+      if (!valid) m = (MK == MASK_U8) ? T(bwd_mask_lane_u8(false)) : T(0.0f);
       T gx[3];
 #ifdef BWD_SCALAR_MOM
       T momi[NM > 0 ? NM : 1];
@@ -678,7 +780,10 @@ __global__ void __launch_bounds__(BWD_THREADS, BWD_MIN_BLOCKS) bwd_tma_kernel(co
 #else
       T* const momi = mom;
 #endif
-      if constexpr (Op::SPILL > 0) {
+      if constexpr (USE_TMEM) {
+        const TmemSpill sp{tmem_base};
+        Op::template bwd<MK, WANT_GIN, T>(x, m, s_ab, p.aux, gy, gx, momi, sp);
+      } else if constexpr (Op::SPILL > 0) {
         const SmemSpill sp{smem_u32(reinterpret_cast<unsigned char*>(s_ring) + TMA_RING_BYTES) + threadIdx.x * 16u};
         Op::template bwd<MK, WANT_GIN, T>(x, m, s_ab, p.aux, gy, gx, momi, sp);
       } else {
@@ -695,10 +800,15 @@ __global__ void __launch_bounds__(BWD_THREADS, BWD_MIN_BLOCKS) bwd_tma_kernel(co
       }
     }   // sub-tiles
   }
+  if constexpr (USE_TMEM) {
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (threadIdx.x < 32) tmem_dealloc(s_tmem, TMEM_COLS);
+  }
 #ifdef BWD_SCALAR_MOM
-  if (NC > 0) finish_knot_grads<NC, float, BWD_THREADS>(p, b, mom, s_C, s_mom, s_part, &s_ticket);
+  if (NC > 0) finish_knot_grads<Op, float, BWD_THREADS>(p, b, mom, s_C, s_mom, s_part, &s_ticket);
 #else
-  if (NC > 0) finish_knot_grads<NC, T, BWD_THREADS>(p, b, mom, s_C, s_mom, s_part, &s_ticket);
+  if (NC > 0) finish_knot_grads<Op, T, BWD_THREADS>(p, b, mom, s_C, s_mom, s_part, &s_ticket);
 #endif
 }
 

@@ -168,17 +168,26 @@ CURL_HD void rgb2lab_fwd(const T x[3], T lab[3], LabJac<T>* jac) {
   lab[2] = vfma(vsub(f[1], f[2]), T(k::BN_S), T(0.5f));      // colors.py:50,59
 }
 
-template <class T>
+// FOLD (the fused layer only, see "Units of the fused layer's reverse sweep"): glab arrives as
+// (g_L LN_S3, g_a AN_S3, -g_b BN_S3); the sign of the third is absorbed by the MB?2 column.
+template <class T, bool FOLD = false>
 CURL_HD void rgb2lab_bwd(const LabJac<T>& jac, const T glab[3], T gx[3]) {
   // constants carry the 1/3 of d_f and the SRGB_DK of d_lin; the sign of d f_z is in the MB?2 column
-  const T ga = vmul(glab[1], T(k::AN_S3)), gb = vmul(glab[2], T(k::BN_S3));
   T gt[3];
-  gt[0] = vmul(ga, jac.d_f[0]);
-  gt[1] = vmul(vsub(vfma(glab[0], T(k::LN_S3), gb), ga), jac.d_f[1]);
-  gt[2] = vmul(gb, jac.d_f[2]);
-  gx[0] = vmul(vfma(gt[2], T(-k::MB02), vfma(gt[1], T(k::MB01), vmul(gt[0], T(k::MB00)))), jac.d_lin[0]);
-  gx[1] = vmul(vfma(gt[2], T(-k::MB12), vfma(gt[1], T(k::MB11), vmul(gt[0], T(k::MB10)))), jac.d_lin[1]);
-  gx[2] = vmul(vfma(gt[2], T(-k::MB22), vfma(gt[1], T(k::MB21), vmul(gt[0], T(k::MB20)))), jac.d_lin[2]);
+  if (FOLD) {
+    gt[0] = vmul(glab[1], jac.d_f[0]);
+    gt[1] = vmul(vsub(vsub(glab[0], glab[2]), glab[1]), jac.d_f[1]);
+    gt[2] = vmul(glab[2], jac.d_f[2]);            // = -(g_b BN_S3) d_f: the column below carries the other sign
+  } else {
+    const T ga = vmul(glab[1], T(k::AN_S3)), gb = vmul(glab[2], T(k::BN_S3));
+    gt[0] = vmul(ga, jac.d_f[0]);
+    gt[1] = vmul(vsub(vfma(glab[0], T(k::LN_S3), gb), ga), jac.d_f[1]);
+    gt[2] = vmul(gb, jac.d_f[2]);
+  }
+  constexpr float sg = FOLD ? 1.0f : -1.0f;
+  gx[0] = vmul(vfma(gt[2], T(sg * k::MB02), vfma(gt[1], T(k::MB01), vmul(gt[0], T(k::MB00)))), jac.d_lin[0]);
+  gx[1] = vmul(vfma(gt[2], T(sg * k::MB12), vfma(gt[1], T(k::MB11), vmul(gt[0], T(k::MB10)))), jac.d_lin[1]);
+  gx[2] = vmul(vfma(gt[2], T(sg * k::MB22), vfma(gt[1], T(k::MB21), vmul(gt[0], T(k::MB20)))), jac.d_lin[2]);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -218,15 +227,21 @@ CURL_HD void lab2rgb_fwd(const T lab[3], T rgb[3], RgbJac<T>* jac) {
   }
 }
 
-template <class T>
+// FOLD (the fused layer only): glab leaves WITHOUT its factors (FY_S3, FX_S3, FZ_S3); see "Units of the fused
+// layer's reverse sweep" below.
+template <class T, bool FOLD = false>
 CURL_HD void lab2rgb_bwd(const RgbJac<T>& jac, const T grgb[3], T glab[3]) {
   const T gv0 = vmul(grgb[0], jac.d_gam[0]), gv1 = vmul(grgb[1], jac.d_gam[1]), gv2 = vmul(grgb[2], jac.d_gam[2]);
   const T gf0 = vmul(vfma(gv2, T(k::NB02), vfma(gv1, T(k::NB01), vmul(gv0, T(k::NB00)))), jac.d_finv[0]);
   const T gf1 = vmul(vfma(gv2, T(k::NB12), vfma(gv1, T(k::NB11), vmul(gv0, T(k::NB10)))), jac.d_finv[1]);
   const T gf2 = vmul(vfma(gv2, T(k::NB22), vfma(gv1, T(k::NB21), vmul(gv0, T(k::NB20)))), jac.d_finv[2]);
-  glab[0] = vmul(vadd(vadd(gf0, gf1), gf2), T(k::FY_S3));
-  glab[1] = vmul(gf0, T(k::FX_S3));
-  glab[2] = vmul(gf2, T(k::FZ_S3));
+  if (FOLD) {
+    glab[0] = vadd(vadd(gf0, gf1), gf2); glab[1] = gf0; glab[2] = gf2;
+  } else {
+    glab[0] = vmul(vadd(vadd(gf0, gf1), gf2), T(k::FY_S3));
+    glab[1] = vmul(gf0, T(k::FX_S3));
+    glab[2] = vmul(gf2, T(k::FZ_S3));
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -249,7 +264,10 @@ struct HsvJac {
   T nkdf_h, nkdf_s, kmx_s;
 };
 
-template <class T, bool JAC, bool IN_UNIT>
+// FOLD (the fused layer only): the hue gradient arrives divided by 6 and the saturation gradient negated (see
+// "Units of the fused layer's reverse sweep"), so pass_h carries no 1/6 and nkdf_s, kmx_s no minus sign; with
+// IN_UNIT the input-clamp passes pin_c are part of the RGB curves' output gates (self_curve_fwd<.., OUT_PIN>).
+template <class T, bool JAC, bool IN_UNIT, bool FOLD = false>
 CURL_HD void rgb2hsv_fwd(const T x[3], T hsv[3], HsvJac<T>* jac) {
   T xc[3];
 #pragma unroll
@@ -281,16 +299,17 @@ CURL_HD void rgb2hsv_fwd(const T x[3], T hsv[3], HsvJac<T>* jac) {
   hsv[1] = vmin(vmax(s, T(k::HSV_LO)), T(1.0f));
   hsv[2] = mx;  // already inside [1e-9, 1]
   if (JAC) {
-    const T pass_h6 = vmul(vgate_eq(hsv[0], h), T((float)(1.0 / 6.0)));   // d h / d hr = 60/360
+    const T pass_h6 = FOLD ? vgate_eq(hsv[0], h) : vmul(vgate_eq(hsv[0], h), T((float)(1.0 / 6.0)));   // d h / d hr = 60/360
     const T pass_s = vgate_eq(hsv[1], s);
-    const T pin0 = vgate_eq(xc[0], x[0]), pin1 = vgate_eq(xc[1], x[1]), pin2 = vgate_eq(xc[2], x[2]);
     const T A = vmul(pass_h6, dinv);      // dinv == 0 on grey pixels blocks the hue gradient
     jac->A = A;
     jac->sd[0] = vsub(s2, s1); jac->sd[1] = vsub(s0, s2); jac->sd[2] = vsub(s1, s0);
-    jac->pin[0] = pin0; jac->pin[1] = pin1; jac->pin[2] = pin2;
+    if (!(FOLD && IN_UNIT)) {
+      jac->pin[0] = vgate_eq(xc[0], x[0]); jac->pin[1] = vgate_eq(xc[1], x[1]); jac->pin[2] = vgate_eq(xc[2], x[2]);
+    }
     const T num = vfma(s2, d01, vfma(s1, d20, vmul(s0, d12)));
     jac->nkdf_h = vmul(vmul(A, num), dinv);                    // -(d h / d df): d(1/df) = -1/df^2
-    jac->nkdf_s = vneg(vmul(pass_s, minv));                    // -(d s / d df), s = df / mx
+    jac->nkdf_s = FOLD ? vmul(pass_s, minv) : vneg(vmul(pass_s, minv));   // -(d s / d df), s = df / mx
     jac->kmx_s = vmul(jac->nkdf_s, s);                         // d s / d mx = -s / mx
     const T e0 = vgate_eq(xc[0], mn), e1 = vgate_eq(xc[1], mn);
     const T ns0 = vsub(T(1.0f), s0), ne0 = vsub(T(1.0f), e0);
@@ -303,14 +322,16 @@ CURL_HD void rgb2hsv_fwd(const T x[3], T hsv[3], HsvJac<T>* jac) {
   }
 }
 
-template <class T>
+template <class T, bool NO_PIN = false>
 CURL_HD void rgb2hsv_bwd(const HsvJac<T>& j, const T ghsv[3], T gx[3]) {
   const T ngdf = vfma(ghsv[0], j.nkdf_h, vmul(ghsv[1], j.nkdf_s));
   const T gmx = vsub(vfma(ghsv[1], j.kmx_s, ghsv[2]), ngdf);
   const T ghA = vmul(ghsv[0], j.A);
 #pragma unroll
-  for (int c = 0; c < 3; ++c)
-    gx[c] = vmul(j.pin[c], vfma(ghA, j.sd[c], vfma(ngdf, j.amin[c], vmul(gmx, j.amax[c]))));
+  for (int c = 0; c < 3; ++c) {
+    const T g = vfma(ghA, j.sd[c], vfma(ngdf, j.amin[c], vmul(gmx, j.amax[c])));
+    gx[c] = NO_PIN ? g : vmul(j.pin[c], g);
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -333,8 +354,13 @@ struct Hsv2RgbJac {
   T pin_v;
 };
 
-template <class T, bool JAC, bool IN_UNIT>
-CURL_HD void hsv2rgb_fwd(const T in[3], T rgb[3], Hsv2RgbJac<T>* jac) {
+// FOLD (the fused layer only): hk is formed without its factor 6 and hsv2rgb_bwd returns -d/ds (see "Units of
+// the fused layer's reverse sweep").
+// poff (the fused layer's backward with a {0,1} mask): added to p, 0 for a kept pixel and NaN for a masked one
+// -- the NaN reaches all three outputs, the final clamp gate [sat(x + res) == x + res] is then false, and the
+// mask has been applied with one packed add instead of three packed multiplies.  Nothing else reads p.
+template <class T, bool JAC, bool IN_UNIT, bool FOLD = false, bool POFF = false>
+CURL_HD void hsv2rgb_fwd(const T in[3], T rgb[3], Hsv2RgbJac<T>* jac, T poff = T(0.0f)) {
   const T h = IN_UNIT ? in[0] : vsat(in[0]);                    // colors.py:141
   const T s = IN_UNIT ? in[1] : vsat(in[1]);
   const T v = IN_UNIT ? in[2] : vsat(in[2]);
@@ -349,7 +375,7 @@ CURL_HD void hsv2rgb_fwd(const T in[3], T rgb[3], Hsv2RgbJac<T>* jac) {
   } else {
     const T yr = vabs_add(tr, -1.0f), yg = vnabs_add(tg, 2.0f), yb = vnabs_add(tb, 2.0f);
     ramp[0] = vsat(yr); ramp[1] = vsat(yg); ramp[2] = vsat(yb);
-    T w6 = vmul(w, T(6.0f));
+    T w6 = FOLD ? w : vmul(w, T(6.0f));
     if (!IN_UNIT) w6 = vmul(w6, vgate_eq(h, in[0]));
     // on a slope (ends included, as torch.clamp passes gradient on the closed interval): +-1, else 0
     jac->hk[0] = vmul(w6, vcopysign(vgate_eq(ramp[0], yr), tr));
@@ -360,18 +386,19 @@ CURL_HD void hsv2rgb_fwd(const T in[3], T rgb[3], Hsv2RgbJac<T>* jac) {
     jac->vs = IN_UNIT ? v : vmul(v, vgate_eq(s, in[1]));
     jac->pin_v = IN_UNIT ? T(1.0f) : vgate_eq(v, in[2]);
   }
-  rgb[0] = vfma(w, ramp[0], p);                                 // colors.py:143-150
-  rgb[1] = vfma(w, ramp[1], p);                                 // colors.py:153-159
-  rgb[2] = vfma(w, ramp[2], p);                                 // colors.py:162-168 ; colors.py:175 inert (above)
+  const T pp = POFF ? vadd(p, poff) : p;
+  rgb[0] = vfma(w, ramp[0], pp);                                // colors.py:143-150
+  rgb[1] = vfma(w, ramp[1], pp);                                // colors.py:153-159
+  rgb[2] = vfma(w, ramp[2], pp);                                // colors.py:162-168 ; colors.py:175 inert (above)
 }
 
-template <class T, bool IN_UNIT>
+template <class T, bool IN_UNIT, bool FOLD = false>
 CURL_HD void hsv2rgb_bwd(const Hsv2RgbJac<T>& j, const T grgb[3], T ghsv[3]) {
   const T gw = vfma(grgb[0], j.ramp[0], vfma(grgb[1], j.ramp[1], vmul(grgb[2], j.ramp[2])));
   ghsv[0] = vfma(grgb[0], j.hk[0], vfma(grgb[1], j.hk[1], vmul(grgb[2], j.hk[2])));
   const T gp = vsub(vadd(vadd(grgb[0], grgb[1]), grgb[2]), gw);   // p enters r, g, b directly and w = v - p
   const T gv = vfma(gp, j.oms, gw);                               // v enters through w and p = v (1 - s)
-  ghsv[1] = vneg(vmul(gp, j.vs));
+  ghsv[1] = FOLD ? vmul(gp, j.vs) : vneg(vmul(gp, j.vs));
   ghsv[2] = IN_UNIT ? gv : vmul(gv, j.pin_v);
 }
 
@@ -387,14 +414,17 @@ struct CurveJac {
   T d;     // pass_out * pass_in * (alpha + 2 beta xin)
 };
 
-template <class T, bool JAC, bool PRECLAMP>
+// OUT_PIN (the fused layer's RGB curves): the output gate is [clamp(y, 1e-9, 1) == y], i.e. it includes the pass
+// of RGB2HSV's input clamp (colors.py:205) that follows directly, so that stage need not multiply it in; the
+// max(o, 1e-9) is the value RGB2HSV forms anyway.
+template <class T, bool JAC, bool PRECLAMP, bool OUT_PIN = false>
 CURL_HD T self_curve_fwd(T x, float alpha, float beta, CurveJac<T>* jac) {
   const T xin = PRECLAMP ? vsat(x) : x;
   const T s = vfma(T(beta), xin, T(alpha));        // curves.py:31-32 (closed form)
   if (!JAC) return vmul_sat(xin, s);               // curves.py:35-36
   const T y = vmul(xin, s);
   const T o = vsat(y);
-  const T po = vgate_eq(o, y);
+  const T po = OUT_PIN ? vgate_eq(vmax(o, T(k::HSV_LO)), y) : vgate_eq(o, y);
   jac->a = vmul(po, xin);
   T d = vmul(po, vfma(T(beta), xin, s));
   if (PRECLAMP) d = vmul(d, vgate_eq(xin, x));
@@ -444,11 +474,11 @@ CURL_HD void single_curve_bwd(const T x[3], int cin, int cout, float alpha, floa
 template <class T>
 struct Self3Jac { CurveJac<T> c[3]; };
 
-template <class T, bool JAC>
+template <class T, bool JAC, bool OUT_PIN = false>
 CURL_HD void adjust_self3_fwd(const T x[3], const float* ab, T y[3], Self3Jac<T>* jac) {
-  y[0] = self_curve_fwd<T, JAC, false>(x[0], ab[0], ab[1], JAC ? &jac->c[0] : nullptr);
-  y[1] = self_curve_fwd<T, JAC, true>(x[1], ab[2], ab[3], JAC ? &jac->c[1] : nullptr);
-  y[2] = self_curve_fwd<T, JAC, true>(x[2], ab[4], ab[5], JAC ? &jac->c[2] : nullptr);
+  y[0] = self_curve_fwd<T, JAC, false, OUT_PIN>(x[0], ab[0], ab[1], JAC ? &jac->c[0] : nullptr);
+  y[1] = self_curve_fwd<T, JAC, true, OUT_PIN>(x[1], ab[2], ab[3], JAC ? &jac->c[1] : nullptr);
+  y[2] = self_curve_fwd<T, JAC, true, OUT_PIN>(x[2], ab[4], ab[5], JAC ? &jac->c[2] : nullptr);
 }
 
 template <class T>
@@ -494,17 +524,46 @@ CURL_HD void adjust_hsv_fwd(const T x[3], const float* ab, T y[3], HsvCurveJac<T
                  : self_curve_fwd<T, JAC, true>(x[2], ab[6], ab[7], JAC ? &jac->cv : nullptr);
 }
 
+// beta1: the hue -> sat curve's beta (ab[3]); the fused layer passes it in the folded units of its reverse sweep
 template <class T>
-CURL_HD void adjust_hsv_bwd(const HsvCurveJac<T>& j, const float* ab, const T gy[3], T gx[3], T* mom /*8*/) {
+CURL_HD void adjust_hsv_bwd(const HsvCurveJac<T>& j, float beta1, const T gy[3], T gx[3], T* mom /*8*/) {
   gx[2] = self_curve_bwd(j.cv, gy[2], mom + 6);
   const T gs1 = self_curve_bwd(j.cs, gy[1], mom + 4);
   const T gsc = vmul(gs1, j.p);                    // d loss / d scale of curve 1
   mom[2] = vadd(mom[2], gsc);
   mom[3] = vfma(gsc, j.h1, mom[3]);
   gx[1] = vmul(gs1, j.q);
-  const T gh1 = vfma(gsc, T(ab[3]), gy[0]);        // hue feeds curve 1 through beta_1
+  const T gh1 = vfma(gsc, T(beta1), gy[0]);        // hue feeds curve 1 through beta_1
   gx[0] = self_curve_bwd(j.ch, gh1, mom + 0);
 }
+
+// ------------------------------------------------------------------------------------------------
+// Units of the fused layer's reverse sweep (FOLD).  Between two curve groups the gradient passes through
+// constant factors: (FY_S3, FX_S3, FZ_S3) leaving lab2rgb_bwd, (LN_S3, AN_S3, BN_S3) entering rgb2lab_bwd, the 6
+// of d ramp / d h, the 1/6 of d h / d hr, the signs of d p / d s and d s / d df.  The reverse sweep leaves them
+// out (11 packed instructions per pixel pair) and works in scaled units instead:
+//   gradient arriving at the Lab curves  = true / (FY_S3, FX_S3, FZ_S3);  leaving them towards rgb2lab_bwd the
+//     products FY_S3 LN_S3 = (300/116)(1.16/3) = 1, FX_S3 AN_S3 = 1, FZ_S3 BN_S3 = -1 remain (the two
+//     conversions are inverse affine maps): only a sign, which rgb2lab_bwd's matrix column absorbs;
+//   hue gradient = true / 6 between hsv2rgb_bwd and rgb2hsv_bwd; sat gradient = -true on the same stretch.
+// What is left to do per image, not per pixel:
+//   curve_fold_m(c): factor of the two moments of curve c after the reduction;
+//   layer_beta1(beta_1) = -beta_1 / 6 for gh1 = gsc beta_1 + g_hue in those units.
+// c = 0..2 Lab, 3..5 RGB, 6..9 HSV (hue, hue->sat, sat, val).  The stand-alone ops use 1 everywhere.
+// ------------------------------------------------------------------------------------------------
+CURL_HD double curve_fold_m(bool layer, int c) {
+  if (!layer) return 1.0;
+  switch (c) {
+    case 0: return 300.0 / 116.0;
+    case 1: return 660.0 / 500.0;
+    case 2: return -660.0 / 200.0;
+    case 6: return 6.0;
+    case 7: return -1.0;
+    case 8: return -1.0;
+    default: return 1.0;
+  }
+}
+CURL_HD float layer_beta1(float beta1) { return (float)((double)beta1 * (-1.0 / 6.0)); }
 
 // ------------------------------------------------------------------------------------------------
 // The layer                                     (reference model.py:137-176)
@@ -559,33 +618,60 @@ struct KeepInRegisters {
 constexpr int PARK_STAGES = CURL_PARK_STAGES;
 constexpr int SPILL_SLOTS = 6 * PARK_STAGES;   // LabJac 6 + Self3Jac 6 + RgbJac 6 + Self3Jac 6
 
-// Six values per record, parked and fetched two at a time (put2 / get2 on an even slot).
+// Six values per record, parked and fetched as a whole (put6 / get6 at slot o, a multiple of 6).
 template <class T, class S> CURL_HD void spill_save(const S& sp, int o, const LabJac<T>& j) {
-  sp.put2(o, j.d_lin[0], j.d_lin[1]); sp.put2(o + 2, j.d_lin[2], j.d_f[0]); sp.put2(o + 4, j.d_f[1], j.d_f[2]);
+  sp.put6(o, j.d_lin[0], j.d_lin[1], j.d_lin[2], j.d_f[0], j.d_f[1], j.d_f[2]);
 }
 template <class T, class S> CURL_HD void spill_load(const S& sp, int o, LabJac<T>& j) {
-  sp.get2(o, j.d_lin[0], j.d_lin[1]); sp.get2(o + 2, j.d_lin[2], j.d_f[0]); sp.get2(o + 4, j.d_f[1], j.d_f[2]);
+  sp.get6(o, j.d_lin[0], j.d_lin[1], j.d_lin[2], j.d_f[0], j.d_f[1], j.d_f[2]);
 }
 template <class T, class S> CURL_HD void spill_save(const S& sp, int o, const RgbJac<T>& j) {
-  sp.put2(o, j.d_finv[0], j.d_finv[1]); sp.put2(o + 2, j.d_finv[2], j.d_gam[0]); sp.put2(o + 4, j.d_gam[1], j.d_gam[2]);
+  sp.put6(o, j.d_finv[0], j.d_finv[1], j.d_finv[2], j.d_gam[0], j.d_gam[1], j.d_gam[2]);
 }
 template <class T, class S> CURL_HD void spill_load(const S& sp, int o, RgbJac<T>& j) {
-  sp.get2(o, j.d_finv[0], j.d_finv[1]); sp.get2(o + 2, j.d_finv[2], j.d_gam[0]); sp.get2(o + 4, j.d_gam[1], j.d_gam[2]);
+  sp.get6(o, j.d_finv[0], j.d_finv[1], j.d_finv[2], j.d_gam[0], j.d_gam[1], j.d_gam[2]);
 }
 template <class T, class S> CURL_HD void spill_save(const S& sp, int o, const Self3Jac<T>& j) {
-#pragma unroll
-  for (int c = 0; c < 3; ++c) sp.put2(o + 2 * c, j.c[c].a, j.c[c].d);
+  sp.put6(o, j.c[0].a, j.c[0].d, j.c[1].a, j.c[1].d, j.c[2].a, j.c[2].d);
 }
 template <class T, class S> CURL_HD void spill_load(const S& sp, int o, Self3Jac<T>& j) {
-#pragma unroll
-  for (int c = 0; c < 3; ++c) sp.get2(o + 2 * c, j.c[c].a, j.c[c].d);
+  sp.get6(o, j.c[0].a, j.c[0].d, j.c[1].a, j.c[1].d, j.c[2].a, j.c[2].d);
 }
 
-// Recompute-forward + reverse.  mom: 20 accumulators (S0,S1 per curve), accumulated in place.
-// SPILL: a policy with put2(slot, T, T) / get2(slot, T&, T&) (see above) or KeepInRegisters.
+// RGB -> HSV record (tensor-memory parking only, -DCURL_PARK_J5): the 13 values the fused layer uses (no pin).
+#ifdef CURL_PARK_J5
+constexpr bool PARK_J5 = true;
+#else
+constexpr bool PARK_J5 = false;
+#endif
+constexpr int J5_SLOT = 24, J5_SLOTS = 14;
+template <class T, class S> CURL_HD void spill_save(const S& sp, int o, const HsvJac<T>& j) {
+  sp.put8(o, j.sd[0], j.sd[1], j.sd[2], j.amax[0], j.amax[1], j.amax[2], j.amin[0], j.amin[1]);
+  sp.put6(o + 8, j.amin[2], j.A, j.nkdf_h, j.nkdf_s, j.kmx_s, j.kmx_s);
+}
+template <class T, class S> CURL_HD void spill_load(const S& sp, int o, HsvJac<T>& j) {
+  T dummy;
+  sp.get8(o, j.sd[0], j.sd[1], j.sd[2], j.amax[0], j.amax[1], j.amax[2], j.amin[0], j.amin[1]);
+  sp.get6(o + 8, j.amin[2], j.A, j.nkdf_h, j.nkdf_s, j.kmx_s, dummy);
+}
+
+// The lane value layer_bwd takes as `m`: the mask itself for MASK_F32 (multiplied in at every stage like the
+// reference), ignored for MASK_NONE, and for a {0,1} mask (MASK_U8) the GATE OFFSET 0 (kept) / NaN (masked).
+CURL_HD float bwd_mask_lane_u8(bool keep) {
+#if defined(__CUDA_ARCH__)
+  return keep ? 0.0f : __int_as_float(0x7fc00000);
+#else
+  return keep ? 0.0f : NAN;
+#endif
+}
+
+// Recompute-forward + reverse.  mom: 20 accumulators (S0,S1 per curve), accumulated in place, in the folded units
+// of curve_fold_m.  ab: 10 x (alpha, beta) followed by layer_beta1(beta of the hue -> sat curve).
+// SPILL: a policy with put6(slot, 6 x T) / get6(slot, 6 x T&) (see above) or KeepInRegisters.
 template <class T, int MK, bool WANT_GX, class SPILL>
 CURL_HD void layer_bwd(const T x[3], T m, const float* ab, const T gout[3], T gx[3], T* mom, const SPILL& sp) {
   constexpr bool kSpill = SPILL::kActive;
+  constexpr bool UNIT = MK != MASK_F32;          // no fractional mask between the stages: values stay in [0, 1]
   T lab[3], lab2[3], rgb[3], rgb2[3], hsv[3], hsv2[3], res[3];
   LabJac<T> j1; Self3Jac<T> j2; RgbJac<T> j3; Self3Jac<T> j4; HsvJac<T> j5; HsvCurveJac<T> j6; Hsv2RgbJac<T> j7;
   rgb2lab_fwd<T, WANT_GX>(x, lab, &j1);
@@ -595,40 +681,45 @@ CURL_HD void layer_bwd(const T x[3], T m, const float* ab, const T gout[3], T gx
   if (MK == MASK_F32) vscale3(lab2, m);
   lab2rgb_fwd<T, true>(lab2, rgb, &j3);
   if constexpr (kSpill && PARK_STAGES >= 3) spill_save<T>(sp, 12, j3);
-  adjust_self3_fwd<T, true>(rgb, ab + 6, rgb2, &j4);
+  adjust_self3_fwd<T, true, UNIT>(rgb, ab + 6, rgb2, &j4);      // UNIT: output gates include RGB2HSV's input clamp
   if constexpr (kSpill && PARK_STAGES >= 4) spill_save<T>(sp, 18, j4);
   if (MK == MASK_F32) vscale3(rgb2, m);
-  rgb2hsv_fwd<T, true, MK != MASK_F32>(rgb2, hsv, &j5);
+  rgb2hsv_fwd<T, true, UNIT, true>(rgb2, hsv, &j5);
+  if constexpr (kSpill && PARK_J5 && UNIT) spill_save<T>(sp, J5_SLOT, j5);
   adjust_hsv_fwd<T, true, true>(hsv, ab + 12, hsv2, &j6);
   if (MK == MASK_F32) {
     vscale3(hsv2, m);
-    hsv2rgb_fwd<T, true, false>(hsv2, res, &j7);
+    hsv2rgb_fwd<T, true, false, true>(hsv2, res, &j7);
+  } else if (MK == MASK_U8) {
+    hsv2rgb_fwd<T, true, true, true, true>(hsv2, res, &j7, m);   // m is the gate offset here: 0 keeps, NaN masks
   } else {
-    hsv2rgb_fwd<T, true, true>(hsv2, res, &j7);
+    hsv2rgb_fwd<T, true, true, true>(hsv2, res, &j7);
   }
   T g[3];
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
     const T sum = vadd(x[c], res[c]);
-    const T pass = vgate_eq(vsat(sum), sum);         // clamp passes on [0,1] inclusive
-    g[c] = vmul(gout[c], (MK == MASK_NONE) ? pass : vmul(pass, m));
+    const T pass = vgate_eq(vsat(sum), sum);         // clamp passes on [0,1] inclusive (false for a masked pixel's NaN)
+    g[c] = vmul(gout[c], MK == MASK_F32 ? vmul(pass, m) : pass);
   }
   T a[3], b[3];
-  if (MK == MASK_F32) hsv2rgb_bwd<T, false>(j7, g, a); else hsv2rgb_bwd<T, true>(j7, g, a);
+  if (MK == MASK_F32) hsv2rgb_bwd<T, false, true>(j7, g, a); else hsv2rgb_bwd<T, true, true>(j7, g, a);
   if (MK == MASK_F32) vscale3(a, m);
-  adjust_hsv_bwd(j6, ab + 12, a, b, mom + 12);
-  rgb2hsv_bwd(j5, b, a);
+  adjust_hsv_bwd(j6, ab[2 * LAYER_CURVES], a, b, mom + 12);
+  if constexpr (kSpill) sp.before_loads();       // parked records are about to be read back
+  if constexpr (kSpill && PARK_J5 && UNIT) spill_load<T>(sp, J5_SLOT, j5);
+  rgb2hsv_bwd<T, UNIT>(j5, b, a);
   if (MK == MASK_F32) vscale3(a, m);
   if constexpr (kSpill && PARK_STAGES >= 4) spill_load<T>(sp, 18, j4);
   adjust_self3_bwd(j4, a, b, mom + 6);
   if constexpr (kSpill && PARK_STAGES >= 3) spill_load<T>(sp, 12, j3);
-  lab2rgb_bwd(j3, b, a);
+  lab2rgb_bwd<T, true>(j3, b, a);
   if (MK == MASK_F32) vscale3(a, m);
   if constexpr (kSpill && PARK_STAGES >= 2) spill_load<T>(sp, 6, j2);
   adjust_self3_bwd(j2, a, b, mom + 0);
   if (WANT_GX) {
     if constexpr (kSpill && PARK_STAGES >= 1) spill_load<T>(sp, 0, j1);
-    rgb2lab_bwd(j1, b, a);
+    rgb2lab_bwd<T, true>(j1, b, a);
     gx[0] = vadd(g[0], a[0]); gx[1] = vadd(g[1], a[1]); gx[2] = vadd(g[2], a[2]);
   }
 }

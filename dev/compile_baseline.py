@@ -1,8 +1,14 @@
-"""One-off baseline (not part of bench.py, not a product path): the reference's op sequence (oracle/curl_oracle.py)
-under torch.compile (inductor) on the B200 -- "the reference's Blackwell path" of SURVEY.md 8(d) -- beside
-this library, forward + backward with image gradient.  Prints one JSON line.
+"""`torch.compile` of the reference's op sequence on the B200 -- "the reference's Blackwell path" of SURVEY.md 8(d),
+the strongest stand-in the fused kernels must beat -- beside eager PyTorch and this library.  bench.py runs it
+as a subprocess (gpu_compile_baseline; a hung or failed compile must not take the headline line with it) and
+embeds the one JSON line it prints.
 
     python dev/compile_baseline.py [B H W]
+
+What is compiled: oracle/curl_oracle_compile.py -- the oracle with `non_nan_inv` written as torch.where and the
+in-place channel writes as torch.stack, the only changes dynamo needs; pinned to the oracle on CPU in
+tests/test_oracle_pins.py::test_compile_variant_equals_oracle.  fullgraph=True (one graph, no breaks),
+inductor defaults (Triton kernels).  Not a product path.
 """
 import json
 import os
@@ -14,6 +20,7 @@ sys.path.insert(0, ROOT)
 import torch  # noqa: E402
 
 from oracle import curl_oracle as O  # noqa: E402
+from oracle import curl_oracle_compile as OC  # noqa: E402
 import curl_b200  # noqa: E402
 
 
@@ -40,35 +47,52 @@ def main():
     gout = torch.randn(B, 3, H, W, generator=g, device=dev)
     greg = torch.ones(B, device=dev)
     mpx = B * H * W / 1e6
-    res = {"shape": [B, H, W]}
+    res = {"shape": [B, H, W], "mpx_per_step": mpx, "torch": torch.__version__}
 
-    def run(layer_fn):
+    def fwd_bwd(layer_fn):
         def f():
             x = img.detach().requires_grad_(True)
             l, r, h = (t.detach().requires_grad_(True) for t in (L, R, Hk))
             o, rg = layer_fn(x, mask, l, r, h)
             torch.autograd.backward([o, rg], [gout, greg])
-            return x.grad
+            return x.grad, l.grad, o.detach()
         return f
 
-    ours = curl_b200.CURLLayer().to(dev)
-    ms = timed(run(ours), 10)
-    res["curl_b200"] = {"ms": ms, "mpx_per_s": mpx / (ms / 1e3)}
-    g_ours = run(ours)().clone()
+    def fwd(layer_fn):
+        def f():
+            with torch.no_grad():
+                return layer_fn(img, mask, L, R, Hk)[0]
+        return f
 
-    ms = timed(run(O.curl_layer), 3)
-    res["eager"] = {"ms": ms, "mpx_per_s": mpx / (ms / 1e3)}
+    def entry(ms_f, ms_fb):
+        return {"fwd_ms": ms_f, "fwd_mpx_per_s": mpx / (ms_f / 1e3), "fwd_bwd_ms": ms_fb,
+                "fwd_bwd_mpx_per_s": mpx / (ms_fb / 1e3)}
+
+    ours = curl_b200.CURLLayer().to(dev)
+    res["curl_b200"] = entry(timed(fwd(ours), 20), timed(fwd_bwd(ours), 10))
+    gi_o, gl_o, out_o = (t.clone() for t in fwd_bwd(ours)())
+
+    torch.cuda.reset_peak_memory_stats(dev)
+    res["eager"] = entry(timed(fwd(O.curl_layer), 3), timed(fwd_bwd(O.curl_layer), 3))
+    res["eager"]["peak_mem_gb"] = torch.cuda.max_memory_allocated(dev) / 1e9
 
     t0 = time.time()
     try:
-        comp = torch.compile(O.curl_layer)
-        fc = run(comp)
-        g_c = fc().clone()
+        comp = torch.compile(OC.curl_layer, fullgraph=True)
+        fb = fwd_bwd(comp)
+        gi_c, gl_c, out_c = (t.clone() for t in fb())
+        ff = fwd(comp)
+        ff()
         torch.cuda.synchronize()
         res["compile_s"] = time.time() - t0
-        ms = timed(fc, 5)
-        res["torch_compile"] = {"ms": ms, "mpx_per_s": mpx / (ms / 1e3),
-                                "max_abs_gimg_vs_ours": float((g_c - g_ours).abs().max())}
+        torch.cuda.reset_peak_memory_stats(dev)
+        e = entry(timed(ff, 10), timed(fb, 5))
+        e["peak_mem_gb"] = torch.cuda.max_memory_allocated(dev) / 1e9
+        e["frac_out_over_1e5_vs_curl_b200"] = float(((out_c - out_o).abs() > 1e-5).float().mean())
+        e["rel_gL_vs_curl_b200"] = float((gl_c - gl_o).abs().max() / gl_o.abs().max())
+        e["what"] = ("torch.compile(fullgraph=True, inductor) of oracle/curl_oracle_compile.py = the reference's op "
+                     "sequence with non_nan_inv as torch.where and channel writes as torch.stack")
+        res["torch_compile"] = e
     except Exception as e:
         res["torch_compile"] = {"unavailable": "%s: %s" % (type(e).__name__, str(e)[:300])}
     print(json.dumps(res))

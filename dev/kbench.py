@@ -7,7 +7,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from curl_b200 import _lib as L
 
 def bind(path):
-    lib = ctypes.CDLL(path)
+    lib = ctypes.CDLL(os.path.abspath(path))
     for name, (res, args) in L.SIGNATURES.items():
         if not hasattr(lib, name):
             continue        # a layer-only experiment build

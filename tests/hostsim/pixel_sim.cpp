@@ -26,6 +26,8 @@ struct Seg { const float* p; int64_t ld; int nc, K; float* g; };
 struct Curves {
   std::vector<float> C, ab;
   double reg = 0.0;
+  bool layer = false;        // the fused layer's folded units (curve_fold_m, layer_beta1)
+  // ab: (alpha, beta) per curve, then layer_beta1 -- the layout the kernels stage in shared memory
   void stage(const Seg* segs, int nseg, int b) {
     C.clear(); ab.clear(); reg = 0.0;
     for (int s = 0; s < nseg; ++s) {
@@ -41,6 +43,7 @@ struct Curves {
         reg += curve_regulariser(C.data() + off, segs[s].K);
         off += segs[s].K;
       }
+    if (layer) ab.push_back(layer_beta1(ab[2 * 7 + 1]));
   }
   void grads(const Seg* segs, int nseg, int b, const std::vector<double>& mom, double greg) const {
     int off = 0, cb = 0;
@@ -49,7 +52,8 @@ struct Curves {
       for (int c = 0; c < segs[s].nc; ++c) {
         for (int i = 0; i < K; ++i)
           segs[s].g[(size_t)b * segs[s].nc * K + c * K + i] =
-              curve_knot_grad(C.data() + off, K, i, mom[2 * (cb + c)], mom[2 * (cb + c) + 1], greg, true);
+              curve_knot_grad(C.data() + off, K, i, mom[2 * (cb + c)] * curve_fold_m(layer, cb + c),
+                              mom[2 * (cb + c) + 1] * curve_fold_m(layer, cb + c), greg, true);
         off += K;
       }
       cb += segs[s].nc;
@@ -80,6 +84,7 @@ int sim_layer(int do_bwd, const float* img, const void* mask, int mask_kind, con
               int Kl, int Kr, int Kh) {
   Seg segs[3] = {{L, ldL, 3, Kl, gL}, {R, ldR, 3, Kr, gR}, {Hk, ldH, 4, Kh, gH}};
   Curves cv;
+  cv.layer = true;
   for (int b = 0; b < B; ++b) {
     cv.stage(segs, 3, b);
     if (reg) reg[b] = (float)cv.reg;
@@ -100,7 +105,7 @@ int sim_layer(int do_bwd, const float* img, const void* mask, int mask_kind, con
         float gx[3];
         for (auto& v : mom) v = 0.0f;
         if (mask_kind == MASK_NONE) layer_bwd_mk<MASK_NONE>(x, m, cv.ab.data(), gy, gx, mom.data());
-        else if (mask_kind == MASK_U8) layer_bwd_mk<MASK_U8>(x, m, cv.ab.data(), gy, gx, mom.data());
+        else if (mask_kind == MASK_U8) layer_bwd_mk<MASK_U8>(x, bwd_mask_lane_u8(m != 0.0f), cv.ab.data(), gy, gx, mom.data());
         else layer_bwd_mk<MASK_F32>(x, m, cv.ab.data(), gy, gx, mom.data());
         for (int k = 0; k < 20; ++k) momd[k] += (double)mom[k];
         if (gimg) { gimg[o] = gx[0]; gimg[o + HW] = gx[1]; gimg[o + 2 * (size_t)HW] = gx[2]; }
@@ -151,7 +156,7 @@ int sim_adjust(int do_bwd, int group, const float* in, const float* P, int64_t l
       if (group == 2) {
         HsvCurveJac<float> j;
         adjust_hsv_fwd<float, true, false>(x, cv.ab.data(), y, &j);
-        adjust_hsv_bwd(j, cv.ab.data(), gy, gx, mom);
+        adjust_hsv_bwd(j, cv.ab[3], gy, gx, mom);
       } else {
         Self3Jac<float> j;
         adjust_self3_fwd<float, true>(x, cv.ab.data(), y, &j);
