@@ -31,8 +31,19 @@ constexpr int THREADS = CURL_THREADS;
 #ifndef BWD_SPILL
 #define BWD_SPILL (6 * CURL_PARK_STAGES)
 #endif
+// Shipped configuration of the aligned backward: Jac records AND the 20 moment accumulators parked in tensor
+// memory (TmemSpill below), which brings the kernel to 128 registers = four 128-thread blocks per SM.
+// -DCURL_PARK_SMEM selects the round-1 configuration (records in shared memory, moments in registers, 3 blocks).
+#if !defined(CURL_PARK_SMEM) && !defined(CURL_PARK_TMEM)
+#define CURL_PARK_TMEM
+#define CURL_PARK_MOM
+#endif
 #ifndef BWD_MIN_BLOCKS
+#ifdef CURL_PARK_MOM
+#define BWD_MIN_BLOCKS 4
+#else
 #define BWD_MIN_BLOCKS 3
+#endif
 #endif
 constexpr int MAX_SEGS = 3;
 constexpr int MAX_CURVES = 10;
@@ -549,6 +560,7 @@ template <class Op> constexpr size_t tma_smem_bytes() {
 // (conflict-free) and one instruction parks or fetches two packed values.
 struct SmemSpill {
   static constexpr bool kActive = true;
+  static constexpr bool kMomParked = false;
   unsigned base;   // shared-space byte address, already offset by threadIdx.x * 16
   // asm volatile: the compiler must not forward the stored value to the later load (that would keep
   // the value live in a register, which is exactly what parking is meant to avoid)
@@ -572,19 +584,33 @@ struct SmemSpill {
   __device__ __forceinline__ void get6(int o, F2& a, F2& b, F2& c, F2& d, F2& e, F2& f) const {
     get2(o, a, b); get2(o + 2, c, d); get2(o + 4, e, f);
   }
+  // split fetch: the LDS results are tracked by the hardware scoreboard, nothing to wait for explicitly
+  __device__ __forceinline__ void get6_issue(int o, F2& a, F2& b, F2& c, F2& d, F2& e, F2& f) const { get6(o, a, b, c, d, e, f); }
+  __device__ __forceinline__ void get6_wait(F2&, F2&, F2&, F2&, F2&, F2&) const {}
 };
 
 // The same parking space in TENSOR MEMORY (-DCURL_PARK_TMEM): each thread owns one TMEM lane (shape 32x32b: lane
 // i of a warp addresses TMEM lane 32 (warp % 4) + i) and parks a record of six packed values = 12 consecutive
 // 32-bit columns with tcgen05.st (x8 + x4), fetching it with tcgen05.ld + tcgen05.wait::ld.  No shared memory, no
 // LSU instructions, no bank conflicts; the block allocates TMEM_COLS columns for its lifetime.
-#ifdef CURL_PARK_J5
-constexpr int TMEM_COLS = 128;      // 24 + 14 slots of two columns, a power of two >= 32
+#if defined(CURL_PARK_J5) || defined(CURL_PARK_MOM)
+constexpr int TMEM_COLS = 128;      // records: columns 0..75 (24 + 14 slots of two columns); moments: 80..127
 #else
 constexpr int TMEM_COLS = 64;       // >= 2 * Op::SPILL (48), a power of two >= 32
 #endif
+#ifdef CURL_PARK_MOM
+constexpr bool PARK_MOM = true;     // the 20 moment accumulators live in tensor memory between their updates
+#else
+constexpr bool PARK_MOM = false;
+#endif
+constexpr int TMEM_MOM_COL = 80;    // Lab 80..91, RGB 92..103, HSV 104..119 (two columns per accumulator)
 struct TmemSpill {
   static constexpr bool kActive = true;
+  static constexpr bool kMomParked = PARK_MOM;
+  __device__ __forceinline__ void mom_get6(int k, F2* m) const { get6((TMEM_MOM_COL >> 1) + k, m[0], m[1], m[2], m[3], m[4], m[5]); }
+  __device__ __forceinline__ void mom_put6(int k, const F2* m) const { put6((TMEM_MOM_COL >> 1) + k, m[0], m[1], m[2], m[3], m[4], m[5]); }
+  __device__ __forceinline__ void mom_get8(F2* m) const { get8((TMEM_MOM_COL >> 1) + 12, m[0], m[1], m[2], m[3], m[4], m[5], m[6], m[7]); }
+  __device__ __forceinline__ void mom_put8(const F2* m) const { put8((TMEM_MOM_COL >> 1) + 12, m[0], m[1], m[2], m[3], m[4], m[5], m[6], m[7]); }
   unsigned base;   // TMEM address: this warp's lane quarter in bits 31..16, the block's first column in bits 15..0
   // tcgen05.st is asynchronous: the stores of this pixel pair must have completed before they are read back
   __device__ __forceinline__ void before_loads() const { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
@@ -594,6 +620,21 @@ struct TmemSpill {
         "tcgen05.st.sync.aligned.32x32b.x4.b32 [%0 + 8], {%9, %10, %11, %12};" ::"r"(base + 2 * o),
         "f"(a.lo()), "f"(a.hi()), "f"(b.lo()), "f"(b.hi()), "f"(c.lo()), "f"(c.hi()), "f"(d.lo()), "f"(d.hi()),
         "f"(e.lo()), "f"(e.hi()), "f"(f.lo()), "f"(f.hi()) : "memory");
+  }
+  // split fetch: the values are exchanged as raw 64-bit registers so that no instruction touches them between the
+  // tcgen05.ld and the tcgen05.wait::ld (which takes them as in/out operands: nothing may be moved across it)
+  __device__ __forceinline__ void get6_issue(int o, F2& a, F2& b, F2& c, F2& d, F2& e, F2& f) const {
+    asm volatile(
+        "{\n.reg .b32 t<12>;\n"
+        "tcgen05.ld.sync.aligned.32x32b.x8.b32 {t0, t1, t2, t3, t4, t5, t6, t7}, [%6];\n"
+        "tcgen05.ld.sync.aligned.32x32b.x4.b32 {t8, t9, t10, t11}, [%6 + 8];\n"
+        "mov.b64 %0, {t0, t1};\n mov.b64 %1, {t2, t3};\n mov.b64 %2, {t4, t5};\n"
+        "mov.b64 %3, {t6, t7};\n mov.b64 %4, {t8, t9};\n mov.b64 %5, {t10, t11};\n}"
+        : "=l"(a.u), "=l"(b.u), "=l"(c.u), "=l"(d.u), "=l"(e.u), "=l"(f.u)
+        : "r"(base + 2 * o) : "memory");
+  }
+  __device__ __forceinline__ void get6_wait(F2& a, F2& b, F2& c, F2& d, F2& e, F2& f) const {
+    asm volatile("tcgen05.wait::ld.sync.aligned;" : "+l"(a.u), "+l"(b.u), "+l"(c.u), "+l"(d.u), "+l"(e.u), "+l"(f.u)::"memory");
   }
   __device__ __forceinline__ void put8(int o, F2 a, F2 b, F2 c, F2 d, F2 e, F2 f, F2 g, F2 h) const {
     asm volatile(
@@ -649,6 +690,7 @@ __global__ void __launch_bounds__(BWD_THREADS, BWD_MIN_BLOCKS) bwd_tma_kernel(co
   constexpr bool USE_TMEM = PARK_IN_TMEM && Op::SPILL > 0;
   static_assert(!USE_TMEM || (2 * Op::SPILL <= TMEM_COLS && BWD_THREADS == 128), "TMEM parking: 4 warps, 2 columns per slot");
   static_assert(!PARK_J5 || PARK_IN_TMEM, "-DCURL_PARK_J5 needs -DCURL_PARK_TMEM");
+  static_assert(!PARK_MOM || PARK_IN_TMEM, "-DCURL_PARK_MOM needs -DCURL_PARK_TMEM");
   const int b = blockIdx.y;
   const int HW = p.HW;
   const float* in = p.in + (size_t)b * 3 * HW;
@@ -694,6 +736,12 @@ __global__ void __launch_bounds__(BWD_THREADS, BWD_MIN_BLOCKS) bwd_tma_kernel(co
   if (threadIdx.x == 0)
     for (int it = 0; it < TMA_STAGES && it < n_my; ++it) issue(it);
   if (NC > 0) stage_curves<Op, true>(p, b, s_C, s_ab, nullptr, false);
+  constexpr bool MOM_TMEM = USE_TMEM && PARK_MOM && NC == LAYER_CURVES;
+  if constexpr (MOM_TMEM) {
+    const TmemSpill sp{tmem_base};
+    const F2 z[8] = {F2(0.0f), F2(0.0f), F2(0.0f), F2(0.0f), F2(0.0f), F2(0.0f), F2(0.0f), F2(0.0f)};
+    sp.mom_put6(0, z); sp.mom_put6(6, z); sp.mom_put8(z);
+  }
 
   using T = F2;
 #ifdef BWD_SCALAR_MOM
@@ -703,8 +751,10 @@ __global__ void __launch_bounds__(BWD_THREADS, BWD_MIN_BLOCKS) bwd_tma_kernel(co
   for (int k = 0; k < NM; ++k) mom[k] = 0.0f;
 #else
   T mom[NM > 0 ? NM : 1];
+  if constexpr (!MOM_TMEM) {
 #pragma unroll
-  for (int k = 0; k < NM; ++k) mom[k] = T(0.0f);
+    for (int k = 0; k < NM; ++k) mom[k] = T(0.0f);
+  }
 #endif
 
   // The mask plane is only 4-byte aligned in general, so it cannot ride the bulk copies; it is
@@ -800,6 +850,11 @@ __global__ void __launch_bounds__(BWD_THREADS, BWD_MIN_BLOCKS) bwd_tma_kernel(co
       }
     }   // sub-tiles
   }
+  if constexpr (MOM_TMEM) {      // the accumulators come back to registers for the reduction
+    const TmemSpill sp{tmem_base};
+    sp.before_loads();
+    sp.mom_get6(0, mom); sp.mom_get6(6, mom + 6); sp.mom_get8(mom + 12);
+  }
   if constexpr (USE_TMEM) {
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
@@ -810,6 +865,123 @@ __global__ void __launch_bounds__(BWD_THREADS, BWD_MIN_BLOCKS) bwd_tma_kernel(co
 #else
   if (NC > 0) finish_knot_grads<Op, T, BWD_THREADS>(p, b, mom, s_C, s_mom, s_part, &s_ticket);
 #endif
+}
+
+// ---------------------------------------------------------------------------------------------
+// Forward, aligned path, with the input planes streamed through a shared-memory ring by bulk async copies
+// (-DFWD_TMA).  The plain forward kernel leaves 22 % of its warp samples waiting for LDG data: a thread can
+// only have the loads of its own next pixels in flight if it holds them in registers, and a register prefetch
+// costs occupancy (forward experiments).  Here one elected thread keeps the next FWD_TMA_STAGES - 1
+// tiles of the block in flight at no register cost; the arithmetic and the 128-bit streaming stores are those
+// of fwd_kernel<Op, MK, 4>.
+// ---------------------------------------------------------------------------------------------
+#ifndef FWD_TMA_SUB
+#define FWD_TMA_SUB 2          // sub-tiles (4 pixels per thread each) per ring stage
+#endif
+#ifndef FWD_TMA_STAGES_N
+#define FWD_TMA_STAGES_N 2
+#endif
+#ifndef FWD_TMA_BLOCKS
+#define FWD_TMA_BLOCKS 9       // resident blocks per SM the grid is sized for (48 registers: 10 fit)
+#endif
+constexpr int FT_SUB_PX = THREADS * 4;
+constexpr int FT_TILE = FT_SUB_PX * FWD_TMA_SUB;
+constexpr int FT_STAGES = FWD_TMA_STAGES_N;
+constexpr size_t FT_RING_BYTES = (size_t)FT_STAGES * 3 * FT_TILE * sizeof(float);
+
+template <class Op, int MK>
+__global__ void __launch_bounds__(THREADS) fwd_tma_kernel(const KParams p) {
+  constexpr int NC = Op::NC;
+  extern __shared__ __align__(128) float s_ring[];   // [STAGES][3][TILE]
+  __shared__ __align__(8) unsigned long long s_full[FT_STAGES];
+  __shared__ float s_C[NC > 0 ? CURL_MAX_KNOTS : 1];
+  __shared__ float s_ab[NC > 0 ? 2 * NC : 1];
+  __shared__ double s_reg[NC > 0 ? NC : 1];
+  const int b = blockIdx.y;
+  const int HW = p.HW;
+  const float* in = p.in + (size_t)b * 3 * HW;
+  float* out = p.out + (size_t)b * 3 * HW;
+  const int n_tiles = (HW + FT_TILE - 1) / FT_TILE;
+  const int n_my = ((int)blockIdx.x < n_tiles) ? (n_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+
+  auto issue = [&](int it) {   // thread 0 only
+    const int s = it % FT_STAGES;
+    const int px0 = (blockIdx.x + it * gridDim.x) * FT_TILE;
+    const int n = min(FT_TILE, HW - px0);
+    const unsigned bytes = (unsigned)n * sizeof(float);
+    float* dst = s_ring + (size_t)s * 3 * FT_TILE;
+    mbar_expect_tx(&s_full[s], bytes * 3);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) bulk_g2s(dst + c * FT_TILE, in + (size_t)c * HW + px0, bytes, &s_full[s]);
+  };
+
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int s = 0; s < FT_STAGES; ++s) mbar_init(&s_full[s], 1);
+    mbar_fence_init();
+  }
+  // a partial last tile leaves the tail of its stage untouched: make that finite once (results there are not stored)
+  for (int i = threadIdx.x; i < (int)(FT_RING_BYTES / sizeof(float4)); i += THREADS)
+    reinterpret_cast<float4*>(s_ring)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  __syncthreads();
+  if (threadIdx.x == 0)
+    for (int it = 0; it < FT_STAGES && it < n_my; ++it) issue(it);
+  if (NC > 0) {
+    const bool owner = (blockIdx.x == 0) && (p.reg != nullptr);
+    stage_curves<Op, false>(p, b, s_C, s_ab, s_reg, owner);
+    if (owner && threadIdx.x == 0) {
+      double r = 0.0;
+      for (int j = 0; j < NC; ++j) r += s_reg[j];
+      p.reg[b] = (float)r;
+    }
+  }
+
+  using G = Group<4>;
+  using T = F2;
+  const int tile_stride = (int)gridDim.x * FT_TILE;
+  int px_tile = (int)blockIdx.x * FT_TILE + (int)threadIdx.x * 4;
+  int s = 0;
+  unsigned parity = 0u;
+#pragma unroll 1
+  for (int it = 0; it < n_my; ++it, px_tile += tile_stride) {
+    if (it > 0) {      // refill behind a barrier that follows the previous tile's arithmetic (see bwd_tma_kernel)
+      __syncthreads();
+      if (threadIdx.x == 0 && it - 1 + FT_STAGES < n_my) issue(it - 1 + FT_STAGES);
+    }
+    mbar_wait(&s_full[s], parity);
+    const float* stage = s_ring + (size_t)s * 3 * FT_TILE + threadIdx.x * 4;
+    if (++s == FT_STAGES) { s = 0; parity ^= 1u; }
+#ifdef FWD_TMA_UNROLL
+#pragma unroll
+#else
+#pragma unroll 1
+#endif
+    for (int q = 0; q < FWD_TMA_SUB; ++q) {
+      const int px = px_tile + q * FT_SUB_PX;
+      if (px < HW) {     // HW % 4 == 0: a thread's four pixels are inside or outside together
+        const float* src = stage + q * FT_SUB_PX;
+        const float4 a0 = *reinterpret_cast<const float4*>(src);
+        const float4 a1 = *reinterpret_cast<const float4*>(src + FT_TILE);
+        const float4 a2 = *reinterpret_cast<const float4*>(src + 2 * FT_TILE);
+        const G m = load_mask<MK, 4>(p.mask, (size_t)b * HW + px);
+        G o0, o1, o2;
+        {
+          const T x[3] = {F2(a0.x, a0.y), F2(a1.x, a1.y), F2(a2.x, a2.y)};
+          T y[3];
+          Op::template fwd<MK, T>(x, m.v[0], s_ab, p.aux, y);
+          o0.v[0] = y[0]; o1.v[0] = y[1]; o2.v[0] = y[2];
+        }
+        {
+          const T x[3] = {F2(a0.z, a0.w), F2(a1.z, a1.w), F2(a2.z, a2.w)};
+          T y[3];
+          Op::template fwd<MK, T>(x, m.v[1], s_ab, p.aux, y);
+          o0.v[1] = y[0]; o1.v[1] = y[1]; o2.v[1] = y[2];
+        }
+        o0.st(out + px); o1.st(out + HW + px); o2.st(out + 2 * (size_t)HW + px);
+      }
+    }
+  }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -851,8 +1023,30 @@ static bool aligned4(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 3
 
 static int check_launch() { return cudaGetLastError() == cudaSuccess ? CURL_OK : CURL_ERR_LAUNCH; }
 
+// Grid of the ring forward: whole waves of FWD_TMA_BLOCKS resident blocks per SM, like bwd_grid_x.
+static int fwd_tma_grid_x(int B, int HW) {
+  const long long tiles = ((long long)HW + FT_TILE - 1) / FT_TILE;
+  const int sms = sm_count();
+  constexpr int R = FWD_TMA_BLOCKS;
+  for (int w = 2 * R; w <= 6 * R; w += R) {
+    const long long total = (long long)sms * w;
+    if (total % B == 0 && total / B <= tiles) return apply_grid_cap(total / B);
+  }
+  long long cap = ((long long)sms * 2 * R + B - 1) / B;
+  long long n = tiles < cap ? tiles : cap;
+  return apply_grid_cap(n);
+}
+
 template <class Op, int MK>
 static int launch_fwd(const KParams& p, int B, bool vec4, cudaStream_t st) {
+#ifdef FWD_TMA
+  if (vec4 && Op::NC == LAYER_CURVES) {
+    if (!ensure_dyn_smem<fwd_tma_kernel<Op, MK>>(FT_RING_BYTES)) return CURL_ERR_LAUNCH;
+    dim3 grid(fwd_tma_grid_x(B, p.HW), B);
+    fwd_tma_kernel<Op, MK><<<grid, THREADS, FT_RING_BYTES, st>>>(p);
+    return check_launch();
+  }
+#endif
   const int vec = vec4 ? 4 : 1;
   dim3 grid(blocks_per_image(B, p.HW, vec, FWD_GRID_BLOCKS_PER_SM), B);
   if (vec4) fwd_kernel<Op, MK, 4><<<grid, THREADS, 0, st>>>(p);

@@ -611,6 +611,7 @@ CURL_HD void layer_fwd(const T x[3], T m, const float* ab, T out[3]) {
 // scalar tail path).
 struct KeepInRegisters {
   static constexpr bool kActive = false;
+  static constexpr bool kMomParked = false;
 };
 #ifndef CURL_PARK_STAGES
 #define CURL_PARK_STAGES 4         // how many of the first four stages' records are parked (6 slots each)
@@ -637,6 +638,32 @@ template <class T, class S> CURL_HD void spill_save(const S& sp, int o, const Se
 template <class T, class S> CURL_HD void spill_load(const S& sp, int o, Self3Jac<T>& j) {
   sp.get6(o, j.c[0].a, j.c[0].d, j.c[1].a, j.c[1].d, j.c[2].a, j.c[2].d);
 }
+
+// Split fetch: *_issue starts the fetch of a record (the destination registers are pending), *_wait makes them
+// readable.  Issued one stage ahead of its use, a fetch costs no stall (-DCURL_PARK_PREFETCH).
+template <class T, class S> CURL_HD void spill_load_issue(const S& sp, int o, LabJac<T>& j) {
+  sp.get6_issue(o, j.d_lin[0], j.d_lin[1], j.d_lin[2], j.d_f[0], j.d_f[1], j.d_f[2]);
+}
+template <class T, class S> CURL_HD void spill_load_wait(const S& sp, LabJac<T>& j) {
+  sp.get6_wait(j.d_lin[0], j.d_lin[1], j.d_lin[2], j.d_f[0], j.d_f[1], j.d_f[2]);
+}
+template <class T, class S> CURL_HD void spill_load_issue(const S& sp, int o, RgbJac<T>& j) {
+  sp.get6_issue(o, j.d_finv[0], j.d_finv[1], j.d_finv[2], j.d_gam[0], j.d_gam[1], j.d_gam[2]);
+}
+template <class T, class S> CURL_HD void spill_load_wait(const S& sp, RgbJac<T>& j) {
+  sp.get6_wait(j.d_finv[0], j.d_finv[1], j.d_finv[2], j.d_gam[0], j.d_gam[1], j.d_gam[2]);
+}
+template <class T, class S> CURL_HD void spill_load_issue(const S& sp, int o, Self3Jac<T>& j) {
+  sp.get6_issue(o, j.c[0].a, j.c[0].d, j.c[1].a, j.c[1].d, j.c[2].a, j.c[2].d);
+}
+template <class T, class S> CURL_HD void spill_load_wait(const S& sp, Self3Jac<T>& j) {
+  sp.get6_wait(j.c[0].a, j.c[0].d, j.c[1].a, j.c[1].d, j.c[2].a, j.c[2].d);
+}
+#ifdef CURL_PARK_PREFETCH
+constexpr bool PARK_PREFETCH = true;
+#else
+constexpr bool PARK_PREFETCH = false;
+#endif
 
 // RGB -> HSV record (tensor-memory parking only, -DCURL_PARK_J5): the 13 values the fused layer uses (no pin).
 #ifdef CURL_PARK_J5
@@ -705,20 +732,32 @@ CURL_HD void layer_bwd(const T x[3], T m, const float* ab, const T gout[3], T gx
   T a[3], b[3];
   if (MK == MASK_F32) hsv2rgb_bwd<T, false, true>(j7, g, a); else hsv2rgb_bwd<T, true, true>(j7, g, a);
   if (MK == MASK_F32) vscale3(a, m);
+  if constexpr (SPILL::kMomParked) sp.mom_get8(mom + 12);      // the HSV group's 8 accumulators
   adjust_hsv_bwd(j6, ab[2 * LAYER_CURVES], a, b, mom + 12);
+  if constexpr (SPILL::kMomParked) sp.mom_put8(mom + 12);
   if constexpr (kSpill) sp.before_loads();       // parked records are about to be read back
   if constexpr (kSpill && PARK_J5 && UNIT) spill_load<T>(sp, J5_SLOT, j5);
+  constexpr bool PF = kSpill && PARK_PREFETCH && PARK_STAGES == 4;      // fetch every record one stage ahead of its use
+  if constexpr (PF) spill_load_issue<T>(sp, 18, j4);
   rgb2hsv_bwd<T, UNIT>(j5, b, a);
   if (MK == MASK_F32) vscale3(a, m);
-  if constexpr (kSpill && PARK_STAGES >= 4) spill_load<T>(sp, 18, j4);
+  if constexpr (PF) { spill_load_wait<T>(sp, j4); spill_load_issue<T>(sp, 12, j3); }
+  else if constexpr (kSpill && PARK_STAGES >= 4) spill_load<T>(sp, 18, j4);
+  if constexpr (SPILL::kMomParked) sp.mom_get6(6, mom + 6);
   adjust_self3_bwd(j4, a, b, mom + 6);
-  if constexpr (kSpill && PARK_STAGES >= 3) spill_load<T>(sp, 12, j3);
+  if constexpr (SPILL::kMomParked) sp.mom_put6(6, mom + 6);
+  if constexpr (PF) { spill_load_wait<T>(sp, j3); spill_load_issue<T>(sp, 6, j2); }
+  else if constexpr (kSpill && PARK_STAGES >= 3) spill_load<T>(sp, 12, j3);
   lab2rgb_bwd<T, true>(j3, b, a);
   if (MK == MASK_F32) vscale3(a, m);
-  if constexpr (kSpill && PARK_STAGES >= 2) spill_load<T>(sp, 6, j2);
+  if constexpr (PF) { spill_load_wait<T>(sp, j2); if (WANT_GX) spill_load_issue<T>(sp, 0, j1); }
+  else if constexpr (kSpill && PARK_STAGES >= 2) spill_load<T>(sp, 6, j2);
+  if constexpr (SPILL::kMomParked) sp.mom_get6(0, mom + 0);
   adjust_self3_bwd(j2, a, b, mom + 0);
+  if constexpr (SPILL::kMomParked) sp.mom_put6(0, mom + 0);
   if (WANT_GX) {
-    if constexpr (kSpill && PARK_STAGES >= 1) spill_load<T>(sp, 0, j1);
+    if constexpr (PF) spill_load_wait<T>(sp, j1);
+    else if constexpr (kSpill && PARK_STAGES >= 1) spill_load<T>(sp, 0, j1);
     rgb2lab_bwd<T, true>(j1, b, a);
     gx[0] = vadd(g[0], a[0]); gx[1] = vadd(g[1], a[1]); gx[2] = vadd(g[2], a[2]);
   }
