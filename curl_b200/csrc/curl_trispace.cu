@@ -16,11 +16,15 @@
 namespace curl {
 namespace tri {
 
+// Forward launch shape: 128 threads x 3 blocks per SM (164 registers, NO spills).  Round 1 shipped 256 x 2, whose
+// 128-register cap spilled 28-112 bytes per thread; measured on B200 (ms, 512^2 x 32 / 4K x 8):
+//   126 coefficients: 256x2 0.433 / 3.174, 128x3 0.430 / 3.171, 128x2 0.429 / 3.171, 256x1 (no cap) 0.496 / 3.341
+//    35 coefficients: 256x2 0.187 / 1.254, 128x3 0.175 / 1.253, 128x2 0.193 / 1.382, 256x1 0.235 / 1.534
 #ifndef TRI_FWD_THREADS
-#define TRI_FWD_THREADS 256
+#define TRI_FWD_THREADS 128
 #endif
 #ifndef TRI_FWD_MIN_BLOCKS
-#define TRI_FWD_MIN_BLOCKS 2
+#define TRI_FWD_MIN_BLOCKS 3
 #endif
 constexpr int THREADS = TRI_FWD_THREADS;
 constexpr int DEG = 4;                       // the reference's polynomial_order default (model.py:413)
@@ -42,11 +46,17 @@ struct TParams {
 using host::sm_count;
 
 // coefficients of image b -> shared memory as [space][monomial] Coef4 records {c0, c1, c2, 0}
+// (the space index is a compile-time constant: indexing p.coef[] with a run-time value made the compiler copy
+// the whole parameter block to local memory -- a 112-byte stack frame in every kernel of this file)
 template <int NC>
 __device__ __forceinline__ void stage_coef(const TParams& p, int b, Coef4* s_coef) {
-  for (int i = threadIdx.x; i < 3 * NC * 4; i += blockDim.x) {
-    const int s = i / (4 * NC), r = i - s * 4 * NC, k = r >> 2, c = r & 3;
-    s_coef[s * NC + k].v[c] = c < 3 ? p.coef[s][((size_t)b * 3 + c) * NC + k] : 0.0f;
+#pragma unroll
+  for (int s = 0; s < 3; ++s) {
+    const float* src = p.coef[s] + (size_t)b * 3 * NC;
+    for (int r = threadIdx.x; r < NC * 4; r += blockDim.x) {
+      const int k = r >> 2, c = r & 3;
+      s_coef[s * NC + k].v[c] = c < 3 ? src[c * NC + k] : 0.0f;
+    }
   }
   __syncthreads();
 }
@@ -306,7 +316,8 @@ __global__ void __launch_bounds__(BT, TRI_BWD_MIN_BLOCKS) trispace_bwd_kernel(co
     double a = 0.0;
     for (unsigned r = 0; r < gridDim.x; ++r) a += (double)__ldcg(rows + (size_t)r * NG + k);
     const int s = k / (3 * NC), j = k - s * 3 * NC;
-    p.gcoef[s][(size_t)b * 3 * NC + j] = (float)a;
+    float* dst = s == 0 ? p.gcoef[0] : (s == 1 ? p.gcoef[1] : p.gcoef[2]);   // no run-time index into the parameter block
+    dst[(size_t)b * 3 * NC + j] = (float)a;
   }
 }
 

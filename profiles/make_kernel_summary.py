@@ -1,4 +1,4 @@
-# builds one profiles/r01_ncu_<name>.md from a gpurun_out/*.ncu-rep -- run on the CPU box:
+# builds one profiles/<round>_ncu_<name>.md (round from $ROUND, default r02) from a gpurun_out/*.ncu-rep -- run on the CPU box:
 #   python profiles/make_kernel_summary.py <report> <name> <pixels per launch> <algorithmic B/px> "<command>"
 import csv, subprocess, sys, os
 rep, name, px, alg, cmd = sys.argv[1], sys.argv[2], float(sys.argv[3]), sys.argv[4], sys.argv[5]
@@ -8,13 +8,15 @@ want = ['gpu__time_duration.sum', 'dram__bytes_read.sum', 'dram__bytes_write.sum
         'sm__inst_issued.avg.per_cycle_active', 'sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active',
         'sm__pipe_fmaheavy_cycles_active.avg.pct_of_peak_sustained_elapsed', 'sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active',
         'sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active', 'sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active',
+        'sm__inst_executed_pipe_tmem.avg.pct_of_peak_sustained_active', 'launch__occupancy_limit_registers', 'launch__occupancy_limit_shared_mem',
         'l1tex__data_pipe_lsu_wavefronts_mem_shared.sum', 'l1tex__data_pipe_lsu_wavefronts_mem_shared.sum.pct_of_peak_sustained_elapsed',
         'l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum', 'sm__throughput.avg.pct_of_peak_sustained_elapsed',
         'smsp__average_warp_latency_per_inst_issued.ratio', 'sm__cycles_elapsed.max']
 o = subprocess.run(['ncu', '-i', rep, '--page', 'raw', '--csv'], capture_output=True, text=True).stdout
 rr = list(csv.reader(o.splitlines())); h, u, v = rr[0], rr[1], rr[2]
 d = dict(zip(h, zip(u, v)))
-L = ['# Round 1 -- ncu --set full, `%s`' % d['Kernel Name'][1], '',
+RND = os.environ.get('ROUND', 'r02')
+L = ['# %s -- ncu --set full, `%s`' % (RND, d['Kernel Name'][1]), '',
      '`%s` (%.2f Mpx per launch), --clock-control none. Raw report: %s (scratch).' % (cmd, px / 1e6, rep), '',
      '| metric | value | unit |', '|---|---|---|']
 for w in want:
@@ -35,5 +37,5 @@ k = 'l1tex__data_pipe_lsu_wavefronts_mem_shared.sum'
 if k in d:
     line += '; %.1f shared-memory wavefronts per pixel' % (float(d[k][1].replace(',', '')) / px)
 L += ['', line + '.']
-open(os.path.join(os.path.dirname(os.path.abspath(__file__)), 'r01_ncu_%s.md' % name), 'w').write('\n'.join(L) + '\n')
+open(os.path.join(os.path.dirname(os.path.abspath(__file__)), '%s_ncu_%s.md' % (RND, name)), 'w').write('\n'.join(L) + '\n')
 print('\n'.join(L))
