@@ -1136,6 +1136,8 @@ const char* curl_strerror(int code) {
     case CURL_ERR_WORKSPACE: return "workspace missing, misaligned or too small (see curl_bwd_workspace_bytes)";
     case CURL_ERR_LAUNCH: return "CUDA launch failed";
     case CURL_ERR_MISALIGNED: return "pointer not 4-byte aligned";
+    case CURL_ERR_TOO_LARGE: return "shape needs more scratch than the allocation-free entry point's fixed 1 MiB array "
+                                    "(CURL_NOALLOC_SCRATCH_BYTES); use curl_layer_bwd_f32 with a caller-supplied workspace";
     default: return "unknown error";
   }
 }
@@ -1396,3 +1398,56 @@ int curl_apply_curve_bwd_f32(const float* in, const float* C, int64_t ldC, int c
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// Allocation-free variant of curl_layer_bwd_f32 (no counterpart in the reference; added
+// for callers that cannot allocate: code under CUDA-graph capture, tight serving loops, harnesses
+// that forbid cudaMalloc).  The backward's scratch -- per-image tickets + per-block moment partials, what
+// curl_bwd_workspace_bytes() sizes -- lives in a file-scope device array instead of a caller-supplied workspace.
+//   * every GPU that loads the library holds CURL_NOALLOC_SCRATCH_BYTES (1 MiB) until the process exits;
+//   * shapes whose workspace exceeds that are rejected with CURL_ERR_TOO_LARGE before anything is launched;
+//   * every call shares the ONE array, which keeps the previous call's contents: the tickets (the only part that
+//     must start at zero) are cleared by the memset node launch_bwd enqueues; the partial rows are fully
+//     overwritten before they are read.  Two calls that overlap on the GPU (different streams, or one stream per
+//     host thread) RACE on it -- serialise them, or use curl_layer_bwd_f32 with one workspace per stream;
+//   * calls no cudaMalloc / cudaFree / allocating library routine.  In host code the array's name is only a
+//     stand-in for the symbol, not a device address: its address is looked up once per device, with that
+//     device current, by cudaGetSymbolAddress and handed to the kernel through the same KParams as a workspace.
+// ---------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_noalloc_scratch[CURL_NOALLOC_SCRATCH_BYTES];
+
+static void* noalloc_scratch_address() {
+  static void* cached[host::MAX_DEVICES] = {nullptr};
+  const int dev = host::current_device();
+  if (dev < 0) return nullptr;
+  if (cached[dev] == nullptr) {
+    void* ptr = nullptr;
+    if (cudaGetSymbolAddress(&ptr, g_noalloc_scratch) != cudaSuccess || ptr == nullptr) return nullptr;
+    cached[dev] = ptr;
+  }
+  return cached[dev];
+}
+
+extern "C" int curl_layer_bwd_noalloc_f32(const float* img, const void* mask, int mask_kind, const float* L, int64_t ldL,
+                                          const float* R, int64_t ldR, const float* Hk, int64_t ldH, const float* gout,
+                                          const float* greg, float* gimg, float* gL, float* gR, float* gH, int B, int H,
+                                          int W, int K_lab, int K_rgb, int K_hsv, void* stream) {
+  KParams p;
+  int rc = layer_params(p, img, mask, mask_kind, L, ldL, R, ldR, Hk, ldH, B, H, W, K_lab, K_rgb, K_hsv);
+  if (rc != CURL_OK) return rc;
+  if (!gout || !gL || !gR || !gH) return CURL_ERR_BAD_ARG;
+  if (!aligned4(gout) || (gimg && !aligned4(gimg))) return CURL_ERR_MISALIGNED;
+  const size_t need = curl_bwd_workspace_bytes(B, H, W);
+  if (need == 0 || need > (size_t)CURL_NOALLOC_SCRATCH_BYTES) return CURL_ERR_TOO_LARGE;
+  void* scratch = noalloc_scratch_address();
+  if (scratch == nullptr) return CURL_ERR_LAUNCH;
+  p.gout = gout; p.greg = greg; p.out = gimg;
+  p.seg[0].g = gL; p.seg[1].g = gR; p.seg[2].g = gH;
+  const bool v4 = can_vec4(p, mask_kind);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  switch (mask_kind) {
+    case CURL_MASK_NONE: return launch_bwd<OpLayer, MASK_NONE>(p, B, v4, scratch, CURL_NOALLOC_SCRATCH_BYTES, st);
+    case CURL_MASK_U8: return launch_bwd<OpLayer, MASK_U8>(p, B, v4, scratch, CURL_NOALLOC_SCRATCH_BYTES, st);
+    default: return launch_bwd<OpLayer, MASK_F32>(p, B, v4, scratch, CURL_NOALLOC_SCRATCH_BYTES, st);
+  }
+}

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define CURL_ABI_VERSION 8
+#define CURL_ABI_VERSION 9
 
 /* error codes */
 #define CURL_OK 0
@@ -35,6 +35,7 @@ extern "C" {
 #define CURL_ERR_WORKSPACE (-3)      /* workspace missing or too small */
 #define CURL_ERR_LAUNCH (-4)         /* cudaGetLastError() after the launch was not cudaSuccess */
 #define CURL_ERR_MISALIGNED (-5)     /* a base pointer is not 4-byte aligned */
+#define CURL_ERR_TOO_LARGE (-6)      /* curl_layer_bwd_noalloc_f32: shape needs more than CURL_NOALLOC_SCRATCH_BYTES */
 
 #define CURL_MAX_KNOTS 1024
 
@@ -122,6 +123,27 @@ int curl_layer_fwd_u8(const uint8_t* img, int in_layout, const void* mask, int m
 
 /* Bytes of device workspace the two *_bwd_f32 entry points need for this shape (host-only call). */
 size_t curl_bwd_workspace_bytes(int B, int H, int W);
+
+/*
+ * Allocation-free variant of curl_layer_bwd_f32.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate device memory (code under CUDA-graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  Same arguments, semantics and results as curl_layer_bwd_f32 minus
+ * the workspace: the scratch (tickets + per-block moment partials) is a file-scope device array of
+ * CURL_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until the process exits.
+ *   - shapes with curl_bwd_workspace_bytes(B, H, W) > CURL_NOALLOC_SCRATCH_BYTES return CURL_ERR_TOO_LARGE
+ *     (nothing is launched); every BASELINE shape fits (4K x 64: 0.57 MB);
+ *   - calls no cudaMalloc / cudaFree / allocating routine; the first call on a device looks the array's address
+ *     up once (cudaGetSymbolAddress);
+ *   - ALL calls share the one array: calls that overlap on the GPU (different streams) race on it.  Serialise
+ *     them, or use curl_layer_bwd_f32 with a workspace per stream.  What must start at zero is cleared per call.
+ */
+#define CURL_NOALLOC_SCRATCH_BYTES (1 << 20)
+int curl_layer_bwd_noalloc_f32(const float* img, const void* mask, int mask_kind,
+                               const float* L, int64_t ldL, const float* R, int64_t ldR,
+                               const float* Hk, int64_t ldH,
+                               const float* gout, const float* greg,
+                               float* gimg, float* gL, float* gR, float* gH,
+                               int B, int H, int W, int K_lab, int K_rgb, int K_hsv, void* stream);
 
 /* Stand-alone colour conversion, forward.  Replaces colors.<Module>.forward(img). */
 int curl_color_fwd_f32(int conversion, const float* in, float* out, int B, int H, int W, void* stream);
