@@ -291,6 +291,44 @@ __global__ void FWD_BOUNDS fwd_kernel(const KParams p) {
   const int stride = gridDim.x * THREADS * VEC;
   using G = Group<VEC>;
   using T = typename G::T;
+#ifdef FWD_PREFETCH
+  if constexpr (VEC == 4 && Op::NC == LAYER_CURVES) {
+    // The next group's loads are issued between the two lanes' arithmetic (pinned there by the fences: left alone
+    // the compiler hoists them to the top of the iteration, where they are live across the whole chain and cost
+    // occupancy -- the round-1 prefetch).  They are in flight for half an iteration of every resident warp.
+    int i = (blockIdx.x * THREADS + threadIdx.x) * VEC;
+    if (i >= HW) return;
+    G c0 = G::ld(in + i), c1 = G::ld(in + HW + i), c2 = G::ld(in + 2 * (size_t)HW + i);
+    G m = load_mask<MK, VEC>(p.mask, (size_t)b * HW + i);
+    while (true) {
+      G o0, o1, o2, n0, n1, n2, nm;
+      {
+        const T x[3] = {c0.v[0], c1.v[0], c2.v[0]};
+        T y[3];
+        Op::template fwd<MK, T>(x, m.v[0], s_ab, p.aux, y);
+        o0.v[0] = y[0]; o1.v[0] = y[1]; o2.v[0] = y[2];
+      }
+      const int inext = i + stride;
+      const bool more = inext < HW;
+      asm volatile("" ::: "memory");
+      if (more) {
+        n0 = G::ld(in + inext); n1 = G::ld(in + HW + inext); n2 = G::ld(in + 2 * (size_t)HW + inext);
+        nm = load_mask<MK, VEC>(p.mask, (size_t)b * HW + inext);
+      }
+      asm volatile("" ::: "memory");
+      {
+        const T x[3] = {c0.v[1], c1.v[1], c2.v[1]};
+        T y[3];
+        Op::template fwd<MK, T>(x, m.v[1], s_ab, p.aux, y);
+        o0.v[1] = y[0]; o1.v[1] = y[1]; o2.v[1] = y[2];
+      }
+      o0.st(out + i); o1.st(out + HW + i); o2.st(out + 2 * (size_t)HW + i);
+      if (!more) break;
+      c0 = n0; c1 = n1; c2 = n2; m = nm; i = inext;
+    }
+    return;
+  }
+#endif
   for (int i = (blockIdx.x * THREADS + threadIdx.x) * VEC; i < HW; i += stride) {
     const G c0 = G::ld(in + i), c1 = G::ld(in + HW + i), c2 = G::ld(in + 2 * (size_t)HW + i);
     const G m = load_mask<MK, VEC>(p.mask, (size_t)b * HW + i);

@@ -134,15 +134,31 @@ struct LabJac {
   T d_f[3];    // 3 (d f_k / d t_k)
 };
 
-template <class T, bool JAC>
+// DIRECT (forward-only callers; requires !JAC): the powers are taken as 2^(p lg x) in one step instead of the
+// x * 2^((p - 1) lg x) form that shares its LG2 + EX2 with the derivative -- one packed multiply fewer per channel,
+// and for the cube root (|p| 1/3 instead of 2/3) a smaller amplification of the LG2 error.  The sRGB power keeps
+// direct form too unless CURL_FWD_SHARED_SRGB is defined: 2.4 instead of 0.4 amplifies the LG2 error six times, but
+// the shared form pays two more roundings, and measured against the fp64 oracle the direct one is no worse.
+#ifdef CURL_FWD_SHARED_SRGB
+constexpr bool FWD_DIRECT_SRGB = false;
+#else
+constexpr bool FWD_DIRECT_SRGB = true;     // measured (dev/fwd_accuracy.py): mean |err| vs fp64 1.21e-7 (shared form 1.23e-7), 2.5 % faster
+#endif
+template <class T, bool JAC, bool DIRECT = false>
 CURL_HD void rgb2lab_fwd(const T x[3], T lab[3], LabJac<T>* jac) {
+  static_assert(!(JAC && DIRECT), "the derivative records need the shared form");
   T lin[3];
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
     // colors.py:37-38.  In the pow branch x > 0.04045 so the reference's clamp(min=1e-4) is inert.
     const T u = vfma(x[c], T(k::SRGB_A), T(k::SRGB_B));
-    const T u14 = vmul(u, vex2(vmul(vlg2(u), T(0.4f))));
-    const T hi = vmul(u, u14);
+    T u14, hi;
+    if (DIRECT && FWD_DIRECT_SRGB) {
+      hi = vex2(vmul(vlg2(u), T(2.4f)));
+    } else {
+      u14 = vmul(u, vex2(vmul(vlg2(u), T(0.4f))));
+      hi = vmul(u, u14);
+    }
     lin[c] = vsel_le(x[c], T(k::SRGB_T), vmul(x[c], T(k::SRGB_INV_SLOPE)), hi);
     if (JAC) jac->d_lin[c] = vsel_le(x[c], T(k::SRGB_T), T(k::SRGB_INV_SLOPE_BY_DK), u14);   // (d lin / d x) / SRGB_DK
   }
@@ -150,14 +166,25 @@ CURL_HD void rgb2lab_fwd(const T x[3], T lab[3], LabJac<T>* jac) {
   t[0] = vfma(lin[2], T(k::M20), vfma(lin[1], T(k::M10), vmul(lin[0], T(k::M00))));  // colors.py:40-41
   t[1] = vfma(lin[2], T(k::M21), vfma(lin[1], T(k::M11), vmul(lin[0], T(k::M01))));
   t[2] = vfma(lin[2], T(k::M22), vfma(lin[1], T(k::M12), vmul(lin[0], T(k::M02))));
-  T f[3];
+  T f[3], ef[3];
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
-    // colors.py:45-47.  In the cube-root branch t > eps^3 > 1e-4 so the clamp is inert.
-    const T e = vex2(vmul(vlg2(t[c]), T((float)(-2.0 / 3.0))));   // t^(-2/3)
-    const T cr = vmul(t[c], e);
-    f[c] = vsel_le(t[c], T(k::F_T), vfma(t[c], T(k::F_SLOPE), T(k::F_OFF)), cr);
-    if (JAC) jac->d_f[c] = vsel_le(t[c], T(k::F_T), T(k::F_SLOPE_X3), e);                      // 3 (d f / d t)
+    // colors.py:45-47, cube-root branch.  There t > eps^3 > 1e-4 so the reference's clamp is inert.
+    if (DIRECT) {
+      f[c] = vex2(vmul(vlg2(t[c]), T((float)(1.0 / 3.0))));         // t^(1/3)
+    } else {
+      ef[c] = vex2(vmul(vlg2(t[c]), T((float)(-2.0 / 3.0))));       // t^(-2/3)
+      f[c] = vmul(t[c], ef[c]);
+    }
+    if (JAC) jac->d_f[c] = ef[c];                                    // 3 (d f / d t)
+  }
+  // ... and the linear branch t <= eps^3.  (Skipping these selects for warps in which no pixel needs them -- a vote
+  // on min(X, Y, Z) <= eps^3 -- was measured slower, 4K x 16 backward 1.806 -> 1.845 ms, forward 0.774 -> 0.783: on
+  // uniform inputs 2.5 % of the pixels have a Z that small, i.e. 80 % of the warps take the branch anyway.)
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    f[c] = vsel_le(t[c], T(k::F_T), vfma(t[c], T(k::F_SLOPE), T(k::F_OFF)), f[c]);
+    if (JAC) jac->d_f[c] = vsel_le(t[c], T(k::F_T), T(k::F_SLOPE_X3), ef[c]);
   }
   // colors.py:50,57: (116 fy - 16) / 100 = 1.16 (fy - 4/29).  Written as a difference first so that a black
   // pixel (fy == 4/29 exactly) gives L == 0 exactly, as the reference's separately rounded 116 fy - 16 does: L = 0
@@ -199,19 +226,26 @@ struct RgbJac {
   T d_gam[3];   // (d rgb_c / d v_c) / GAM_DK
 };
 
-template <class T, bool JAC>
+template <class T, bool JAC, bool DIRECT = false>
 CURL_HD void lab2rgb_fwd(const T lab[3], T rgb[3], RgbJac<T>* jac) {
+  static_assert(!(JAC && DIRECT), "the derivative records need the shared form");
   T f[3];
   f[1] = vfma(lab[0], T(k::FY_S), T(k::FY_O));                    // colors.py:97,104
   f[0] = vfma(lab[1], T(k::FX_S), vadd(f[1], T(k::FX_O)));        // colors.py:98,104
   f[2] = vfma(lab[2], T(k::FZ_S), vadd(f[1], T(k::FZ_O)));        // colors.py:99,104
-  T xyz[3];
+  T xyz[3], sq[3];
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
-    // colors.py:110-111.  In the cube branch f > eps > 1e-4 so the clamp is inert.
-    const T sq = vmul(f[c], f[c]);
-    xyz[c] = vsel_le(f[c], T(k::FINV_T), vfma(f[c], T(k::FINV_SLOPE), T(k::FINV_OFF)), vmul(sq, f[c]));
-    if (JAC) jac->d_finv[c] = vsel_le(f[c], T(k::FINV_T), T(k::FINV_SLOPE_BY3), sq);             // (d finv / d f) / 3
+    // colors.py:110-111, cube branch.  There f > eps > 1e-4 so the clamp is inert.
+    sq[c] = vmul(f[c], f[c]);
+    xyz[c] = vmul(sq[c], f[c]);
+    if (JAC) jac->d_finv[c] = sq[c];                                // (d finv / d f) / 3
+  }
+  // ... and the linear branch f <= eps
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    xyz[c] = vsel_le(f[c], T(k::FINV_T), vfma(f[c], T(k::FINV_SLOPE), T(k::FINV_OFF)), xyz[c]);
+    if (JAC) jac->d_finv[c] = vsel_le(f[c], T(k::FINV_T), T(k::FINV_SLOPE_BY3), sq[c]);
   }
   T v[3];
   v[0] = vfma(xyz[2], T(k::N20), vfma(xyz[1], T(k::N10), vmul(xyz[0], T(k::N00))));  // colors.py:114,117
@@ -220,8 +254,14 @@ CURL_HD void lab2rgb_fwd(const T lab[3], T rgb[3], RgbJac<T>* jac) {
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
     // colors.py:118-119.  In the pow branch v > 0.0031308 > 1e-4 so the clamp is inert.
-    const T e = vex2(vmul(vlg2(v[c]), T(k::GAM_E)));               // v^(1/2.4 - 1)
-    const T hi = vfma(vmul(v[c], e), T(1.055f), T(-0.055f));
+    T e, pw;
+    if (DIRECT) {
+      pw = vex2(vmul(vlg2(v[c]), T((float)(1.0 / 2.4))));          // v^(1/2.4)
+    } else {
+      e = vex2(vmul(vlg2(v[c]), T(k::GAM_E)));                     // v^(1/2.4 - 1)
+      pw = vmul(v[c], e);
+    }
+    const T hi = vfma(pw, T(1.055f), T(-0.055f));
     rgb[c] = vsel_le(v[c], T(k::LIN_T), vmul(v[c], T(k::LIN_SLOPE)), hi);
     if (JAC) jac->d_gam[c] = vsel_le(v[c], T(k::LIN_T), T(k::LIN_SLOPE_BY_DK), e);               // (d rgb / d v) / GAM_DK
   }
@@ -281,7 +321,10 @@ CURL_HD void rgb2hsv_fwd(const T x[3], T hsv[3], HsvJac<T>* jac) {
   // (colors.py:186-193) and 1/mx must stay exact: dfc r = 1/mx either way.
   const T dfc = vmax(df, T(1e-20f));
   const T rr = vrcp(vmul(dfc, mx));
-  const T dinv = vsel_eq(df, T(0.0f), T(0.0f), vmul(mx, rr));  // colors.py:186-193,220
+  // colors.py:186-193,220: 1/df := 0 on grey pixels.  The forward needs no select for it: there all three channel
+  // differences are exactly 0, mx rr = 1e20 is finite, so every d * dinv term is an exact 0 either way, and the sum
+  // is multiplied by the [df != 0] gate below (colors.py:221, the `where`).  Only the derivative record needs the 0.
+  const T dinv = JAC ? vsel_eq(df, T(0.0f), T(0.0f), vmul(mx, rr)) : vmul(mx, rr);
   const T nz = vgate_ne(df, T(0.0f));
   const T s0 = vgate_eq(xc[0], mx), s1 = vgate_eq(xc[1], mx), s2 = vgate_eq(xc[2], mx);
   const T d12 = vsub(xc[1], xc[2]), d20 = vsub(xc[2], xc[0]), d01 = vsub(xc[0], xc[1]);
@@ -295,7 +338,9 @@ CURL_HD void rgb2hsv_fwd(const T x[3], T hsv[3], HsvJac<T>* jac) {
   const T minv = vmul(dfc, rr);                                // colors.py:234 (mx >= 1e-9, never 0)
   const T s = vmul(df, minv);                                  // colors.py:235-237
   // colors.py:240
-  hsv[0] = vmin(vmax(h, T(k::HSV_LO)), T(1.0f));
+  // (the upper bound of the hue clamp is inert: hr <= 5 gives h <= 5/6, and a negative hr gives fl(1 + hr/6) <= 1)
+  // (the derivative path keeps the inert min so that the backward kernels' code is unchanged)
+  hsv[0] = JAC ? vmin(vmax(h, T(k::HSV_LO)), T(1.0f)) : vmax(h, T(k::HSV_LO));
   hsv[1] = vmin(vmax(s, T(k::HSV_LO)), T(1.0f));
   hsv[2] = mx;  // already inside [1e-9, 1]
   if (JAC) {
@@ -582,10 +627,10 @@ CURL_HD void vscale3(T a[3], T m) { a[0] = vmul(a[0], m); a[1] = vmul(a[1], m); 
 template <class T, int MK>
 CURL_HD void layer_fwd(const T x[3], T m, const float* ab, T out[3]) {
   T lab[3], lab2[3], rgb[3], rgb2[3], hsv[3], hsv2[3], res[3];
-  rgb2lab_fwd<T, false>(x, lab, nullptr);
+  rgb2lab_fwd<T, false, true>(x, lab, nullptr);
   adjust_self3_fwd<T, false>(lab, ab, lab2, nullptr);
   if (MK == MASK_F32) vscale3(lab2, m);
-  lab2rgb_fwd<T, false>(lab2, rgb, nullptr);
+  lab2rgb_fwd<T, false, true>(lab2, rgb, nullptr);
   adjust_self3_fwd<T, false>(rgb, ab + 6, rgb2, nullptr);
   if (MK == MASK_F32) vscale3(rgb2, m);
   rgb2hsv_fwd<T, false, MK != MASK_F32>(rgb2, hsv, nullptr);

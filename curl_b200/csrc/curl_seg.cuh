@@ -79,11 +79,11 @@ CURL_HD int seg_cout(int k) { return k < 6 ? k % 3 : (k == 6 ? 0 : (k == 7 ? 1 :
 template <int MK>
 CURL_HD void seg_layer_fwd(const float x[3], float m, const SegCurve cv[LAYER_CURVES], float out[3]) {
   float a[3], b[3];
-  rgb2lab_fwd<float, false>(x, a, nullptr);
+  rgb2lab_fwd<float, false, true>(x, a, nullptr);
 #pragma unroll
   for (int k = 0; k < 3; ++k) { seg_apply_fwd<false>(cv[k], a, seg_cin(k), seg_cout(k), b, nullptr); a[0] = b[0]; a[1] = b[1]; a[2] = b[2]; }
   if (MK == MASK_F32) vscale3(a, m);
-  lab2rgb_fwd<float, false>(a, b, nullptr);
+  lab2rgb_fwd<float, false, true>(a, b, nullptr);
 #pragma unroll
   for (int k = 3; k < 6; ++k) { seg_apply_fwd<false>(cv[k], b, seg_cin(k), seg_cout(k), a, nullptr); b[0] = a[0]; b[1] = a[1]; b[2] = a[2]; }
   if (MK == MASK_F32) vscale3(b, m);
