@@ -64,8 +64,8 @@ def test_layer_vs_golden(case, layer_golden):
     rep["gimg"] = parity.check_image(case, ours["gimg"], r32["gimg"], r64["gimg"], scale=gscale, tol=parity.GRAD_TOL)
     for k in ("gL", "gR", "gH"):
         assert ours[k].shape == r32[k].shape
-        if case == "identity":
-            continue  # every pixel of this case sits on a tie/clamp bound; see parity.py
+        # ('identity': every pixel sits on a tie / clamp bound and the reference's own fp32 and fp64 gradients differ
+        # by 3 % of the max-norm; judged, like the other edge cases, by fp64 triangulation -- parity.check_knots)
         rep[k] = parity.check_knots(case, ours[k], r32[k], r64[k])
     # element-wise against the reference's fp32 run: pixels on exact boundaries (black, white, grey) must take
     # the reference's side.  Genuine ties that rounding decides are bounded by the reference's own
