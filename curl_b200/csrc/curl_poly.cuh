@@ -129,38 +129,41 @@ CURL_HD T vsigmoid(T p) {
 // NV = 3 (spatial=False) or 5 (spatial=True: x = column / width, y = row / height appended, model.py:472-484).
 // coef: [space R, L, H][NC] Coef4 records.
 // ------------------------------------------------------------------------------------------------
-// sig (nullable): receives the nine sigmoid outputs [space][channel], which is all the backward needs
-// besides the image to skip re-evaluating the three polynomials.
-template <class T, int NV, int DEG>
-CURL_HD void trispace_fwd(const T rgb[3], T xs, T ys, const Coef4* coef, bool clamp, T out[3], T* sig = nullptr) {
+// sink(space, channel, value) receives the nine sigmoid outputs, which is all the backward needs besides the
+// image to skip re-evaluating the three polynomials (the forward kernel stores them as they appear).
+// ROLLED: the loop over the three spaces is NOT unrolled on the device.  Fully unrolled, ptxas schedules the spaces'
+// coefficient loads and colour conversions across each other; that overlap is worth 5-14 % where the registers
+// hold it, but the 126-coefficient forward WITHOUT stores of the sigmoids in between (the inference path) then
+// spills 132-224 bytes per thread whatever its register cap (4K x 8: 4.38 ms; rolled 3.33 ms, no spills, and the
+// polynomial code exists once).  Same operations in the same order either way: bit-identical results.
+struct NoSigSink { template <class T> CURL_HD void operator()(int, int, T) const {} };
+template <class T, int NV, int DEG, bool ROLLED = false, class Sink = NoSigSink>
+CURL_HD void trispace_fwd(const T rgb[3], T xs, T ys, const Coef4* coef, bool clamp, T out[3], Sink sink = Sink()) {
   constexpr int NC = poly_num_coeffs(NV, DEG);
-  T v[5], p[3], s[3], r[3], res[3];
-  v[3] = xs; v[4] = ys;
-  v[0] = rgb[0]; v[1] = rgb[1]; v[2] = rgb[2];
-  poly_eval<T, NV, DEG>(v, coef, p);
+  T res[3] = {T(0.0f), T(0.0f), T(0.0f)};
+#if defined(__CUDA_ARCH__)
+#pragma unroll(ROLLED ? 1 : 3)
+#endif
+  for (int sp = 0; sp < 3; ++sp) {
+    T v[5], p[3], s[3], r[3];
+    v[3] = xs; v[4] = ys;
+    if (sp == 0) { v[0] = rgb[0]; v[1] = rgb[1]; v[2] = rgb[2]; }
+    else if (sp == 1) rgb2lab_fwd<T, false>(rgb, v, nullptr);
+    else rgb2hsv_fwd<T, false, false>(rgb, v, nullptr);
+    poly_eval<T, NV, DEG>(v, coef + sp * NC, p);
 #pragma unroll
-  for (int k = 0; k < 3; ++k) {
-    s[k] = vsigmoid(p[k]);
-    if (sig) sig[k] = s[k];
-    res[k] = vfma(s[k], T(2.0f), T(-1.0f));                                                // model.py:490,497
+    for (int k = 0; k < 3; ++k) { s[k] = vsigmoid(p[k]); sink(sp, k, s[k]); }              // saved plane 3 * sp + k
+    if (sp == 0) { r[0] = s[0]; r[1] = s[1]; r[2] = s[2]; }                                // model.py:490
+    else if (sp == 1) lab2rgb_fwd<T, false>(s, r, nullptr);                                // model.py:491
+    else hsv2rgb_fwd<T, false, false>(s, r, nullptr);                                      // model.py:492
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const T term = vfma(r[k], T(2.0f), T(-1.0f));                                        // model.py:497-499
+      res[k] = sp == 0 ? term : vadd(res[k], term);                                        // model.py:501
+    }
   }
-  rgb2lab_fwd<T, false>(rgb, v, nullptr);
-  poly_eval<T, NV, DEG>(v, coef + NC, p);
 #pragma unroll
-  for (int k = 0; k < 3; ++k) { s[k] = vsigmoid(p[k]); if (sig) sig[3 + k] = s[k]; }
-  lab2rgb_fwd<T, false>(s, r, nullptr);                                                    // model.py:491
-#pragma unroll
-  for (int k = 0; k < 3; ++k) res[k] = vadd(res[k], vfma(r[k], T(2.0f), T(-1.0f)));        // model.py:498,501
-  rgb2hsv_fwd<T, false, false>(rgb, v, nullptr);
-  poly_eval<T, NV, DEG>(v, coef + 2 * NC, p);
-#pragma unroll
-  for (int k = 0; k < 3; ++k) { s[k] = vsigmoid(p[k]); if (sig) sig[6 + k] = s[k]; }
-  hsv2rgb_fwd<T, false, false>(s, r, nullptr);                                             // model.py:492
-#pragma unroll
-  for (int k = 0; k < 3; ++k) {
-    res[k] = vadd(res[k], vfma(r[k], T(2.0f), T(-1.0f)));                                  // model.py:499,501
-    out[k] = clamp ? vadd_sat(rgb[k], res[k]) : res[k];                                    // model.py:508
-  }
+  for (int k = 0; k < 3; ++k) out[k] = clamp ? vadd_sat(rgb[k], res[k]) : res[k];          // model.py:508
 }
 
 // Backward, per-pixel part (the image is data -- TriSpaceRegNet.forward feeds the input or target

@@ -27,8 +27,8 @@ namespace tri {
 #define TRI_FWD_MIN_BLOCKS 3
 #endif
 constexpr int THREADS = TRI_FWD_THREADS;
-constexpr int DEG = 4;                       // the reference's polynomial_order default (model.py:413)
-constexpr int MAX_NC = poly_num_coeffs(5, DEG);
+constexpr int MAX_DEG = 4;                   // degrees 1..4 are instantiated (the reference's default polynomial_order is 4,
+                                             // model.py:413; ChannelPolyLayer's own default degree is 3, model.py:208)
 
 struct TParams {
   const float* img;      // [B][3][HW]
@@ -73,9 +73,10 @@ __device__ __forceinline__ void coords(int idx, int W, float fW, float fH, float
 // kernel is FMA-bound (about 1500 multiply-adds per pixel), not HBM-bound, and the fully unrolled
 // monomial walk wants its registers; VEC = 1: scalar path for odd HW or unaligned bases.
 // ---------------------------------------------------------------------------------------------
-template <int NV, int VEC, bool SAVE>
+template <int NV, int DEG, int VEC, bool SAVE>
 __global__ void __launch_bounds__(THREADS, TRI_FWD_MIN_BLOCKS) trispace_fwd_kernel(const TParams p) {
   constexpr int NC = poly_num_coeffs(NV, DEG);
+  constexpr bool ROLLED = NV == 5 && DEG == 4 && !SAVE;     // see trispace_fwd (curl_poly.cuh)
   __shared__ Coef4 s_coef[3 * NC];
   const int b = blockIdx.y;
   stage_coef<NC>(p, b, s_coef);
@@ -98,13 +99,20 @@ __global__ void __launch_bounds__(THREADS, TRI_FWD_MIN_BLOCKS) trispace_fwd_kern
         for (int k = 0; k < 4; ++k) coords(i + k, p.W, fW, fH, &xs[k], &ys[k]);
       }
       const F4 x[3] = {F4(F2(c0.x, c0.y), F2(c0.z, c0.w)), F4(F2(c1.x, c1.y), F2(c1.z, c1.w)), F4(F2(c2.x, c2.y), F2(c2.z, c2.w))};
-      F4 y[3], sv[9];
-      trispace_fwd<F4, NV, DEG>(x, F4(F2(xs[0], xs[1]), F2(xs[2], xs[3])), F4(F2(ys[0], ys[1]), F2(ys[2], ys[3])), s_coef, clamp, y,
-                                SAVE ? sv : nullptr);
+      // the short polynomial stores its sigmoids after the three spaces (35 coefficients, 4K x 8: 1.248 ms against
+      // 1.271 storing as they appear); the long one as they appear (3.30 against 3.34 ms, and 8 B of spills for 60)
+      constexpr bool DEFER = SAVE && NV == 3;
+      F4 y[3], sv[DEFER ? 9 : 1];
+      trispace_fwd<F4, NV, DEG, ROLLED>(x, F4(F2(xs[0], xs[1]), F2(xs[2], xs[3])), F4(F2(ys[0], ys[1]), F2(ys[2], ys[3])), s_coef, clamp, y,
+                                       [&](int sp, int k, F4 v) {
+                                         if constexpr (DEFER) sv[3 * sp + k] = v;
+                                         else if constexpr (SAVE) __stcs(reinterpret_cast<float4*>(sg + (size_t)(3 * sp + k) * HW + i),
+                                                                         make_float4(v.a.lo(), v.a.hi(), v.b.lo(), v.b.hi()));
+                                       });
 #pragma unroll
       for (int c = 0; c < 3; ++c)
         __stcs(reinterpret_cast<float4*>(out + (size_t)c * HW + i), make_float4(y[c].a.lo(), y[c].a.hi(), y[c].b.lo(), y[c].b.hi()));
-      if constexpr (SAVE) {
+      if constexpr (DEFER) {
 #pragma unroll
         for (int c = 0; c < 9; ++c)
           __stcs(reinterpret_cast<float4*>(sg + (size_t)c * HW + i), make_float4(sv[c].a.lo(), sv[c].a.hi(), sv[c].b.lo(), sv[c].b.hi()));
@@ -116,27 +124,22 @@ __global__ void __launch_bounds__(THREADS, TRI_FWD_MIN_BLOCKS) trispace_fwd_kern
       float xs[2] = {0.f, 0.f}, ys[2] = {0.f, 0.f};
       if (NV == 5) { coords(i, p.W, fW, fH, &xs[0], &ys[0]); coords(i + 1, p.W, fW, fH, &xs[1], &ys[1]); }
       const F2 x[3] = {F2(c0.x, c0.y), F2(c1.x, c1.y), F2(c2.x, c2.y)};
-      F2 y[3], sv[9];
-      trispace_fwd<F2, NV, DEG>(x, F2(xs[0], xs[1]), F2(ys[0], ys[1]), s_coef, clamp, y, SAVE ? sv : nullptr);
+      F2 y[3];
+      trispace_fwd<F2, NV, DEG, ROLLED>(x, F2(xs[0], xs[1]), F2(ys[0], ys[1]), s_coef, clamp, y, [&](int sp, int k, F2 v) {
+        if constexpr (SAVE) __stcs(reinterpret_cast<float2*>(sg + (size_t)(3 * sp + k) * HW + i), make_float2(v.lo(), v.hi()));
+      });
 #pragma unroll
       for (int c = 0; c < 3; ++c)
         __stcs(reinterpret_cast<float2*>(out + (size_t)c * HW + i), make_float2(y[c].lo(), y[c].hi()));
-      if constexpr (SAVE) {
-#pragma unroll
-        for (int c = 0; c < 9; ++c)
-          __stcs(reinterpret_cast<float2*>(sg + (size_t)c * HW + i), make_float2(sv[c].lo(), sv[c].hi()));
-      }
     } else {
       const float x[3] = {__ldcs(in + i), __ldcs(in + HW + i), __ldcs(in + 2 * (size_t)HW + i)};
-      float xs = 0.f, ys = 0.f, y[3], sv[9];
+      float xs = 0.f, ys = 0.f, y[3];
       if (NV == 5) coords(i, p.W, fW, fH, &xs, &ys);
-      trispace_fwd<float, NV, DEG>(x, xs, ys, s_coef, clamp, y, SAVE ? sv : nullptr);
+      trispace_fwd<float, NV, DEG, ROLLED>(x, xs, ys, s_coef, clamp, y, [&](int sp, int k, float v) {
+        if constexpr (SAVE) __stcs(sg + (size_t)(3 * sp + k) * HW + i, v);
+      });
 #pragma unroll
       for (int c = 0; c < 3; ++c) __stcs(out + (size_t)c * HW + i, y[c]);
-      if constexpr (SAVE) {
-#pragma unroll
-        for (int c = 0; c < 9; ++c) __stcs(sg + (size_t)c * HW + i, sv[c]);
-      }
     }
   }
 }
@@ -159,7 +162,7 @@ __global__ void __launch_bounds__(THREADS, TRI_FWD_MIN_BLOCKS) trispace_fwd_kern
 constexpr int BT = TRI_BT;           // threads per block = pixels per tile
 constexpr int T_PITCH = BT + 4;
 
-template <int NV>
+template <int NV, int DEG>
 constexpr size_t bwd_smem_bytes() {
   return ((size_t)12 * poly_num_coeffs(NV, DEG) + (size_t)poly_num_coeffs(NV, DEG) * T_PITCH + (size_t)BT * 4) * sizeof(float);
 }
@@ -170,7 +173,7 @@ constexpr size_t bwd_smem_bytes() {
 #ifndef TRI_SKEW_NS
 #define TRI_SKEW_NS 0
 #endif
-template <int NV, bool SAVED>
+template <int NV, int DEG, bool SAVED>
 __global__ void __launch_bounds__(BT, TRI_BWD_MIN_BLOCKS) trispace_bwd_kernel(const TParams p) {
   constexpr int NC = poly_num_coeffs(NV, DEG);
   constexpr int NG = 9 * NC;
@@ -271,7 +274,10 @@ __global__ void __launch_bounds__(BT, TRI_BWD_MIN_BLOCKS) trispace_bwd_kernel(co
         const float4 g2 = reinterpret_cast<const float4*>(s_G + 2 * BT)[q];
 #pragma unroll
         for (int j = 0; j < J; ++j) {
-          const int k = lane + 32 * j < NC ? lane + 32 * j : lane;   // surplus slots redo row `lane`; never stored
+          // surplus slots redo a row that exists and falls in other banks than the live rows 32 * j + (0..): row
+          // `lane` when there are 32 rows (row 0 would share its banks with row 32: +3 % on the 35-coefficient
+          // backward), row 0 for the small polynomials; never stored
+          const int k = lane + 32 * j < NC ? lane + 32 * j : (NC >= 32 ? lane : 0);
           const float4 m = reinterpret_cast<const float4*>(s_T + k * T_PITCH)[q];
           const F2 mlo(m.x, m.y), mhi(m.z, m.w);
           acc[sp][j][0] = vfma(F2(g0.x, g0.y), mlo, acc[sp][j][0]);
@@ -341,39 +347,41 @@ static int check_args(const float* img, const float* R, const float* L, const fl
                       int B, int H, int W) {
   if (B <= 0 || H <= 0 || W <= 0 || (long long)H * W > 0x3fffffffLL || B > 65535) return CURL_ERR_BAD_ARG;
   if (!img || !R || !L || !Hc) return CURL_ERR_BAD_ARG;
-  if (degree != DEG || (spatial != 0 && spatial != 1)) return CURL_ERR_BAD_ARG;
+  if (degree < 1 || degree > MAX_DEG || (spatial != 0 && spatial != 1)) return CURL_ERR_BAD_ARG;
   if (!aligned4(img) || !aligned4(R) || !aligned4(L) || !aligned4(Hc)) return CURL_ERR_MISALIGNED;
   return CURL_OK;
 }
 
-template <int NV>
+template <int NV, int DEG>
 static int launch_fwd(const TParams& p, int B, int vec, cudaStream_t st) {
   // four pixels per thread halve the coefficient reads (the forward's shared-memory pipe is 77 % busy at
   // two).  Measured at 4K x 8: 35 coefficients 46.4 -> 50.6 Gpx/s (53.2 without saving); 126 coefficients
   // 20.2 -> 17.4 (the nested evaluation of 126 terms for four pixels no longer fits 128 registers), so the
   // spatial polynomial stays at two.
-  if (NV == 5 && vec == 4) vec = 2;
+#ifndef TRI_SPATIAL_VEC4
+  if (NV == 5 && DEG == 4 && vec == 4) vec = 2;
+#endif
   dim3 grid(grid_x(B, p.HW, THREADS * vec, FWD_BLOCKS_PER_SM), B);
   if (p.sig) {
-    if (vec == 4) trispace_fwd_kernel<NV, 4, true><<<grid, THREADS, 0, st>>>(p);
-    else if (vec == 2) trispace_fwd_kernel<NV, 2, true><<<grid, THREADS, 0, st>>>(p);
-    else trispace_fwd_kernel<NV, 1, true><<<grid, THREADS, 0, st>>>(p);
+    if (vec == 4) trispace_fwd_kernel<NV, DEG, 4, true><<<grid, THREADS, 0, st>>>(p);
+    else if (vec == 2) trispace_fwd_kernel<NV, DEG, 2, true><<<grid, THREADS, 0, st>>>(p);
+    else trispace_fwd_kernel<NV, DEG, 1, true><<<grid, THREADS, 0, st>>>(p);
   } else {
-    if (vec == 4) trispace_fwd_kernel<NV, 4, false><<<grid, THREADS, 0, st>>>(p);
-    else if (vec == 2) trispace_fwd_kernel<NV, 2, false><<<grid, THREADS, 0, st>>>(p);
-    else trispace_fwd_kernel<NV, 1, false><<<grid, THREADS, 0, st>>>(p);
+    if (vec == 4) trispace_fwd_kernel<NV, DEG, 4, false><<<grid, THREADS, 0, st>>>(p);
+    else if (vec == 2) trispace_fwd_kernel<NV, DEG, 2, false><<<grid, THREADS, 0, st>>>(p);
+    else trispace_fwd_kernel<NV, DEG, 1, false><<<grid, THREADS, 0, st>>>(p);
   }
   return cudaGetLastError() == cudaSuccess ? CURL_OK : CURL_ERR_LAUNCH;
 }
 
-template <int NV>
+template <int NV, int DEG>
 static int launch_bwd(const TParams& p, int B, cudaStream_t st) {
-  auto kern = p.sig ? trispace_bwd_kernel<NV, true> : trispace_bwd_kernel<NV, false>;
-  const bool ok = p.sig ? host::ensure_dyn_smem<trispace_bwd_kernel<NV, true>>(bwd_smem_bytes<NV>())
-                        : host::ensure_dyn_smem<trispace_bwd_kernel<NV, false>>(bwd_smem_bytes<NV>());
+  auto kern = p.sig ? trispace_bwd_kernel<NV, DEG, true> : trispace_bwd_kernel<NV, DEG, false>;
+  const bool ok = p.sig ? host::ensure_dyn_smem<trispace_bwd_kernel<NV, DEG, true>>(bwd_smem_bytes<NV, DEG>())
+                        : host::ensure_dyn_smem<trispace_bwd_kernel<NV, DEG, false>>(bwd_smem_bytes<NV, DEG>());
   if (!ok) return CURL_ERR_LAUNCH;
   dim3 grid(bwd_grid_x(B, p.HW), B);
-  kern<<<grid, BT, bwd_smem_bytes<NV>(), st>>>(p);
+  kern<<<grid, BT, bwd_smem_bytes<NV, DEG>(), st>>>(p);
   return cudaGetLastError() == cudaSuccess ? CURL_OK : CURL_ERR_LAUNCH;
 }
 
@@ -406,13 +414,15 @@ int curl_trispace_fwd_f32(const float* img, const float* R, const float* L, cons
   if (p.HW % 4 == 0 && (bits & 15u) == 0) vec = 4;
 #endif
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  return spatial ? launch_fwd<5>(p, B, vec, st) : launch_fwd<3>(p, B, vec, st);
+#define CURL_TRI_FWD(D) case D: return spatial ? launch_fwd<5, D>(p, B, vec, st) : launch_fwd<3, D>(p, B, vec, st)
+  switch (degree) { CURL_TRI_FWD(1); CURL_TRI_FWD(2); CURL_TRI_FWD(3); default: CURL_TRI_FWD(4); }
+#undef CURL_TRI_FWD
 }
 
 size_t curl_trispace_bwd_workspace_bytes(int B, int H, int W, int degree, int spatial) {
-  if (B <= 0 || H <= 0 || W <= 0 || degree != DEG) return 0;
+  if (B <= 0 || H <= 0 || W <= 0 || degree < 1 || degree > MAX_DEG) return 0;
   const size_t tick_bytes = ((size_t)B * sizeof(unsigned) + 255) / 256 * 256;
-  return tick_bytes + (size_t)B * bwd_grid_x(B, H * W) * 9 * poly_num_coeffs(spatial ? 5 : 3, DEG) * sizeof(float);
+  return tick_bytes + (size_t)B * bwd_grid_x(B, H * W) * 9 * poly_num_coeffs(spatial ? 5 : 3, degree) * sizeof(float);
 }
 
 int curl_trispace_bwd_f32(const float* img, const float* R, const float* L, const float* Hc, int degree,
@@ -434,7 +444,9 @@ int curl_trispace_bwd_f32(const float* img, const float* R, const float* L, cons
   p.HW = H * W; p.W = W; p.H = H; p.clamp = final_clamp ? 1 : 0;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (cudaMemsetAsync(workspace, 0, tick_bytes, st) != cudaSuccess) return CURL_ERR_LAUNCH;
-  return spatial ? launch_bwd<5>(p, B, st) : launch_bwd<3>(p, B, st);
+#define CURL_TRI_BWD(D) case D: return spatial ? launch_bwd<5, D>(p, B, st) : launch_bwd<3, D>(p, B, st)
+  switch (degree) { CURL_TRI_BWD(1); CURL_TRI_BWD(2); CURL_TRI_BWD(3); default: CURL_TRI_BWD(4); }
+#undef CURL_TRI_BWD
 }
 
 }  // extern "C"

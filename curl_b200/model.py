@@ -172,8 +172,8 @@ class TriSpaceRegNet(nn.Module):
     conversions, three polynomials, sigmoids, inverse conversions, residual sum, final clamp -- as one
     fused sm_100a kernel forward and one backward.  Same constructor arguments, attribute and
     state-dict names (`polylayer`, `backbone`, `rgb2lab` .. `hsv2rgb`, `x`, `y`) and methods
-    (generate_coefficients, generate_residual, generate_image, forward).  Only polynomial_order == 4
-    (the default) is built.  `backbone`: any module mapping [B,3,H,W] -> [B, 9 * num_coeffs]; without
+    (generate_coefficients, generate_residual, generate_image, forward).  polynomial_order 1..4 (4 is the
+    reference's default and what its scripts use).  `backbone`: any module mapping [B,3,H,W] -> [B, 9 * num_coeffs]; without
     it the reference's timm EfficientNetV2 + 4-layer head (model.py:427-435) is created, which needs
     timm.  The backbone stays on PyTorch/cuDNN."""
 

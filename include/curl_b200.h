@@ -187,8 +187,8 @@ int curl_apply_curve_bwd_f32(const float* in, const float* C, int64_t ldC, int c
  * order as ChannelPolyLayer.generate_powers enumerates them.  R, L, Hc: [B][3][NC] contiguous,
  * NC = curl_trispace_num_coeffs(degree, spatial) (35 / 126 for degree 4).  One pass per pixel; the
  * reference's [B, H, W, NC] monomial tensor (504 B/px per space) is never formed.
- * Only degree == 4 (the reference's polynomial_order default) is built; other degrees return
- * CURL_ERR_BAD_ARG.
+ * Degrees 1..4 are built (4 is the reference's polynomial_order default and the only one its scripts use;
+ * NC = 4/10/20/35 without and 6/21/56/126 with the spatial variables); other degrees return CURL_ERR_BAD_ARG.
  * saved: NULL, or [B][9][H][W] receiving the nine sigmoid outputs (3 spaces x 3 channels) -- the only
  * intermediate the backward needs besides the image.  Handing the same buffer to
  * curl_trispace_bwd_f32 skips re-evaluating the three polynomials there (36 B/px of HBM for about

@@ -151,6 +151,9 @@ def main():
 
 
 TRISPACE_CASES = ["rgb", "spatial", "spatial_mobile", "uint8", "edges"]
+# ChannelPolyLayer(degree, ...) is generic in the degree (model.py:263-333); appended after the degree-4 cases so
+# that those regenerate bit for bit (one seeded generator runs through the list)
+TRISPACE_DEG_CASES = {"deg1_spatial": 1, "deg2_rgb": 2, "deg2_spatial": 2, "deg3_rgb": 3, "deg3_spatial": 3}
 
 
 def trispace_golden():
@@ -159,8 +162,9 @@ def trispace_golden():
     coefficient gradients of loss = sum(out * gout) by autograd."""
     g = torch.Generator().manual_seed(20261105)
     blob = {}
-    for case in TRISPACE_CASES:
-        spatial = case.startswith("spatial")
+    for case in TRISPACE_CASES + list(TRISPACE_DEG_CASES):
+        spatial = "spatial" in case
+        degree = TRISPACE_DEG_CASES.get(case, 4)
         B, H, W = (1, 16, 32) if case == "edges" else (2, 14, 18)
         if case == "edges":
             img = _edge_image()
@@ -168,13 +172,13 @@ def trispace_golden():
             img = torch.rand(B, 3, H, W, generator=g)
             if case == "uint8":
                 img = (img * 255).round() / 255
-        _, net = ref_loader.load_trispace(4, spatial, mobile=(case == "spatial_mobile"))
+        _, net = ref_loader.load_trispace(degree, spatial, mobile=(case == "spatial_mobile"))
         nc = net.polylayer.num_coeffs
         R, L, Hc = (0.3 * torch.randn(B, 3, nc, generator=g) for _ in range(3))
         gout = torch.randn(B, 3, H, W, generator=g)
         blob.update({f"{case}.img": img.numpy(), f"{case}.R": R.numpy(), f"{case}.L": L.numpy(),
                      f"{case}.H": Hc.numpy(), f"{case}.gout": gout.numpy(),
-                     f"{case}.spatial": np.array(int(spatial))})
+                     f"{case}.spatial": np.array(int(spatial)), f"{case}.degree": np.array(degree)})
         for tag, dtype in (("f32", torch.float32), ("f64", torch.float64)):
             net_d = net.to(dtype) if dtype == torch.float64 else net
             for clamp in (0, 1):
@@ -297,6 +301,8 @@ def real_golden():
 if __name__ == "__main__":
     if "--loss-only" in sys.argv:
         loss_golden()
+    elif "--trispace-only" in sys.argv:
+        trispace_golden()
     elif "--real-only" in sys.argv:
         real_golden()
         print("real.npz", os.path.getsize(os.path.join(GOLDEN_DIR, "real.npz")), "bytes")

@@ -108,18 +108,20 @@ def unit_to_u8(y):
     return out
 
 
-def trispace(img, R, L, Hc, spatial, clamp, gout=None):
+def trispace(img, R, L, Hc, spatial, clamp, gout=None, degree=4):
     """Returns out[B,3,H,W] or, when gout is given, dict(gR, gL, gH)."""
     img = _c(img); R = _c(R); L = _c(L); Hc = _c(Hc)
     B, _, h, w = img.shape
     if gout is None:
         out = np.empty_like(img)
-        rc = lib().sim_trispace(0, _f(img), _f(R), _f(L), _f(Hc), int(spatial), int(clamp), None, _f(out), None, None, None, B, h, w)
+        rc = lib().sim_trispace_deg(0, _f(img), _f(R), _f(L), _f(Hc), int(spatial), int(degree), int(clamp), None, _f(out),
+                                    None, None, None, B, h, w)
         assert rc == 0
         return out
     gout = _c(gout)
     gR = np.empty_like(R); gL = np.empty_like(L); gH = np.empty_like(Hc)
-    rc = lib().sim_trispace(1, _f(img), _f(R), _f(L), _f(Hc), int(spatial), int(clamp), _f(gout), None, _f(gR), _f(gL), _f(gH), B, h, w)
+    rc = lib().sim_trispace_deg(1, _f(img), _f(R), _f(L), _f(Hc), int(spatial), int(degree), int(clamp), _f(gout), None,
+                                _f(gR), _f(gL), _f(gH), B, h, w)
     assert rc == 0
     return dict(gR=gR, gL=gL, gH=gH)
 

@@ -177,10 +177,10 @@ int sim_adjust(int do_bwd, int group, const float* in, const float* P, int64_t l
 // do_bwd == 1: gR/gL/gH[B][3][NC] accumulated in double over the image (the device kernel's tiling
 // and reduction are not modelled -- only the per-pixel math and the monomial order).
 }  // extern "C"
-template <int NV>
+template <int NV, int DEG>
 static void sim_trispace_nv(int do_bwd, const float* img, const float* R, const float* L, const float* Hc, int clamp,
                             const float* gout, float* out, float* gR, float* gL, float* gH, int B, int H, int W) {
-  constexpr int NC = poly_num_coeffs(NV, 4);
+  constexpr int NC = poly_num_coeffs(NV, DEG);
   const int HW = H * W;
   std::vector<Coef4> coef(3 * NC);
   std::vector<float> terms(NC);
@@ -198,17 +198,17 @@ static void sim_trispace_nv(int do_bwd, const float* img, const float* R, const 
       const float xs = NV == 5 ? (float)(i % W) / (float)W : 0.f, ys = NV == 5 ? (float)(i / W) / (float)H : 0.f;
       if (!do_bwd) {
         float y[3];
-        trispace_fwd<float, NV, 4>(x, xs, ys, coef.data(), clamp != 0, y);
+        trispace_fwd<float, NV, DEG>(x, xs, ys, coef.data(), clamp != 0, y);
         for (int c = 0; c < 3; ++c) out[((size_t)b * 3 + c) * HW + i] = y[c];
       } else {
         const float g[3] = {gout[((size_t)b * 3 + 0) * HW + i], gout[((size_t)b * 3 + 1) * HW + i], gout[((size_t)b * 3 + 2) * HW + i]};
         float vars[3][3], gp[3][3];
-        trispace_gpoly<float, NV, 4>(x, xs, ys, coef.data(), clamp != 0, g, vars, gp);
+        trispace_gpoly<float, NV, DEG>(x, xs, ys, coef.data(), clamp != 0, g, vars, gp);
         for (int s = 0; s < 3; ++s) {
           const float v[5] = {vars[s][0], vars[s][1], vars[s][2], xs, ys};
           terms[0] = 1.0f;
           MonoStore<float> st{terms.data(), 1};
-          mono_visit<float, NV, 4>(v, st);
+          mono_visit<float, NV, DEG>(v, st);
           for (int c = 0; c < 3; ++c)
             for (int k = 0; k < NC; ++k) acc[(s * 3 + c) * NC + k] += (double)gp[s][c] * (double)terms[k];
         }
@@ -222,11 +222,22 @@ static void sim_trispace_nv(int do_bwd, const float* img, const float* R, const 
   }
 }
 extern "C" {
+int sim_trispace_deg(int do_bwd, const float* img, const float* R, const float* L, const float* Hc, int spatial, int degree,
+                     int clamp, const float* gout, float* out, float* gR, float* gL, float* gH, int B, int H, int W) {
+#define SIM_TRI(D)                                                                                  \
+  case D:                                                                                           \
+    if (spatial) sim_trispace_nv<5, D>(do_bwd, img, R, L, Hc, clamp, gout, out, gR, gL, gH, B, H, W); \
+    else sim_trispace_nv<3, D>(do_bwd, img, R, L, Hc, clamp, gout, out, gR, gL, gH, B, H, W);         \
+    return 0;
+  switch (degree) {
+    SIM_TRI(1) SIM_TRI(2) SIM_TRI(3) SIM_TRI(4)
+    default: return -1;
+  }
+#undef SIM_TRI
+}
 int sim_trispace(int do_bwd, const float* img, const float* R, const float* L, const float* Hc, int spatial, int clamp,
                  const float* gout, float* out, float* gR, float* gL, float* gH, int B, int H, int W) {
-  if (spatial) sim_trispace_nv<5>(do_bwd, img, R, L, Hc, clamp, gout, out, gR, gL, gH, B, H, W);
-  else sim_trispace_nv<3>(do_bwd, img, R, L, Hc, clamp, gout, out, gR, gL, gH, B, H, W);
-  return 0;
+  return sim_trispace_deg(do_bwd, img, R, L, Hc, spatial, 4, clamp, gout, out, gR, gL, gH, B, H, W);
 }
 
 // 8-bit I/O conversions of curl_layer_fwd_u8 (curl_vec.cuh), host instantiation: out[i] = u8_to_unit(i)

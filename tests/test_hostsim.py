@@ -95,20 +95,24 @@ def test_u8_conversions_are_exact():
     assert np.array_equal(got, (y * np.float32(255)).astype("uint8"))
 
 
-@pytest.mark.parametrize("case", ["rgb", "spatial", "spatial_mobile", "uint8", "edges"])
+@pytest.mark.parametrize("case", ["rgb", "spatial", "spatial_mobile", "uint8", "edges",
+                                  "deg1_spatial", "deg2_rgb", "deg2_spatial", "deg3_rgb", "deg3_spatial"])
 def test_hostsim_trispace_vs_golden(case, trispace_golden):
     """Per-pixel TriSpace math of the kernels (curl_poly.cuh: compile-time monomial order, fused
     sigmoid / colour chain, hand-derived coefficient gradient) against the reference fixtures."""
     g = trispace_golden
-    spatial = bool(g[f"{case}.spatial"])
+    spatial, degree = bool(g[f"{case}.spatial"]), int(g[f"{case}.degree"])
     img, R, L, Hc, gout = (g[f"{case}.{k}"] for k in ("img", "R", "L", "H", "gout"))
     for clamp in (0, 1):
-        out = hostsim.trispace(img, R, L, Hc, spatial, clamp)
+        out = hostsim.trispace(img, R, L, Hc, spatial, clamp, degree=degree)
         r32, r64 = g[f"{case}.f32.c{clamp}.out"], g[f"{case}.f64.c{clamp}.out"]
         own = np.abs(r32 - r64).max()
         assert np.abs(out - r64).max() <= max(2e-5, 3 * own), (case, clamp)
-        assert (np.abs(out - r32) > 1e-5).mean() <= 2e-3, (case, clamp)
-        gr = hostsim.trispace(img, R, L, Hc, spatial, clamp, gout)
+        # 1e-5 relative to max(1, |value|): the unclamped residual is not confined to [-3, 3] (lab2rgb of an arbitrary
+        # sigmoid triple leaves the gamut -- up to 17.6 in deg2_spatial, where the reference's own fp32 result is
+        # more than 1e-5 from its fp64 one at 0.26 % of the elements)
+        assert (np.abs(out - r32) > 1e-5 * np.maximum(1.0, np.abs(r64))).mean() <= 2e-3, (case, clamp)
+        gr = hostsim.trispace(img, R, L, Hc, spatial, clamp, gout, degree=degree)
         for k in ("gR", "gL", "gH"):
             assert rel_to_max(gr[k], g[f"{case}.f64.c{clamp}.{k}"]) <= 1e-4, (case, clamp, k)
 
