@@ -6,7 +6,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libcurl_b200.so")
 
-ABI_VERSION = 9
+ABI_VERSION = 10
 
 MASK_NONE, MASK_U8, MASK_F32 = 0, 1, 2
 RGB2LAB, LAB2RGB, RGB2HSV, HSV2RGB = 0, 1, 2, 3
@@ -39,6 +39,7 @@ SIGNATURES = {
     "curl_trispace_fwd_f32": (_i, [_p, _p, _p, _p, _i, _i, _i, _p, _p, _i, _i, _i, _p]),
     "curl_trispace_bwd_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),
     "curl_trispace_bwd_f32": (_i, [_p, _p, _p, _p, _i, _i, _i, _p, _p, _p, _p, _p, _p, _sz, _i, _i, _i, _p]),
+    "curl_trispace_bwd_img_f32": (_i, [_p, _p, _p, _p, _i, _i, _i, _p, _p, _p, _i, _i, _i, _p]),
     "curl_layer_seg_fwd_f32": (_i, [_p, _p, _i, _p, _i64, _p, _i64, _p, _i64, _p, _p, _i, _i, _i, _i, _i, _i, _p]),
     "curl_layer_seg_bwd_f32": (_i, [_p, _p, _i, _p, _i64, _p, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _p, _sz,
                                     _i, _i, _i, _i, _i, _i, _p]),

@@ -112,6 +112,49 @@ CURL_HD void poly_eval(const T* x, const Coef4* coef, T out[3]) {
   HornerNode<T, NV, DEG, 0, 0, 0, 0, 0, 0>::eval(x, coef, out);
 }
 
+// Gradient of the polynomial w.r.t. its three colour variables, for the image gradient:
+//   d[j] = d/dx_j  sum_c w[c] * P_c(x),  j = 0..2   (w = the gradient arriving at the three outputs).
+// The three channels are combined first (q_E = w . coef[E], per pixel), then ONE scalar nested evaluation carries its
+// three derivatives along (forward mode): with node(E) = q_E + sum_{v >= V} x_v node(E + e_v),
+//   d_j node(E) = sum_{v >= V} x_v d_j node(E + e_v)  +  node(E + e_j)          (j >= V; 0 for j < V).
+// A node of remaining degree 0 has no derivative and a subtree entered through x or y (v >= 3) contains no colour
+// variable; both are known at compile time, so no accumulator is ever initialised with a zero or fed one.
+template <class T, int NV, int LEFT, int V, int E0, int E1, int E2, int E3, int E4>
+struct HornerGrad {
+  template <int v>
+  static CURL_HD void children(const T* x, const Coef4* coef, const T w[3], T& val, T d[3]) {
+    if constexpr (v < NV) {
+      constexpr int F0 = E0 + (v == 0), F1 = E1 + (v == 1), F2_ = E2 + (v == 2), F3 = E3 + (v == 3), F4 = E4 + (v == 4);
+      constexpr bool CHILD_HAS_D = LEFT - 1 > 0 && v < 3;       // the child's d[j], j in [v, 2]
+      T cv, cd[3];
+      HornerGrad<T, NV, LEFT - 1, v, F0, F1, F2_, F3, F4>::eval(x, coef, w, cv, cd);
+      val = vfma(x[v], cv, val);
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {
+        if (j < v) continue;                                      // the child's subtree has no x_j
+        const bool direct = j == v;                               // d/dx_v (x_v * child) has the term `child`
+        const bool first = LEFT - 1 > 0 ? v == V : v == j;        // nothing has been added to d[j] yet
+        if (direct && CHILD_HAS_D) d[j] = first ? vfma(x[v], cd[j], cv) : vfma(x[v], cd[j], vadd(d[j], cv));
+        else if (direct) d[j] = first ? cv : vadd(d[j], cv);
+        else if (CHILD_HAS_D) d[j] = first ? vmul(x[v], cd[j]) : vfma(x[v], cd[j], d[j]);
+      }
+      children<v + 1>(x, coef, w, val, d);
+    }
+  }
+  static CURL_HD void eval(const T* x, const Coef4* coef, const T w[3], T& val, T d[3]) {
+    const Coef4 cf = coef[mono_rank(NV, E0, E1, E2, E3, E4)];
+    val = vfma(w[2], T(cf.v[2]), vfma(w[1], T(cf.v[1]), vmul(w[0], T(cf.v[0]))));
+    if constexpr (LEFT > 0) children<V>(x, coef, w, val, d);
+  }
+};
+
+template <class T, int NV, int DEG>
+CURL_HD void poly_grad_colour(const T* x, const Coef4* coef, const T w[3], T d[3]) {
+  static_assert(DEG >= 1, "a constant has no gradient");
+  T val;
+  HornerGrad<T, NV, DEG, 0, 0, 0, 0, 0, 0>::eval(x, coef, w, val, d);
+}
+
 // sigmoid and its derivative from the value
 template <class T>
 CURL_HD T vsigmoid(T p) {
@@ -173,21 +216,43 @@ CURL_HD void trispace_fwd(const T rgb[3], T xs, T ys, const Coef4* coef, bool cl
 //   d coef[s][c][k] = sum over pixels of gp[s][c] * monomial_k(vars[s] | x, y),
 // a reduction the caller organises (curl_trispace.cu).
 // sig (nullable): the nine sigmoid outputs the forward saved; when given, no polynomial is evaluated here.
-template <class T, int NV, int DEG>
+// IN_JAC (the image gradient, trispace_gimg): also returns the derivative records of the two input conversions
+// (the values they produce are the same with and without) and the gradient that reaches the image directly through
+// generate_image's  clamp(img + residual)  (model.py:508): gdirect = gout * [pass], or 0 without the clamp.
+template <class T, int NV, int DEG, bool IN_JAC = false>
 CURL_HD void trispace_gpoly(const T rgb[3], T xs, T ys, const Coef4* coef, bool clamp, const T gout[3],
-                            T vars[3][3], T gp[3][3], const T* sig = nullptr) {
+                            T vars[3][3], T gp[3][3], const T* sig = nullptr, LabJac<T>* jin_lab = nullptr,
+                            HsvJac<T>* jin_hsv = nullptr, T* gdirect = nullptr) {
   constexpr int NC = poly_num_coeffs(NV, DEG);
   T v[5], p[3], s[3][3], r_lab[3], r_hsv[3];
   RgbJac<T> jl; Hsv2RgbJac<T> jh;
   v[3] = xs; v[4] = ys;
   v[0] = vars[0][0] = rgb[0]; v[1] = vars[0][1] = rgb[1]; v[2] = vars[0][2] = rgb[2];
-  rgb2lab_fwd<T, false>(rgb, vars[1], nullptr);
-  rgb2hsv_fwd<T, false, false>(rgb, vars[2], nullptr);
+  rgb2lab_fwd<T, IN_JAC>(rgb, vars[1], IN_JAC ? jin_lab : nullptr);
+  rgb2hsv_fwd<T, IN_JAC, false>(rgb, vars[2], IN_JAC ? jin_hsv : nullptr);
   if (sig) {
 #pragma unroll
     for (int sp = 0; sp < 3; ++sp)
 #pragma unroll
       for (int k = 0; k < 3; ++k) s[sp][k] = sig[sp * 3 + k];
+  } else if (IN_JAC) {
+    // the image-gradient kernel: the three evaluations in a rolled loop (see trispace_gimg), operands and results
+    // moved with selects; same operations as below, bit-identical sigmoids
+#if defined(__CUDA_ARCH__)
+#pragma unroll 1
+#endif
+    for (int sp = 0; sp < 3; ++sp) {
+#pragma unroll
+      for (int k = 0; k < 3; ++k) v[k] = sp == 0 ? vars[0][k] : (sp == 1 ? vars[1][k] : vars[2][k]);
+      poly_eval<T, NV, DEG>(v, coef + sp * NC, p);
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        const T sk = vsigmoid(p[k]);
+        s[0][k] = sp == 0 ? sk : s[0][k];
+        s[1][k] = sp == 1 ? sk : s[1][k];
+        s[2][k] = sp == 2 ? sk : s[2][k];
+      }
+    }
   } else {
     poly_eval<T, NV, DEG>(v, coef, p);
 #pragma unroll
@@ -213,6 +278,7 @@ CURL_HD void trispace_gpoly(const T rgb[3], T xs, T ys, const Coef4* coef, bool 
       const T sum = vadd(rgb[k], res);
       g = vmul(g, vgate_eq(vsat(sum), sum));       // clamp passes gradient on [0,1] inclusive
     }
+    if (IN_JAC) gdirect[k] = clamp ? g : T(0.0f);
     g2[k] = vmul(g, T(2.0f));
   }
   T ga[3][3];
@@ -223,6 +289,40 @@ CURL_HD void trispace_gpoly(const T rgb[3], T xs, T ys, const Coef4* coef, bool 
   for (int sp = 0; sp < 3; ++sp)
 #pragma unroll
     for (int k = 0; k < 3; ++k) gp[sp][k] = vmul(ga[sp][k], vmul(s[sp][k], vsub(T(1.0f), s[sp][k])));   // d sigmoid
+}
+
+// Image gradient of generate_residual (+ generate_image).  The reference obtains it from autograd whenever the image
+// handed to TriSpaceRegNet requires a gradient (model.py:486-508 is differentiable in `img`; its own scripts feed
+// data, so they never ask).  x = column / W and y = row / H are constants (model.py:444-452, frozen parameters).
+//   gimg = gdirect + dQ_R/d rgb + J_rgb2lab^T dQ_L/d lab + J_rgb2hsv^T dQ_H/d hsv,   Q_s = gp[s] . P_s
+template <class T, int NV, int DEG>
+CURL_HD void trispace_gimg(const T rgb[3], T xs, T ys, const Coef4* coef, bool clamp, const T gout[3], T gimg[3],
+                           const T* sig = nullptr) {
+  constexpr int NC = poly_num_coeffs(NV, DEG);
+  T vars[3][3], gp[3][3], gd[3];
+  LabJac<T> jlab; HsvJac<T> jhsv;
+  trispace_gpoly<T, NV, DEG, true>(rgb, xs, ys, coef, clamp, gout, vars, gp, sig, &jlab, &jhsv, gd);
+  // The loop over the spaces stays rolled on the device (as in trispace_fwd<.., ROLLED>: unrolled, ptxas hoists the
+  // three polynomials' coefficient loads across each other -- 6.6 KB of spills per thread in the 126-coefficient
+  // kernel); the space's operands are picked with selects, never by a run-time index (that would put them in local memory).
+#if defined(__CUDA_ARCH__)
+#pragma unroll 1
+#endif
+  for (int sp = 0; sp < 3; ++sp) {
+    T v[5], w[3], d[3], gx[3];
+    v[3] = xs; v[4] = ys;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      v[k] = sp == 0 ? vars[0][k] : (sp == 1 ? vars[1][k] : vars[2][k]);
+      w[k] = sp == 0 ? gp[0][k] : (sp == 1 ? gp[1][k] : gp[2][k]);
+    }
+    poly_grad_colour<T, NV, DEG>(v, coef + sp * NC, w, d);
+    if (sp == 0) { gx[0] = d[0]; gx[1] = d[1]; gx[2] = d[2]; }
+    else if (sp == 1) rgb2lab_bwd(jlab, d, gx);
+    else rgb2hsv_bwd(jhsv, d, gx);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) gimg[k] = sp == 0 ? (clamp ? vadd(gd[k], gx[k]) : gx[k]) : vadd(gimg[k], gx[k]);
+  }
 }
 
 // visitor that writes monomial k to dst[k * pitch]

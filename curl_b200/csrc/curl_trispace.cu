@@ -328,6 +328,64 @@ __global__ void __launch_bounds__(BT, TRI_BWD_MIN_BLOCKS) trispace_bwd_kernel(co
 }
 
 // ---------------------------------------------------------------------------------------------
+// Backward w.r.t. the image: element-wise (no reduction), one packed pixel pair per thread and
+// iteration like the forward's VEC = 2 path; VEC = 1 for odd HW or unaligned bases.  p.out = gimg.
+// The reference's scripts never ask for this gradient (the image is data), so this kernel is about
+// the contract (autograd through model.py:486-508), not a headline: no tuning beyond the forward's.
+// ---------------------------------------------------------------------------------------------
+template <int NV, int DEG, int VEC, bool SAVED>
+__global__ void __launch_bounds__(THREADS, 2) trispace_gimg_kernel(const TParams p) {
+  constexpr int NC = poly_num_coeffs(NV, DEG);
+  __shared__ Coef4 s_coef[3 * NC];
+  const int b = blockIdx.y;
+  stage_coef<NC>(p, b, s_coef);
+  const int HW = p.HW;
+  const float* in = p.img + (size_t)b * 3 * HW;
+  const float* go = p.gout + (size_t)b * 3 * HW;
+  const float* sg = SAVED ? p.sig + (size_t)b * 9 * HW : nullptr;
+  float* gi = p.out + (size_t)b * 3 * HW;
+  const float fW = (float)p.W, fH = (float)p.H;
+  const bool clamp = p.clamp != 0;
+  const int stride = gridDim.x * THREADS * VEC;
+  for (int i = (blockIdx.x * THREADS + threadIdx.x) * VEC; i < HW; i += stride) {
+    if constexpr (VEC == 2) {
+      F2 x[3], g[3], sv[SAVED ? 9 : 1], y[3];
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const float2 a = __ldcs(reinterpret_cast<const float2*>(in + (size_t)c * HW + i));
+        const float2 q = __ldcs(reinterpret_cast<const float2*>(go + (size_t)c * HW + i));
+        x[c] = F2(a.x, a.y); g[c] = F2(q.x, q.y);
+      }
+      if constexpr (SAVED) {
+#pragma unroll
+        for (int c = 0; c < 9; ++c) {
+          const float2 a = __ldcs(reinterpret_cast<const float2*>(sg + (size_t)c * HW + i));
+          sv[c] = F2(a.x, a.y);
+        }
+      }
+      float xs[2] = {0.f, 0.f}, ys[2] = {0.f, 0.f};
+      if (NV == 5) { coords(i, p.W, fW, fH, &xs[0], &ys[0]); coords(i + 1, p.W, fW, fH, &xs[1], &ys[1]); }
+      trispace_gimg<F2, NV, DEG>(x, F2(xs[0], xs[1]), F2(ys[0], ys[1]), s_coef, clamp, g, y, SAVED ? sv : nullptr);
+#pragma unroll
+      for (int c = 0; c < 3; ++c)
+        __stcs(reinterpret_cast<float2*>(gi + (size_t)c * HW + i), make_float2(y[c].lo(), y[c].hi()));
+    } else {
+      float x[3], g[3], sv[SAVED ? 9 : 1], y[3], xs = 0.f, ys = 0.f;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) { x[c] = __ldcs(in + (size_t)c * HW + i); g[c] = __ldcs(go + (size_t)c * HW + i); }
+      if constexpr (SAVED) {
+#pragma unroll
+        for (int c = 0; c < 9; ++c) sv[c] = __ldcs(sg + (size_t)c * HW + i);
+      }
+      if (NV == 5) coords(i, p.W, fW, fH, &xs, &ys);
+      trispace_gimg<float, NV, DEG>(x, xs, ys, s_coef, clamp, g, y, SAVED ? sv : nullptr);
+#pragma unroll
+      for (int c = 0; c < 3; ++c) __stcs(gi + (size_t)c * HW + i, y[c]);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // Host side
 // ---------------------------------------------------------------------------------------------
 static bool aligned16(const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15u) == 0; }
@@ -382,6 +440,19 @@ static int launch_bwd(const TParams& p, int B, cudaStream_t st) {
   if (!ok) return CURL_ERR_LAUNCH;
   dim3 grid(bwd_grid_x(B, p.HW), B);
   kern<<<grid, BT, bwd_smem_bytes<NV, DEG>(), st>>>(p);
+  return cudaGetLastError() == cudaSuccess ? CURL_OK : CURL_ERR_LAUNCH;
+}
+
+template <int NV, int DEG>
+static int launch_gimg(const TParams& p, int B, int vec, cudaStream_t st) {
+  dim3 grid(grid_x(B, p.HW, THREADS * vec, FWD_BLOCKS_PER_SM), B);
+  if (p.sig) {
+    if (vec == 2) trispace_gimg_kernel<NV, DEG, 2, true><<<grid, THREADS, 0, st>>>(p);
+    else trispace_gimg_kernel<NV, DEG, 1, true><<<grid, THREADS, 0, st>>>(p);
+  } else {
+    if (vec == 2) trispace_gimg_kernel<NV, DEG, 2, false><<<grid, THREADS, 0, st>>>(p);
+    else trispace_gimg_kernel<NV, DEG, 1, false><<<grid, THREADS, 0, st>>>(p);
+  }
   return cudaGetLastError() == cudaSuccess ? CURL_OK : CURL_ERR_LAUNCH;
 }
 
@@ -447,6 +518,26 @@ int curl_trispace_bwd_f32(const float* img, const float* R, const float* L, cons
 #define CURL_TRI_BWD(D) case D: return spatial ? launch_bwd<5, D>(p, B, st) : launch_bwd<3, D>(p, B, st)
   switch (degree) { CURL_TRI_BWD(1); CURL_TRI_BWD(2); CURL_TRI_BWD(3); default: CURL_TRI_BWD(4); }
 #undef CURL_TRI_BWD
+}
+
+int curl_trispace_bwd_img_f32(const float* img, const float* R, const float* L, const float* Hc, int degree,
+                              int spatial, int final_clamp, const float* gout, const float* saved, float* gimg,
+                              int B, int H, int W, void* stream) {
+  int rc = check_args(img, R, L, Hc, degree, spatial, B, H, W);
+  if (rc != CURL_OK) return rc;
+  if (!gout || !gimg) return CURL_ERR_BAD_ARG;
+  if (!aligned4(gout) || !aligned4(saved) || !aligned4(gimg)) return CURL_ERR_MISALIGNED;
+  TParams p{};
+  p.img = img; p.coef[0] = R; p.coef[1] = L; p.coef[2] = Hc; p.gout = gout; p.out = gimg;
+  p.sig = const_cast<float*>(saved);
+  p.HW = H * W; p.W = W; p.H = H; p.clamp = final_clamp ? 1 : 0;
+  const uintptr_t bits = reinterpret_cast<uintptr_t>(img) | reinterpret_cast<uintptr_t>(gout) |
+                         reinterpret_cast<uintptr_t>(saved) | reinterpret_cast<uintptr_t>(gimg);
+  const int vec = (p.HW % 2 == 0 && (bits & 7u) == 0) ? 2 : 1;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+#define CURL_TRI_GIMG(D) case D: return spatial ? launch_gimg<5, D>(p, B, vec, st) : launch_gimg<3, D>(p, B, vec, st)
+  switch (degree) { CURL_TRI_GIMG(1); CURL_TRI_GIMG(2); CURL_TRI_GIMG(3); default: CURL_TRI_GIMG(4); }
+#undef CURL_TRI_GIMG
 }
 
 }  // extern "C"

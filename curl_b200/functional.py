@@ -328,8 +328,9 @@ class _MetaShape:
 
 class TriSpaceFn(torch.autograd.Function):
     """Fused TriSpaceRegNet.generate_residual (+ generate_image) (reference model.py:486-508) and its
-    recompute backward w.r.t. the polynomial coefficients.  The image is data on this path
-    (model.py:517-519): asking for its gradient raises."""
+    recompute backward: coefficient gradients (curl_trispace_bwd_f32) and, only when the image requires one, the
+    image gradient (curl_trispace_bwd_img_f32 -- the reference's scripts feed data there, model.py:517-519, but
+    its model.py:486-508 is differentiable in the image and autograd would provide it)."""
 
     @staticmethod
     def forward(ctx, img, R, L, H, degree, spatial, final_clamp, save_activations=True):
@@ -349,7 +350,7 @@ class TriSpaceFn(torch.autograd.Function):
         out = torch.empty_like(img)
         # the nine sigmoid outputs (36 B/px): with them the backward evaluates no polynomial
         saved = None
-        if save_activations and any(ctx.needs_input_grad[1:4]):
+        if save_activations and any(ctx.needs_input_grad[0:4]):
             saved = torch.empty(B, 9, h, w, dtype=torch.float32, device=dev)
         with torch.cuda.device(dev):
             rc = lib.curl_trispace_fwd_f32(_ptr(img), _ptr(coefs[0]), _ptr(coefs[1]), _ptr(coefs[2]), degree,
@@ -366,25 +367,30 @@ class TriSpaceFn(torch.autograd.Function):
     @staticmethod
     @torch.autograd.function.once_differentiable
     def backward(ctx, gout):
-        if ctx.needs_input_grad[0]:
-            raise RuntimeError("curl_b200: the TriSpace residual has no image gradient (the image is data on this "
-                               "path, reference model.py:517-519); detach the image")
         lib = _lib.load()
         img, R, L, H, saved = ctx.saved_tensors
         degree, spatial, final_clamp = ctx.cfg
         dev = img.device
         B, _, h, w = img.shape
         gout = gout.contiguous()
-        gR, gL, gH = torch.empty_like(R), torch.empty_like(L), torch.empty_like(H)
-        n = lib.curl_trispace_bwd_workspace_bytes(B, h, w, degree, spatial)
-        ws = torch.empty(n, dtype=torch.uint8, device=dev)
+        gimg = gR = gL = gH = None
         with torch.cuda.device(dev):
-            rc = lib.curl_trispace_bwd_f32(_ptr(img), _ptr(R), _ptr(L), _ptr(H), degree, spatial, final_clamp,
-                                           _ptr(gout), _ptr(saved), _ptr(gR), _ptr(gL), _ptr(gH), _ptr(ws), n, B, h, w,
-                                           _stream(dev))
-        _lib.check(rc, "curl_trispace_bwd_f32")
-        _lib.count_launch(2)
-        return None, gR, gL, gH, None, None, None, None
+            if any(ctx.needs_input_grad[1:4]):
+                gR, gL, gH = torch.empty_like(R), torch.empty_like(L), torch.empty_like(H)
+                n = lib.curl_trispace_bwd_workspace_bytes(B, h, w, degree, spatial)
+                ws = torch.empty(n, dtype=torch.uint8, device=dev)
+                rc = lib.curl_trispace_bwd_f32(_ptr(img), _ptr(R), _ptr(L), _ptr(H), degree, spatial, final_clamp,
+                                               _ptr(gout), _ptr(saved), _ptr(gR), _ptr(gL), _ptr(gH), _ptr(ws), n, B, h, w,
+                                               _stream(dev))
+                _lib.check(rc, "curl_trispace_bwd_f32")
+                _lib.count_launch(2)
+            if ctx.needs_input_grad[0]:
+                gimg = torch.empty_like(img)
+                rc = lib.curl_trispace_bwd_img_f32(_ptr(img), _ptr(R), _ptr(L), _ptr(H), degree, spatial, final_clamp,
+                                                   _ptr(gout), _ptr(saved), _ptr(gimg), B, h, w, _stream(dev))
+                _lib.check(rc, "curl_trispace_bwd_img_f32")
+                _lib.count_launch()
+        return gimg, gR, gL, gH, None, None, None, None
 
 
 class LossTermsFn(torch.autograd.Function):

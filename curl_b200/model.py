@@ -114,9 +114,11 @@ CURLLayer.forward_u8 = _forward_u8
 class ChannelPolyLayer(nn.Module):
     """Holder of the reference's ChannelPolyLayer state (model.py:206-219): `degree`,
     `num_variables`, `num_out`, `num_coeffs` and the frozen `powers` parameter (state-dict key
-    `polylayer.powers`), in the coefficient order of generate_powers (model.py:221-243).  The
-    arithmetic itself only exists fused into the TriSpace kernels (curl_trispace_*), so calling the
-    layer on its own raises."""
+    `polylayer.powers`), in the coefficient order of generate_powers (model.py:221-243).  On
+    the path the reference's scripts run, the polynomial is evaluated fused inside the TriSpace kernels
+    (curl_trispace_*: TriSpaceRegNet.generate_residual never calls this module's forward).  Called on its own --
+    only the reference's PolyRegNet does that, which is outside this package's scope -- forward (model.py:296-333)
+    runs on library element-wise ops, term by term, without the reference's [NC, B, V, H, W] power tensor."""
 
     def __init__(self, degree=3, num_variables=3, num_out=None):
         super().__init__()
@@ -138,8 +140,37 @@ class ChannelPolyLayer(nn.Module):
                               reverse=True)
 
     def forward(self, img, coeffs):
-        raise NotImplementedError("curl_b200: ChannelPolyLayer runs only fused inside TriSpaceRegNet."
-                                  "generate_residual (curl_trispace_fwd_f32); there is no stand-alone kernel")
+        return _poly_forward(self, img, coeffs)
+
+
+def _poly_forward(layer, img, coeffs):
+    """ChannelPolyLayer.forward / Deg4MobilePolyLayer.forward (model.py:296-333, 345-408): img [B, V, H, W],
+    coeffs [B, num_out, NC] -> [B, num_out, H, W] = sum_k coeffs[:, :, k] * prod_v img[:, v] ** powers[k, v].
+    Stand-alone convenience on library ops (differentiable by autograd); not a kernel and not on the fused path."""
+    if img.dim() != 4 or img.shape[1] != layer.num_variables:
+        raise ValueError("There should be a polynomial variable per channel: expected [B, %d, H, W], got %s"
+                         % (layer.num_variables, tuple(img.shape)))
+    if coeffs.dim() != 3 or coeffs.shape[0] != img.shape[0] or coeffs.shape[1] != layer.num_out \
+            or coeffs.shape[2] != layer.num_coeffs:
+        raise ValueError("coeffs must have shape [%d, %d, %d] (degree %d, %d variables), got %s"
+                         % (img.shape[0], layer.num_out, layer.num_coeffs, layer.degree, layer.num_variables,
+                            tuple(coeffs.shape)))
+    B = img.shape[0]
+    pows = [[None, img[:, v:v + 1]] for v in range(layer.num_variables)]       # pows[v][p] = img[:, v] ** p
+    for v in range(layer.num_variables):
+        for _ in range(2, layer.degree + 1):
+            pows[v].append(pows[v][-1] * pows[v][1])
+    out = None
+    for k, expo in enumerate(ChannelPolyLayer.generate_powers(layer.degree, layer.num_variables)):
+        term = None
+        for v, p in enumerate(expo):
+            if p:
+                term = pows[v][p] if term is None else term * pows[v][p]
+        c = coeffs[:, :, k].reshape(B, layer.num_out, 1, 1)
+        # (the constant term stays connected to img, as the reference's img ** 0 is: zero gradient, not "unused")
+        contrib = c + img[:, 0:1] * 0.0 if term is None else c * term
+        out = contrib if out is None else out + contrib
+    return out
 
 
 class Deg4MobilePolyLayer(nn.Module):
@@ -163,8 +194,7 @@ class Deg4MobilePolyLayer(nn.Module):
         self.powers = nn.Parameter(torch.tensor(powers, dtype=torch.float32), requires_grad=False)
 
     def forward(self, img, coeffs):
-        raise NotImplementedError("curl_b200: Deg4MobilePolyLayer runs only fused inside TriSpaceRegNet."
-                                  "generate_residual (curl_trispace_fwd_f32); there is no stand-alone kernel")
+        return _poly_forward(self, img, coeffs)
 
 
 class TriSpaceRegNet(nn.Module):

@@ -27,8 +27,13 @@ for (B, H, W) in SHAPES:
         def bwd():
             assert lib.curl_trispace_bwd_f32(img.data_ptr(), co[0].data_ptr(), co[1].data_ptr(), co[2].data_ptr(), 4, spatial, 1, gout.data_ptr(), sig_ptr,
                                              gc[0].data_ptr(), gc[1].data_ptr(), gc[2].data_ptr(), ws.data_ptr(), n, B, H, W, st) == 0
+        gimg = torch.empty_like(img)
+        def bwd_img():
+            assert lib.curl_trispace_bwd_img_f32(img.data_ptr(), co[0].data_ptr(), co[1].data_ptr(), co[2].data_ptr(), 4, spatial, 1, gout.data_ptr(), sig_ptr,
+                                                 gimg.data_ptr(), B, H, W, st) == 0
         res = {"shape": [B, H, W], "spatial": spatial, "nc": nc, "saved": sig is not None}
-        for name, fn in (("fwd", fwd), ("bwd", bwd)):
+        legs = (("fwd", fwd), ("bwd", bwd)) + ((("bwd_img", bwd_img),) if hasattr(lib, "curl_trispace_bwd_img_f32") else ())
+        for name, fn in legs:
             for _ in range(2): fn()
             torch.cuda.synchronize()
             e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)

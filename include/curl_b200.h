@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define CURL_ABI_VERSION 9
+#define CURL_ABI_VERSION 10
 
 /* error codes */
 #define CURL_OK 0
@@ -211,6 +211,17 @@ int curl_trispace_bwd_f32(const float* img, const float* R, const float* L, cons
                           int degree, int spatial, int final_clamp, const float* gout, const float* saved,
                           float* gR, float* gL, float* gH, void* workspace, size_t workspace_bytes,
                           int B, int H, int W, void* stream);
+/*
+ * Backward of the same w.r.t. the IMAGE: gimg[B][3][H][W] dense, given gout.  Replaces torch.autograd over
+ * model.py:486-508 when the image handed to TriSpaceRegNet requires a gradient (the reference's own scripts feed
+ * data there, model.py:517-519, and never ask; the coefficient gradients above do not depend on this call).
+ * Element-wise, no workspace: the direct term of generate_image's clamp, plus per space the gradient of the
+ * polynomial w.r.t. its three colour variables (x = column/W, y = row/H are constants, model.py:444-452) chained
+ * through the Jacobians of RGB2LAB / RGB2HSV.  saved: as for curl_trispace_bwd_f32 (NULL: recompute).
+ */
+int curl_trispace_bwd_img_f32(const float* img, const float* R, const float* L, const float* Hc,
+                              int degree, int spatial, int final_clamp, const float* gout, const float* saved,
+                              float* gimg, int B, int H, int W, void* stream);
 
 /*
  * Colour terms of CURLLoss (model.py:36-118): everything in that loss except MS-SSIM.

@@ -183,16 +183,16 @@ def trispace_golden():
             net_d = net.to(dtype) if dtype == torch.float64 else net
             for clamp in (0, 1):
                 a = [t.to(dtype).clone().requires_grad_(True) for t in (R, L, Hc)]
-                xi = img.to(dtype)
+                xi = img.to(dtype).clone().requires_grad_(True)      # the image gradient too (autograd of the reference)
                 if dtype == torch.float64:                    # x / y coordinate parameters are int64: keep them
                     net_d.x.data = net_d.x.data.to(torch.int64) if spatial else net_d.x.data
                     net_d.y.data = net_d.y.data.to(torch.int64) if spatial else net_d.y.data
                 out = net_d.generate_residual(xi, a[0], a[1], a[2])
                 if clamp:
                     out = net_d.generate_image(xi, out)
-                gr = torch.autograd.grad((out * gout.to(dtype)).sum(), a)
+                gr = torch.autograd.grad((out * gout.to(dtype)).sum(), a + [xi])
                 blob[f"{case}.{tag}.c{clamp}.out"] = out.detach().numpy()
-                for k, v in zip(("gR", "gL", "gH"), gr):
+                for k, v in zip(("gR", "gL", "gH", "gimg"), gr):
                     blob[f"{case}.{tag}.c{clamp}.{k}"] = v.numpy()
     np.savez_compressed(os.path.join(GOLDEN_DIR, "trispace.npz"), **blob)
 

@@ -108,8 +108,8 @@ def unit_to_u8(y):
     return out
 
 
-def trispace(img, R, L, Hc, spatial, clamp, gout=None, degree=4):
-    """Returns out[B,3,H,W] or, when gout is given, dict(gR, gL, gH)."""
+def trispace(img, R, L, Hc, spatial, clamp, gout=None, degree=4, want_gimg=False):
+    """Returns out[B,3,H,W] or, when gout is given, dict(gR, gL, gH) (want_gimg: the image gradient instead)."""
     img = _c(img); R = _c(R); L = _c(L); Hc = _c(Hc)
     B, _, h, w = img.shape
     if gout is None:
@@ -119,6 +119,12 @@ def trispace(img, R, L, Hc, spatial, clamp, gout=None, degree=4):
         assert rc == 0
         return out
     gout = _c(gout)
+    if want_gimg:
+        gimg = np.empty_like(img)
+        rc = lib().sim_trispace_deg(2, _f(img), _f(R), _f(L), _f(Hc), int(spatial), int(degree), int(clamp), _f(gout), _f(gimg),
+                                    None, None, None, B, h, w)
+        assert rc == 0
+        return gimg
     gR = np.empty_like(R); gL = np.empty_like(L); gH = np.empty_like(Hc)
     rc = lib().sim_trispace_deg(1, _f(img), _f(R), _f(L), _f(Hc), int(spatial), int(degree), int(clamp), _f(gout), None,
                                 _f(gR), _f(gL), _f(gH), B, h, w)

@@ -174,7 +174,7 @@ int sim_adjust(int do_bwd, int group, const float* in, const float* P, int64_t l
 }
 
 // TriSpace polynomial residual (curl_poly.cuh), host instantiation.  do_bwd == 0: out[B][3][HW];
-// do_bwd == 1: gR/gL/gH[B][3][NC] accumulated in double over the image (the device kernel's tiling
+// do_bwd == 2: out = image gradient; do_bwd == 1: gR/gL/gH[B][3][NC] accumulated in double over the image (the device kernel's tiling
 // and reduction are not modelled -- only the per-pixel math and the monomial order).
 }  // extern "C"
 template <int NV, int DEG>
@@ -200,6 +200,11 @@ static void sim_trispace_nv(int do_bwd, const float* img, const float* R, const 
         float y[3];
         trispace_fwd<float, NV, DEG>(x, xs, ys, coef.data(), clamp != 0, y);
         for (int c = 0; c < 3; ++c) out[((size_t)b * 3 + c) * HW + i] = y[c];
+      } else if (do_bwd == 2) {                        // image gradient -> out
+        const float g[3] = {gout[((size_t)b * 3 + 0) * HW + i], gout[((size_t)b * 3 + 1) * HW + i], gout[((size_t)b * 3 + 2) * HW + i]};
+        float y[3];
+        trispace_gimg<float, NV, DEG>(x, xs, ys, coef.data(), clamp != 0, g, y);
+        for (int c = 0; c < 3; ++c) out[((size_t)b * 3 + c) * HW + i] = y[c];
       } else {
         const float g[3] = {gout[((size_t)b * 3 + 0) * HW + i], gout[((size_t)b * 3 + 1) * HW + i], gout[((size_t)b * 3 + 2) * HW + i]};
         float vars[3][3], gp[3][3];
@@ -214,7 +219,7 @@ static void sim_trispace_nv(int do_bwd, const float* img, const float* R, const 
         }
       }
     }
-    if (do_bwd) {
+    if (do_bwd == 1) {
       float* dst[3] = {gR, gL, gH};
       for (int s = 0; s < 3; ++s)
         for (int j = 0; j < 3 * NC; ++j) dst[s][(size_t)b * 3 * NC + j] = (float)acc[s * 3 * NC + j];

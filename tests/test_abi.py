@@ -31,7 +31,7 @@ def test_header_and_binding_agree(lib):
 
 
 def test_version_and_strerror(lib):
-    assert lib.curl_abi_version() == 9
+    assert lib.curl_abi_version() == 10
     assert lib.curl_strerror(0) == b"success"
     for code in (-1, -2, -3, -4, -5, -6, -99):
         assert len(lib.curl_strerror(code)) > 0

@@ -192,6 +192,11 @@ def test_trispace_writes_stay_inside(lib, shape, spatial):
                                            _p(gR), _p(gL), _p(gH), _p(ws), nws, B, H, W, _st(dev))
             assert rc == 0
             a.check("trispace bwd spatial=%d clamp=%d save=%s" % (spatial, clamp, save))
+            gimg = a.f32(B, 3, H, W)
+            rc = lib.curl_trispace_bwd_img_f32(_p(img), _p(R), _p(L), _p(Hc), 4, spatial, clamp, _p(gout), _p(saved), _p(gimg),
+                                               B, H, W, _st(dev))
+            assert rc == 0
+            a.check("trispace bwd_img spatial=%d clamp=%d save=%s" % (spatial, clamp, save))
             del keep
 
 

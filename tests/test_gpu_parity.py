@@ -469,10 +469,19 @@ def test_trispace_vs_golden(case, clamp, save, trispace_golden):
     degree = int(g[f"{case}.degree"])                # ChannelPolyLayer is generic in the degree (model.py:263-333)
     net = curl_b200.TriSpaceRegNet(polynomial_order=degree, spatial=spatial, backbone=nn.Identity()).to(dev)
     net.save_activations = save      # backward from the saved sigmoid outputs, or recomputing the polynomials
-    img = torch.from_numpy(g[f"{case}.img"]).to(dev)
+    img = torch.from_numpy(g[f"{case}.img"]).to(dev).requires_grad_(True)      # the image gradient as well
     R, L, Hc = (torch.from_numpy(g[f"{case}.{k}"]).to(dev).requires_grad_(True) for k in ("R", "L", "H"))
     out = net.generate_residual(img, R, L, Hc) if not clamp else net._fused(img, R, L, Hc, True)
     out.backward(torch.from_numpy(g[f"{case}.gout"]).to(dev))
+    parity.check_trispace_gimg(img.grad.cpu().numpy(), g[f"{case}.f32.c{clamp}.gimg"], g[f"{case}.f64.c{clamp}.gimg"], (case, clamp, save))
+    # coefficient gradients do not depend on whether the image gradient was asked for
+    a = [t.detach().clone().requires_grad_(True) for t in (R, L, Hc)]
+    o2 = net._fused(img.detach(), *a, bool(clamp))
+    o2.backward(torch.from_numpy(g[f"{case}.gout"]).to(dev))
+    assert torch.equal(o2, out.detach())
+    for t, u in zip(a, (R, L, Hc)):
+        assert torch.equal(t.grad, u.grad)
+    img = img.detach()
     if clamp:       # the two-step public route gives the same image as the fused one
         two = net.generate_image(img, net.generate_residual(img, R.detach(), L.detach(), Hc.detach()))
         assert (two - out.detach()).abs().max().item() <= 1e-6
@@ -542,10 +551,18 @@ def test_trispace_deterministic_and_errors():
         assert torch.equal(x, z)                              # saved sigmoids == recomputed sigmoids, bit for bit
     with pytest.raises(ValueError, match="shape"):
         net.generate_residual(img, co[0][:, :, :35], co[1], co[2])
-    with pytest.raises(RuntimeError, match="no image gradient"):
-        a = [c.clone().requires_grad_(True) for c in co]
-        net._fused(img.clone().requires_grad_(True), *a, True).sum().backward()
-    with pytest.raises(NotImplementedError):
+    # the image gradient alone (frozen coefficients): same values as together with the coefficient gradients,
+    # saved sigmoids == recomputed sigmoids bit for bit
+    gi = []
+    for save, with_coef in ((True, True), (True, False), (False, False)):
+        net.save_activations = save
+        xi = img.clone().requires_grad_(True)
+        a = [c.clone().requires_grad_(with_coef) for c in co]
+        net._fused(xi, *a, True).backward(gout)
+        gi.append(xi.grad.clone())
+    assert torch.equal(gi[0], gi[1]) and torch.equal(gi[0], gi[2])
+    assert torch.isfinite(gi[0]).all() and gi[0].abs().max() > 0
+    with pytest.raises(ValueError, match="variable per channel"):      # stand-alone polynomial: 5 variables expected
         net.polylayer(img, co[0])
     with pytest.raises(RuntimeError, match="bad argument"):      # degrees 1..4 are built
         curl_b200.TriSpaceRegNet(polynomial_order=5, spatial=False, backbone=nn.Identity()).to(dev).generate_residual(

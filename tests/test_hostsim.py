@@ -115,6 +115,9 @@ def test_hostsim_trispace_vs_golden(case, trispace_golden):
         gr = hostsim.trispace(img, R, L, Hc, spatial, clamp, gout, degree=degree)
         for k in ("gR", "gL", "gH"):
             assert rel_to_max(gr[k], g[f"{case}.f64.c{clamp}.{k}"]) <= 1e-4, (case, clamp, k)
+        # image gradient (autograd of the reference through model.py:486-508)
+        gi = hostsim.trispace(img, R, L, Hc, spatial, clamp, gout, degree=degree, want_gimg=True)
+        parity.check_trispace_gimg(gi, g[f"{case}.f32.c{clamp}.gimg"], g[f"{case}.f64.c{clamp}.gimg"], (case, clamp))
 
 
 def _loss_from_terms(sums, L_pred, L_target, mask, msssim):

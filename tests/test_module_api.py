@@ -140,6 +140,32 @@ def test_trispace_api():
         curl_b200.TriSpaceRegNet(spatial=False, polylayer=mob, backbone=nn.Identity())
 
 
+@pytest.mark.parametrize("degree,nv,nout", [(3, 3, 3), (4, 5, 3), (2, 2, None), (0, 3, 3), (1, 4, 2)])
+def test_channel_poly_layer_standalone_forward(degree, nv, nout):
+    """ChannelPolyLayer.forward on its own (model.py:296-333; only the reference's PolyRegNet uses it): value and
+    autograd gradients against the reference's formula (oracle.channel_poly, pinned bit-identical to model.py's)."""
+    gen = torch.Generator().manual_seed(100 * degree + nv)
+    layer = curl_b200.ChannelPolyLayer(degree, nv, nout)
+    img = torch.rand(2, nv, 6, 7, generator=gen, dtype=torch.float64).requires_grad_(True)
+    co = torch.randn(2, layer.num_out, layer.num_coeffs, generator=gen, dtype=torch.float64).requires_grad_(True)
+    out = layer(img, co)
+    ref = O.channel_poly(img, co, degree)
+    assert out.shape == ref.shape == (2, layer.num_out, 6, 7)
+    assert torch.allclose(out, ref, rtol=1e-12, atol=1e-12)
+    gout = torch.randn(out.shape, generator=gen, dtype=torch.float64)
+    g = torch.autograd.grad((out * gout).sum(), (img, co))
+    gr = torch.autograd.grad((ref * gout).sum(), (img, co))
+    for a, b in zip(g, gr):
+        assert torch.allclose(a, b, rtol=1e-10, atol=1e-12)
+    with pytest.raises(ValueError, match="variable per channel"):
+        layer(torch.rand(2, nv + 1, 6, 7), co)
+    with pytest.raises(ValueError, match="coeffs"):
+        layer(img, co[:, :, :-1] if layer.num_coeffs > 1 else co[:, :, :0])
+    if (degree, nv) == (4, 5):
+        mob = curl_b200.Deg4MobilePolyLayer()
+        assert torch.equal(mob(img, co), out)
+
+
 def test_curlloss_api():
     """CURLLoss / MSSSIMMetric (reference model.py:36-118, metric.py:75-214): constructor, attributes,
     state-dict keys; MS-SSIM (the library part of the loss) equals the oracle's on CPU; the fused
