@@ -264,6 +264,9 @@ __device__ __forceinline__ void stage_curves(const KParams& p, int b, float* s_C
 // ---------------------------------------------------------------------------------------------
 // Forward
 // ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void l2_prefetch(const void* gptr, unsigned bytes) {   // bytes: multiple of 16, gptr 16-byte aligned
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gptr), "r"(bytes) : "memory");
+}
 #ifdef FWD_MIN_BLOCKS
 #define FWD_BOUNDS __launch_bounds__(THREADS, FWD_MIN_BLOCKS)
 #else
@@ -332,6 +335,21 @@ __global__ void FWD_BOUNDS fwd_kernel(const KParams p) {
   for (int i = (blockIdx.x * THREADS + threadIdx.x) * VEC; i < HW; i += stride) {
     const G c0 = G::ld(in + i), c1 = G::ld(in + HW + i), c2 = G::ld(in + 2 * (size_t)HW + i);
     const G m = load_mask<MK, VEC>(p.mask, (size_t)b * HW + i);
+#ifdef FWD_L2PF
+    if constexpr (VEC == 4) {
+      // the lines this warp reads in its NEXT iteration, asked into L2 now by one lane (no registers held, unlike a
+      // register prefetch): 32 lanes x 16 B = 512 B per plane
+      const int nb = i - (int)(threadIdx.x & 31) * VEC + stride;
+      if ((threadIdx.x & 31) == 0 && nb < HW) {
+        const int npx = min(32 * VEC, HW - nb) & ~15;
+        if (npx > 0) {
+          l2_prefetch(in + nb, npx * 4u); l2_prefetch(in + HW + nb, npx * 4u); l2_prefetch(in + 2 * (size_t)HW + nb, npx * 4u);
+          if (MK == MASK_U8) l2_prefetch(reinterpret_cast<const unsigned char*>(p.mask) + (size_t)b * HW + nb, (unsigned)npx);
+          if (MK == MASK_F32) l2_prefetch(reinterpret_cast<const float*>(p.mask) + (size_t)b * HW + nb, npx * 4u);
+        }
+      }
+    }
+#endif
     G o0, o1, o2;
 #pragma unroll
     for (int v = 0; v < G::LANES; ++v) {
