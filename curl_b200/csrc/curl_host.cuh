@@ -43,5 +43,18 @@ static inline bool ensure_dyn_smem(size_t bytes) {
   return true;
 }
 
+// Test hook (curl_test_set_grid_cap): when > 0, no layer / colour / curve / TriSpace kernel is launched with more than
+// this many blocks per image, so that SMALL test images drive every block through several loop iterations (ring-stage
+// reuse, mbarrier parity flips, grid-stride steps, several tiles per block) -- the code paths the large benchmark
+// shapes run.  0 (the default) leaves the launch shapes alone.  One instance per shared object: weak (every
+// translation unit of the library defines it, the linker keeps one) and hidden (two copies of the library loaded
+// side by side, as dev/kbench.py does, do not share it).
+__attribute__((weak, visibility("hidden"))) int g_test_grid_cap = 0;
+
+static inline int apply_grid_cap(long long n) {
+  if (g_test_grid_cap > 0 && n > g_test_grid_cap) n = g_test_grid_cap;
+  return (int)(n < 1 ? 1 : n);
+}
+
 }  // namespace host
 }  // namespace curl

@@ -1046,15 +1046,7 @@ __global__ void __launch_bounds__(THREADS) fwd_tma_kernel(const KParams p) {
 using host::sm_count;
 using host::ensure_dyn_smem;
 
-// Test hook (curl_test_set_grid_cap): when > 0, no kernel of this translation unit is launched with more
-// than this many blocks per image, so that SMALL test images drive every block through several loop
-// iterations (ring-stage reuse, mbarrier parity flips, grid-stride steps) -- the code paths the large
-// benchmark shapes run.  0 (the default) leaves the launch shapes alone.
-static int g_grid_cap = 0;
-static int apply_grid_cap(long long n) {
-  if (g_grid_cap > 0 && n > g_grid_cap) n = g_grid_cap;
-  return (int)(n < 1 ? 1 : n);
-}
+using host::apply_grid_cap;   // test hook, see curl_host.cuh
 
 static int blocks_per_image(int B, int HW, int vec, int blocks_per_sm) {
   const long long tiles = ((long long)HW + (long long)THREADS * vec - 1) / ((long long)THREADS * vec);
@@ -1179,8 +1171,8 @@ extern "C" {
 int curl_abi_version(void) { return CURL_ABI_VERSION; }
 
 int curl_test_set_grid_cap(int max_blocks_per_image) {
-  const int old = g_grid_cap;
-  g_grid_cap = max_blocks_per_image > 0 ? max_blocks_per_image : 0;
+  const int old = host::g_test_grid_cap;
+  host::g_test_grid_cap = max_blocks_per_image > 0 ? max_blocks_per_image : 0;
   return old;
 }
 

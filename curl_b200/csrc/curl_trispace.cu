@@ -395,7 +395,7 @@ static int grid_x(int B, int HW, int px_per_block, int blocks_per_sm) {
   const long long tiles = ((long long)HW + px_per_block - 1) / px_per_block;
   long long cap = ((long long)sm_count() * blocks_per_sm + B - 1) / B;
   long long n = tiles < cap ? tiles : cap;
-  return (int)(n < 1 ? 1 : n);
+  return host::apply_grid_cap(n);          // test hook (curl_test_set_grid_cap), a no-op by default
 }
 constexpr int FWD_BLOCKS_PER_SM = 16;
 constexpr int BWD_BLOCKS_PER_SM = 12;   // 3 resident blocks per SM (73 KB of shared memory each) x 4 waves

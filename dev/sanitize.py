@@ -72,6 +72,17 @@ for spatial in (True, False):
         coefs = [(0.3 * torch.randn(2, 3, nc, generator=g, device=dev)).requires_grad_(True) for _ in range(3)]
         tri.generate_residual(rnd(2, 3, 48, 40), *coefs).sum().backward()
         tri.generate_residual(rnd(1, 3, 33, 37), *[c[:1] for c in coefs]).sum().backward()
+        # image gradient too (curl_trispace_bwd_img_f32), fused clamp, vector and scalar paths
+        tri._fused(rnd(2, 3, 48, 40).requires_grad_(True), *coefs, True).sum().backward()
+        tri._fused(rnd(1, 3, 33, 37).requires_grad_(True), *[c[:1].detach() for c in coefs], True).sum().backward()
+        with torch.no_grad():                                   # inference forward (no saved sigmoids: the rolled variant)
+            tri._fused(rnd(2, 3, 48, 40), *coefs, True)
+# lower polynomial degrees
+for degree in (1, 2, 3):
+    for spatial in (True, False):
+        tri = curl_b200.TriSpaceRegNet(polynomial_order=degree, spatial=spatial, backbone=nn.Identity()).to(dev)
+        coefs = [(0.3 * torch.randn(2, 3, tri.num_coeffs, generator=g, device=dev)).requires_grad_(True) for _ in range(3)]
+        tri._fused(rnd(2, 3, 48, 40).requires_grad_(True), *coefs, True).sum().backward()
 
 # CURLLoss colour terms + whole criterion
 pred = rnd(2, 3, 64, 96).requires_grad_(True)

@@ -61,7 +61,7 @@ const char* curl_strerror(int code);
 
 /*
  * TEST HOOK, not part of the reference-facing surface (the reference has nothing like it): caps the
- * number of blocks per image every layer / colour / curve kernel is launched with (0 = no cap, the
+ * number of blocks per image every layer / colour / curve / TriSpace kernel is launched with (0 = no cap, the
  * default) and returns the previous cap.  With a small cap a SMALL image drives each block through
  * many tiles -- shared-memory ring reuse, mbarrier parity flips, grid-stride steps -- so the parity
  * tests can compare exactly the loop structure the 4K benchmark shapes run against the CPU oracle.

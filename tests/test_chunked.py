@@ -37,3 +37,27 @@ def test_chunked_oracle_equals_plain(maskkind, dtype):
         for k in ("gL", "gR", "gH"):
             r = ref[k].double().numpy()
             assert np.abs(got[k] - r).max() <= 20 * tol * np.abs(r).max(), (k, rows)
+
+
+@pytest.mark.parametrize("spatial,degree", [(True, 4), (False, 4), (True, 2)])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
+def test_chunked_trispace_oracle_equals_plain(spatial, degree, dtype):
+    """The row-chunked TriSpace oracle (its own coordinate planes: y = row / H of the whole image) against
+    O.trispace_fwd_bwd on the whole image."""
+    from chunked import trispace_fwd_bwd_chunked
+    gen = torch.Generator().manual_seed(11)
+    B, H, W = 2, 23, 19
+    nc = len(O.poly_powers(degree, 5 if spatial else 3))
+    img = torch.rand(B, 3, H, W, generator=gen)
+    R, L, Hc = (0.3 * torch.randn(B, 3, nc, generator=gen) for _ in range(3))
+    gout = torch.randn(B, 3, H, W, generator=gen)
+    for clamp in (True, False):
+        ref = O.trispace_fwd_bwd(img.to(dtype), R.to(dtype), L.to(dtype), Hc.to(dtype), gout.to(dtype), degree, spatial, clamp)
+        for rows in (4, 23):
+            got = trispace_fwd_bwd_chunked(img, R, L, Hc, gout, degree, spatial, clamp, dtype=dtype, rows=rows)
+            tol = 3e-6 if dtype == torch.float32 else 1e-12
+            r = ref["out"].numpy()
+            assert np.abs(got["out"] - r).max() <= tol * max(1.0, np.abs(r).max()), (clamp, rows)
+            for k in ("gR", "gL", "gH"):
+                r = ref[k].double().numpy()
+                assert np.abs(got[k] - r).max() <= 20 * tol * np.abs(r).max(), (k, clamp, rows)

@@ -200,3 +200,93 @@ def test_capped_grid_stage_kernels(grid_cap):
             assert parity.rel_to_max(a.cpu().numpy(), b.cpu().numpy()) <= 2e-6, i
         else:
             assert torch.equal(a, b), i
+
+
+# ---- TriSpace residual: the same two kinds of test ----------------------------------------------------------
+
+def _tri_inputs(B, H, W, spatial, degree, seed):
+    from oracle import curl_oracle as O
+    gen = torch.Generator().manual_seed(seed)
+    nc = len(O.poly_powers(degree, 5 if spatial else 3))
+    img = torch.rand(B, 3, H, W, generator=gen)
+    co = [0.3 * torch.randn(B, 3, nc, generator=gen) for _ in range(3)]
+    gout = torch.randn(B, 3, H, W, generator=gen)
+    return img, co, gout
+
+
+def _tri_gpu(img, co, gout, spatial, degree, save=True, want_gimg=True):
+    import curl_b200
+    import torch.nn as nn
+    dev = torch.device("cuda:0")
+    net = curl_b200.TriSpaceRegNet(polynomial_order=degree, spatial=spatial, backbone=nn.Identity()).to(dev)
+    net.save_activations = save
+    x = img.to(dev).requires_grad_(want_gimg)
+    a = [c.to(dev).requires_grad_(True) for c in co]
+    out = net._fused(x, *a, True)
+    out.backward(gout.to(dev))
+    res = dict(out=out.detach(), gR=a[0].grad, gL=a[1].grad, gH=a[2].grad)
+    if want_gimg:
+        res["gimg"] = x.grad
+    return {k: v.cpu().numpy() for k, v in res.items()}
+
+
+def _tri_check(got, r32, r64, rep):
+    own = np.abs(r32["out"] - r64["out"]).max()
+    e64 = np.abs(got["out"] - r64["out"])
+    rep["out_max_vs_ref64"] = float(e64.max()); rep["ref32_vs_ref64_max"] = float(own)
+    assert e64.max() <= max(2e-5, 3 * own), rep
+    rep["out_frac_over_1e5_vs_ref32"] = float((np.abs(got["out"] - r32["out"]) > 1e-5 * np.maximum(1.0, np.abs(r64["out"]))).mean())
+    assert rep["out_frac_over_1e5_vs_ref32"] <= 2e-3, rep
+    for k in ("gR", "gL", "gH"):
+        rep[k] = parity.rel_to_max(got[k], r64[k])
+        assert rep[k] <= max(1e-4, 3 * parity.rel_to_max(r32[k], r64[k])), (k, rep)
+    parity.check_trispace_gimg(got["gimg"], r32["gimg"], r64["gimg"], rep)
+
+
+TRI_CAPPED = [("spatial_d4_cap3", (2, 72, 100), True, 4, 3), ("rgb_d4_cap2", (1, 96, 128), False, 4, 2),
+              ("spatial_d2_odd_cap1", (1, 37, 53), True, 2, 1), ("rgb_d3_cap1", (2, 40, 52), False, 3, 1)]
+
+
+@pytest.mark.parametrize("name,shape,spatial,degree,cap", TRI_CAPPED, ids=[c[0] for c in TRI_CAPPED])
+def test_trispace_capped_grid_vs_oracle(name, shape, spatial, degree, cap, grid_cap):
+    """Forward, coefficient-gradient and image-gradient kernels with a few blocks per image (every block takes many
+    grid-stride steps / tiles): bit-identical to the uncapped launch where the result is element-wise, and against
+    the oracle (whole image, fp32 and fp64)."""
+    from chunked import trispace_fwd_bwd_chunked
+    B, H, W = shape
+    img, co, gout = _tri_inputs(B, H, W, spatial, degree, 900 + H)
+    r32 = trispace_fwd_bwd_chunked(img, *co, gout, degree, spatial, True, dtype=torch.float32, rows=H)
+    r64 = trispace_fwd_bwd_chunked(img, *co, gout, degree, spatial, True, dtype=torch.float64, rows=H)
+    free = _tri_gpu(img, co, gout, spatial, degree)
+    assert grid_cap(cap) == 0
+    capped = _tri_gpu(img, co, gout, spatial, degree)
+    capped_recompute = _tri_gpu(img, co, gout, spatial, degree, save=False)
+    assert grid_cap(0) == cap
+    for k in ("out", "gimg"):
+        assert np.array_equal(capped[k], free[k]), k
+        assert np.array_equal(capped_recompute[k], free[k]), k
+    for k in ("gR", "gL", "gH"):
+        assert np.array_equal(capped[k], capped_recompute[k]), k          # saved == recomputed sigmoids
+        assert parity.rel_to_max(capped[k], free[k]) <= 2e-6, k           # only the fold order of the partials differs
+    rep = dict(shape=list(shape), spatial=spatial, degree=degree, cap=cap)
+    _tri_check(capped, r32, r64, rep)
+    REPORT["trispace.capped." + name] = rep
+
+
+TRI_FULL = [("rgb_d4_1080p", (1, 1080, 1920), False, 4, 32), ("spatial_d4_360p", (1, 360, 640), True, 4, 8)]
+
+
+@pytest.mark.parametrize("name,shape,spatial,degree,rows", TRI_FULL, ids=[c[0] for c in TRI_FULL])
+def test_trispace_fullsize_vs_oracle(name, shape, spatial, degree, rows):
+    """Uncapped launches at image sizes where the forward grid-strides and the backward blocks take several tiles
+    (2 Mpx at 35 coefficients), and where x = column / W, y = row / H run over realistic ranges (126 coefficients),
+    against the oracle evaluated in row chunks (tests/chunked.py)."""
+    from chunked import trispace_fwd_bwd_chunked
+    B, H, W = shape
+    img, co, gout = _tri_inputs(B, H, W, spatial, degree, 77 + H)
+    r32 = trispace_fwd_bwd_chunked(img, *co, gout, degree, spatial, True, dtype=torch.float32, rows=rows)
+    r64 = trispace_fwd_bwd_chunked(img, *co, gout, degree, spatial, True, dtype=torch.float64, rows=rows)
+    got = _tri_gpu(img, co, gout, spatial, degree)
+    rep = dict(shape=list(shape), spatial=spatial, degree=degree)
+    _tri_check(got, r32, r64, rep)
+    REPORT["trispace." + name] = rep
