@@ -237,9 +237,12 @@ def _tri_check(got, r32, r64, rep):
     assert e64.max() <= max(2e-5, 3 * own), rep
     rep["out_frac_over_1e5_vs_ref32"] = float((np.abs(got["out"] - r32["out"]) > 1e-5 * np.maximum(1.0, np.abs(r64["out"]))).mean())
     assert rep["out_frac_over_1e5_vs_ref32"] <= 2e-3, rep
+    n_px = got["out"].shape[2] * got["out"].shape[3]
     for k in ("gR", "gL", "gH"):
-        rep[k] = parity.rel_to_max(got[k], r64[k])
-        assert rep[k] <= max(1e-4, 3 * parity.rel_to_max(r32[k], r64[k])), (k, rep)
+        # a coefficient gradient is a random-walk sum over the image (gout is randn): one pixel whose final-clamp gate
+        # flips between two roundings is worth ~ 1/sqrt(n) of it (7e-4 at 2 Mpx; seen in rgb_d4_1080p, where the
+        # reference's own fp32 run is 3e-4 from its fp64 one) -- the same flip allowance as for the layer's knots
+        rep[k] = parity.check_knots_stat(got[k], r32[k], r64[k], n_pixels=n_px)
     parity.check_trispace_gimg(got["gimg"], r32["gimg"], r64["gimg"], rep)
 
 
