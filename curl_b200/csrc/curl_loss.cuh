@@ -87,6 +87,11 @@ CURL_HD T cos_sim3(const T p[3], const T t[3], T pn[3], T tn[3], T* np2_out, T* 
   return vfma(pn[2], tn[2], vfma(pn[1], tn[1], vmul(pn[0], tn[0])));
 }
 
+#ifdef CURL_LOSS_FWD_SHARED
+constexpr bool LOSS_FWD_DIRECT = false;
+#else
+constexpr bool LOSS_FWD_DIRECT = true;
+#endif
 // Forward: the four per-pixel terms and the two Lab L values (for MS-SSIM, model.py:101-103).
 template <class T>
 CURL_HD void loss_terms_fwd(const T pred[3], const T target[3], T m, T s[4], T* L_pred, T* L_target) {
@@ -97,8 +102,10 @@ CURL_HD void loss_terms_fwd(const T pred[3], const T target[3], T m, T s[4], T* 
   T pn[3], tn[3], np2, ip;
   s[1] = cos_sim3(p, t, pn, tn, &np2, &ip);
   T lp[3], lt[3];
-  rgb2lab_fwd<T, false>(p, lp, nullptr);
-  rgb2lab_fwd<T, false>(t, lt, nullptr);
+  // forward only: the powers in their direct form 2^(p lg x) (see rgb2lab_fwd), the same for both images so that
+  // identical pixels give identical Lab values; the backward keeps the form that shares its powers with the derivative
+  rgb2lab_fwd<T, false, LOSS_FWD_DIRECT>(p, lp, nullptr);
+  rgb2lab_fwd<T, false, LOSS_FWD_DIRECT>(t, lt, nullptr);
 #pragma unroll
   for (int c = 0; c < 3; ++c) { lp[c] = vsat(lp[c]); lt[c] = vsat(lt[c]); }                 // model.py:58
   s[2] = vadd(vadd(vabs(vsub(lp[0], lt[0])), vabs(vsub(lp[1], lt[1]))), vabs(vsub(lp[2], lt[2])));
