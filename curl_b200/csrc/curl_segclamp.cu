@@ -3,11 +3,11 @@
 // lookup is a per-pixel gather from the knot table in shared memory.
 //
 // Knot gradients are a per-segment (binned) reduction: every warp owns a private histogram
-// [2][total knots] in shared memory and adds with shared-memory atomics (conflicts only between
-// lanes of one warp that fall in the same segment); the block folds its warps' histograms into one
-// partial row, takes an atomic ticket, and the image's last block folds all rows in a fixed order
-// in double.  The shared-memory float atomics make the LAST BITS run-to-run dependent (the order of
-// same-bin additions inside a warp is not fixed) -- unlike the default path, which is bit-reproducible.
+// [2][total knots] in shared memory and adds to it WITHOUT atomics, in an order fixed by the lane
+// numbers (WarpBins below); the block folds its warps' histograms into one partial row, takes an
+// atomic ticket, and the image's last block folds all rows in a fixed order in double.  Like the
+// default path, the result is bit-reproducible from run to run (round 1 used shared-memory float
+// atomics here, which are not).
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -36,7 +36,6 @@ struct SParams {
   float* partials;       // bwd: [B][gridDim.x][2*NK]
   unsigned* tickets;     // bwd: [B]
   int HW;
-  int rep;               // bwd: histogram copies per warp (lane % rep picks one): divides same-bin conflicts
 };
 
 __host__ __device__ inline int total_knots(const int K[3]) { return 3 * K[0] + 3 * K[1] + 4 * K[2]; }
@@ -94,14 +93,53 @@ __global__ void __launch_bounds__(THREADS) seg_fwd_kernel(const SParams p) {
   }
 }
 
+// Segment bins of one WARP (a private copy in shared memory), updated WITHOUT atomics and in an order that depends only
+// on which lane holds which pixel -- the knot gradients are bit-reproducible from run to run (round 1 used
+// shared-memory float atomics, whose order is not).  add() is called by all 32 lanes together.  Lanes that hit the
+// same bin (match_any) are ranked by lane number; then either
+//   * the groups are small (random content: 32 lanes over K - 1 bins): rank r of every group adds in round r --
+//     within a round each bin has at most one writer -- max-group-size rounds of one plain read-modify-write, or
+//   * a few bins hold most lanes (smooth content): one butterfly reduction per distinct bin, written by its first lane.
+// Both orders are fixed by the lane numbers; which one runs (the cheaper by instruction count) depends on the data only.
 struct WarpBins {
-  float* A;          // this lane's copy of its warp's histogram: A[NK], then B[NK]
-  float* B;
+  float2* AB;        // this warp's histogram: {A_j, B_j} per bin, one 64-bit read-modify-write per update
   const int* off;
+  int lane;
+#ifndef SEG_ROUND_COST
+#define SEG_ROUND_COST 8
+#endif
+#ifndef SEG_LEADER_COST
+#define SEG_LEADER_COST 26
+#endif
+  static constexpr int ROUND_COST = SEG_ROUND_COST, LEADER_COST = SEG_LEADER_COST;
   __device__ __forceinline__ void add(int curve, int j, float a, float b) {
-    if (a != 0.0f || b != 0.0f) {
-      atomicAdd(&A[off[curve] + j], a);
-      atomicAdd(&B[off[curve] + j], b);
+    constexpr unsigned FULL = 0xffffffffu;
+    const bool active = (a != 0.0f) || (b != 0.0f);
+    if (!__any_sync(FULL, active)) return;
+    const int idx = off[curve] + j;
+    const unsigned peers = __match_any_sync(FULL, active ? idx : 0x10000 + lane);   // idle lanes: groups of one
+    const int rank = __popc(peers & ((1u << lane) - 1u));
+    const int maxg = __reduce_max_sync(FULL, active ? __popc(peers) : 0);
+    const unsigned leaders = __ballot_sync(FULL, active && rank == 0);          // the first lane of every group
+    // a round costs about 8 instructions, a butterfly reduction about 26: take the cheaper order
+    if (maxg * ROUND_COST <= __popc(leaders) * LEADER_COST) {
+      for (int r = 0; r < maxg; ++r) {
+        if (active && rank == r) { float2 v = AB[idx]; v.x += a; v.y += b; AB[idx] = v; }
+        __syncwarp();
+      }
+    } else {
+      unsigned todo = leaders;
+      while (todo) {
+        const int leader = __ffs(todo) - 1;
+        const int key = __shfl_sync(FULL, idx, leader);
+        const bool mine = active && idx == key;
+        float va = mine ? a : 0.0f, vb = mine ? b : 0.0f;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { va += __shfl_xor_sync(FULL, va, o); vb += __shfl_xor_sync(FULL, vb, o); }
+        if (lane == leader) { float2 v = AB[key]; v.x += va; v.y += vb; AB[key] = v; }
+        todo &= todo - 1;
+      }
+      __syncwarp();
     }
   }
 };
@@ -113,27 +151,32 @@ __global__ void __launch_bounds__(THREADS) seg_bwd_kernel(const SParams p) {
   __shared__ unsigned s_ticket;
   const int NK = total_knots(p.K), NB = 2 * NK;
   double* s_bins = reinterpret_cast<double*>(smem);          // [NB], used by the image's last block
-  float* s_C = smem + 2 * NB;                                // [NK]
-  float* s_hist = s_C + NK;                                  // [NWARPS * rep][NB]
-  const int NH = NWARPS * p.rep;
+  float* s_hist = smem + 2 * NB;                             // [NWARPS][NK] {A, B} pairs (8-byte aligned for any NK)
+  float* s_C = s_hist + (size_t)NWARPS * NB;                 // [NK]
+  const int NH = NWARPS;
   const int b = blockIdx.y, HW = p.HW;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   SegCurve cv[LAYER_CURVES];
   for (int i = threadIdx.x; i < NH * NB; i += THREADS) s_hist[i] = 0.0f;
   stage(p, b, s_C, s_off, cv);                               // ends with a barrier
-  // smooth images put most lanes of a warp in the same segment; lane % rep spreads them over rep copies
-  float* mine = s_hist + (size_t)(warp * p.rep + lane % p.rep) * NB;
-  WarpBins bins{mine, mine + NK, s_off};
+  WarpBins bins{reinterpret_cast<float2*>(s_hist + (size_t)warp * NB), s_off, lane};
   const float* in = p.img + (size_t)b * 3 * HW;
   const float* go = p.gout + (size_t)b * 3 * HW;
   float* gin = WANT_GIN ? p.gimg + (size_t)b * 3 * HW : nullptr;
-  for (int i = blockIdx.x * THREADS + threadIdx.x; i < HW; i += gridDim.x * THREADS) {
-    const float x[3] = {__ldcs(in + i), __ldcs(in + HW + i), __ldcs(in + 2 * (size_t)HW + i)};
-    const float g[3] = {__ldcs(go + i), __ldcs(go + HW + i), __ldcs(go + 2 * (size_t)HW + i)};
-    const float m = mask1<MK>(p.mask, (size_t)b * HW + i);
+  // the loop is warp-uniform (bins.add is a warp-wide operation): lanes past the end work on a grey pixel with a
+  // zero upstream gradient, which contributes nothing and is not stored
+  for (int i0 = blockIdx.x * THREADS + warp * 32; i0 < HW; i0 += gridDim.x * THREADS) {
+    const int i = i0 + lane;
+    const bool live = i < HW;
+    float x[3] = {0.5f, 0.5f, 0.5f}, g[3] = {0.0f, 0.0f, 0.0f}, m = 1.0f;
+    if (live) {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) { x[c] = __ldcs(in + (size_t)c * HW + i); g[c] = __ldcs(go + (size_t)c * HW + i); }
+      m = mask1<MK>(p.mask, (size_t)b * HW + i);
+    }
     float gx[3];
     seg_layer_bwd<MK, WANT_GIN>(x, m, cv, g, gx, bins);
-    if (WANT_GIN) {
+    if (WANT_GIN && live) {
 #pragma unroll
       for (int c = 0; c < 3; ++c) __stcs(gin + (size_t)c * HW + i, gx[c]);
     }
@@ -143,7 +186,8 @@ __global__ void __launch_bounds__(THREADS) seg_bwd_kernel(const SParams p) {
   float* row = p.partials + ((size_t)b * gridDim.x + blockIdx.x) * NB;
   for (int k = threadIdx.x; k < NB; k += THREADS) {
     float v = 0.0f;
-    for (int w = 0; w < NH; ++w) v += s_hist[w * NB + k];
+    const int at = k < NK ? 2 * k : 2 * (k - NK) + 1;          // row: A[NK] then B[NK]; histograms: {A, B} pairs
+    for (int w = 0; w < NH; ++w) v += s_hist[w * NB + at];
     row[k] = v;
   }
   __threadfence();
@@ -187,13 +231,7 @@ static int grid_x(int B, int HW, int blocks_per_sm) {
 }
 static size_t tick_bytes(int B) { return ((size_t)B * sizeof(unsigned) + 255) / 256 * 256; }
 static size_t fwd_smem(int NK) { return (size_t)NK * sizeof(float); }
-static size_t bwd_smem(int NK, int rep) { return ((size_t)4 * NK + NK + (size_t)NWARPS * rep * 2 * NK) * sizeof(float); }
-// as many histogram copies per warp as fit in 100 KB per block (two blocks per SM): 8 at the default 160 knots
-static int hist_copies(int NK) {
-  int rep = 8;
-  while (rep > 1 && bwd_smem(NK, rep) > 100 * 1024) rep >>= 1;
-  return rep;
-}
+static size_t bwd_smem(int NK) { return ((size_t)4 * NK + NK + (size_t)NWARPS * 2 * NK) * sizeof(float); }
 constexpr int BWD_BLOCKS_PER_SM = 4;
 
 static int fill(SParams& p, const float* img, const void* mask, int mask_kind, const float* L, int64_t ldL,
@@ -219,13 +257,12 @@ static int fill(SParams& p, const float* img, const void* mask, int mask_kind, c
 template <int MK>
 static int launch_bwd(SParams& p, int B, cudaStream_t st) {
   const int NK = total_knots(p.K);
-  p.rep = hist_copies(NK);
   const dim3 grid(grid_x(B, p.HW, BWD_BLOCKS_PER_SM), B);
   auto kern = p.gimg ? seg_bwd_kernel<MK, true> : seg_bwd_kernel<MK, false>;
-  const bool ok = p.gimg ? host::ensure_dyn_smem<seg_bwd_kernel<MK, true>>(bwd_smem(NK, p.rep))
-                         : host::ensure_dyn_smem<seg_bwd_kernel<MK, false>>(bwd_smem(NK, p.rep));
+  const bool ok = p.gimg ? host::ensure_dyn_smem<seg_bwd_kernel<MK, true>>(bwd_smem(NK))
+                         : host::ensure_dyn_smem<seg_bwd_kernel<MK, false>>(bwd_smem(NK));
   if (!ok) return CURL_ERR_LAUNCH;
-  kern<<<grid, THREADS, bwd_smem(NK, p.rep), st>>>(p);
+  kern<<<grid, THREADS, bwd_smem(NK), st>>>(p);
   return cudaGetLastError() == cudaSuccess ? CURL_OK : CURL_ERR_LAUNCH;
 }
 

@@ -262,7 +262,7 @@ int curl_loss_terms_bwd_f32(const float* pred, const float* target, const void* 
  * everything else -- curve wiring, whole-pixel clamps, regulariser, layer chain, arguments -- is as
  * in curl_layer_fwd_f32 / curl_layer_bwd_f32 above.  Scalar kernels (the segment is a per-pixel
  * lookup); knot gradients are a per-segment reduction through per-warp shared-memory histograms
- * (float atomics: last bits are not run-to-run reproducible), then partial rows + ticket + a
+ * (no atomics: same-bin lanes add in lane order, bit-reproducible), then partial rows + ticket + a
  * fixed-order fold in double.  No reference code exists for this variant: checked against the
  * oracle's restatement of the published formula only (parity unpinned).
  */

@@ -790,6 +790,40 @@ def test_segment_clamp_layer_vs_oracle(shape, maskdtype):
     REPORT[f"segclamp.{shape}"] = rep
 
 
+@pytest.mark.parametrize("content", ["noise", "smooth"])
+def test_segment_clamp_knot_gradients_are_reproducible(content):
+    """The per-segment reduction adds without atomics in an order fixed by the lane numbers: three runs give the same
+    bits.  `smooth` puts most lanes of a warp into one segment (the butterfly path of WarpBins::add), `noise`
+    spreads them (the rank-rounds path); both against the oracle as well."""
+    import curl_b200
+    dev = _dev()
+    B, H, W = 2, 96, 160
+    gen = torch.Generator().manual_seed(5)
+    if content == "noise":
+        img = torch.rand(B, 3, H, W, generator=gen)
+    else:
+        yy = torch.linspace(0, 1, H).reshape(1, 1, H, 1); xx = torch.linspace(0, 1, W).reshape(1, 1, 1, W)
+        img = (0.5 + 0.45 * torch.sin(2.0 * xx + 1.5 * yy + torch.arange(3.0).reshape(1, 3, 1, 1))).expand(B, 3, H, W).contiguous()
+    mask = torch.rand(B, 1, H, W, generator=gen) > 0.1
+    L, R, Hk = (0.1 * torch.randn(B, n, generator=gen) for n in (48, 48, 64))
+    gout, greg = torch.randn(B, 3, H, W, generator=gen), torch.randn(B, generator=gen)
+    layer = curl_b200.CURLLayer(segment_clamp=True).to(dev)
+    runs = []
+    for _ in range(3):
+        xi = img.to(dev).requires_grad_(True)
+        kn = [t.to(dev).requires_grad_(True) for t in (L, R, Hk)]
+        out, reg = layer(xi, mask.to(dev), *kn)
+        torch.autograd.backward([out, reg], [gout.to(dev), greg.to(dev)])
+        runs.append([xi.grad.clone()] + [t.grad.clone() for t in kn])
+    for other in runs[1:]:
+        for a, b_ in zip(runs[0], other):
+            assert torch.equal(a, b_)
+    r64 = O.curl_layer_fwd_bwd(img.double(), mask, L.double(), R.double(), Hk.double(), gout.double(), greg.double(),
+                               segment_clamp=True)
+    for k, v in zip(("gL", "gR", "gH"), runs[0][1:]):
+        assert rel_to_max(v.cpu().numpy(), r64[k].numpy()) <= 5e-3, k
+
+
 def test_segment_clamp_properties_and_errors():
     """With all parameters zero every knot is 1, both curve definitions give scale == 1 and the two
     layers must agree exactly; collinear knots on [0, 1] likewise agree up to rounding; without an
@@ -814,7 +848,7 @@ def test_segment_clamp_properties_and_errors():
     out, reg = seg(xi, mask, *kn)
     (out.sum() + reg.sum()).backward()
     for x, y in zip(g1, [k.grad for k in kn]):
-        assert rel_to_max(x.cpu().numpy(), y.cpu().numpy()) <= 1e-5       # float atomics: not bit-identical
+        assert torch.equal(x, y)       # same bins with and without the image gradient, added in a fixed order
     assert torch.count_nonzero(xi.grad * (~mask)) == 0
     with pytest.raises(ValueError):
         seg(img, mask, kn[0][:, :47], kn[1], kn[2])
