@@ -144,9 +144,13 @@ constexpr bool FWD_DIRECT_SRGB = false;
 #else
 constexpr bool FWD_DIRECT_SRGB = true;     // measured (dev/fwd_accuracy.py): mean |err| vs fp64 1.21e-7 (shared form 1.23e-7), 2.5 % faster
 #endif
-template <class T, bool JAC, bool DIRECT = false>
+// SAT12 (the fused forward only; requires !JAC): a and b leave saturated to [0, 1] -- the pre-clamp of the Lab curves
+// that follow (curves.py:36 after the first curve) taken in the producing multiply-add itself (FFMA.SAT per half
+// instead of FFMA2 + two FADD.SAT: two issue slots less per channel and pixel pair; sat(fl(x)) either way).
+template <class T, bool JAC, bool DIRECT = false, bool SAT12 = false>
 CURL_HD void rgb2lab_fwd(const T x[3], T lab[3], LabJac<T>* jac) {
   static_assert(!(JAC && DIRECT), "the derivative records need the shared form");
+  static_assert(!(JAC && SAT12), "the clamp gates need the unclamped values");
   T lin[3];
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
@@ -191,8 +195,13 @@ CURL_HD void rgb2lab_fwd(const T x[3], T lab[3], LabJac<T>* jac) {
   // sits on the boundary of every clamp(.., 0, 1) downstream, which passes gradient only on the closed
   // interval -- a fused 1.16 fy - 0.16 leaves -3e-9 there and silently blocks the L gradient of black pixels.
   lab[0] = vmul(vsub(f[1], T(k::F_OFF)), T(k::LN_S));
-  lab[1] = vfma(vsub(f[0], f[1]), T(k::AN_S), T(0.5f));      // colors.py:50,58
-  lab[2] = vfma(vsub(f[1], f[2]), T(k::BN_S), T(0.5f));      // colors.py:50,59
+  if (SAT12) {
+    lab[1] = vfma_sat(vsub(f[0], f[1]), T(k::AN_S), T(0.5f));
+    lab[2] = vfma_sat(vsub(f[1], f[2]), T(k::BN_S), T(0.5f));
+  } else {
+    lab[1] = vfma(vsub(f[0], f[1]), T(k::AN_S), T(0.5f));      // colors.py:50,58
+    lab[2] = vfma(vsub(f[1], f[2]), T(k::BN_S), T(0.5f));      // colors.py:50,59
+  }
 }
 
 // FOLD (the fused layer only, see "Units of the fused layer's reverse sweep"): glab arrives as
@@ -226,9 +235,11 @@ struct RgbJac {
   T d_gam[3];   // (d rgb_c / d v_c) / GAM_DK
 };
 
-template <class T, bool JAC, bool DIRECT = false>
+// SAT12: as in rgb2lab_fwd, for the RGB curves that follow -- g and b leave saturated (both branches of the select).
+template <class T, bool JAC, bool DIRECT = false, bool SAT12 = false>
 CURL_HD void lab2rgb_fwd(const T lab[3], T rgb[3], RgbJac<T>* jac) {
   static_assert(!(JAC && DIRECT), "the derivative records need the shared form");
+  static_assert(!(JAC && SAT12), "the clamp gates need the unclamped values");
   T f[3];
   f[1] = vfma(lab[0], T(k::FY_S), T(k::FY_O));                    // colors.py:97,104
   f[0] = vfma(lab[1], T(k::FX_S), vadd(f[1], T(k::FX_O)));        // colors.py:98,104
@@ -261,8 +272,10 @@ CURL_HD void lab2rgb_fwd(const T lab[3], T rgb[3], RgbJac<T>* jac) {
       e = vex2(vmul(vlg2(v[c]), T(k::GAM_E)));                     // v^(1/2.4 - 1)
       pw = vmul(v[c], e);
     }
-    const T hi = vfma(pw, T(1.055f), T(-0.055f));
-    rgb[c] = vsel_le(v[c], T(k::LIN_T), vmul(v[c], T(k::LIN_SLOPE)), hi);
+    const bool sat = SAT12 && c > 0;
+    const T hi = sat ? vfma_sat(pw, T(1.055f), T(-0.055f)) : vfma(pw, T(1.055f), T(-0.055f));
+    const T lo = sat ? vmul_sat(v[c], T(k::LIN_SLOPE)) : vmul(v[c], T(k::LIN_SLOPE));
+    rgb[c] = vsel_le(v[c], T(k::LIN_T), lo, hi);
     if (JAC) jac->d_gam[c] = vsel_le(v[c], T(k::LIN_T), T(k::LIN_SLOPE_BY_DK), e);               // (d rgb / d v) / GAM_DK
   }
 }
@@ -336,12 +349,14 @@ CURL_HD void rgb2hsv_fwd(const T x[3], T hsv[3], HsvJac<T>* jac) {
   // colors.py:225-231:  h = (60 hr (+360 if negative)) / 360
   const T h = vfma(hr, T((float)(1.0 / 6.0)), vgate_lt(hr, T(0.0f)));
   const T minv = vmul(dfc, rr);                                // colors.py:234 (mx >= 1e-9, never 0)
-  const T s = vmul(df, minv);                                  // colors.py:235-237
+  const T s = JAC ? vmul(df, minv) : T(0.0f);                  // colors.py:235-237 (the derivative path needs it unclamped)
   // colors.py:240
   // (the upper bound of the hue clamp is inert: hr <= 5 gives h <= 5/6, and a negative hr gives fl(1 + hr/6) <= 1)
   // (the derivative path keeps the inert min so that the backward kernels' code is unchanged)
   hsv[0] = JAC ? vmin(vmax(h, T(k::HSV_LO)), T(1.0f)) : vmax(h, T(k::HSV_LO));
-  hsv[1] = vmin(vmax(s, T(k::HSV_LO)), T(1.0f));
+  // values only: the upper bound inside the multiply (FMUL.SAT per half + one max instead of FMUL2 + min + max);
+  // max(sat(s), LO) == min(max(s, LO), 1) for every s, NaN included
+  hsv[1] = JAC ? vmin(vmax(s, T(k::HSV_LO)), T(1.0f)) : vmax(vmul_sat(df, minv), T(k::HSV_LO));
   hsv[2] = mx;  // already inside [1e-9, 1]
   if (JAC) {
     const T pass_h6 = FOLD ? vgate_eq(hsv[0], h) : vmul(vgate_eq(hsv[0], h), T((float)(1.0 / 6.0)));   // d h / d hr = 60/360
@@ -519,11 +534,13 @@ CURL_HD void single_curve_bwd(const T x[3], int cin, int cout, float alpha, floa
 template <class T>
 struct Self3Jac { CurveJac<T> c[3]; };
 
-template <class T, bool JAC, bool OUT_PIN = false>
+// IN_SAT12 (the fused forward): channels 1 and 2 arrive saturated (rgb2lab_fwd / lab2rgb_fwd <.., SAT12>)
+template <class T, bool JAC, bool OUT_PIN = false, bool IN_SAT12 = false>
 CURL_HD void adjust_self3_fwd(const T x[3], const float* ab, T y[3], Self3Jac<T>* jac) {
+  static_assert(!(JAC && IN_SAT12), "the clamp gates need the unclamped values");
   y[0] = self_curve_fwd<T, JAC, false, OUT_PIN>(x[0], ab[0], ab[1], JAC ? &jac->c[0] : nullptr);
-  y[1] = self_curve_fwd<T, JAC, true, OUT_PIN>(x[1], ab[2], ab[3], JAC ? &jac->c[1] : nullptr);
-  y[2] = self_curve_fwd<T, JAC, true, OUT_PIN>(x[2], ab[4], ab[5], JAC ? &jac->c[2] : nullptr);
+  y[1] = self_curve_fwd<T, JAC, !IN_SAT12, OUT_PIN>(x[1], ab[2], ab[3], JAC ? &jac->c[1] : nullptr);
+  y[2] = self_curve_fwd<T, JAC, !IN_SAT12, OUT_PIN>(x[2], ab[4], ab[5], JAC ? &jac->c[2] : nullptr);
 }
 
 template <class T>
@@ -624,14 +641,19 @@ constexpr int LAYER_CURVES = 10;
 template <class T>
 CURL_HD void vscale3(T a[3], T m) { a[0] = vmul(a[0], m); a[1] = vmul(a[1], m); a[2] = vmul(a[2], m); }
 
+#ifdef CURL_FWD_NO_SAT12
+constexpr bool FWD_SAT12 = false;
+#else
+constexpr bool FWD_SAT12 = true;      // the curves' pre-clamps taken inside the producing conversions (bit-identical)
+#endif
 template <class T, int MK>
 CURL_HD void layer_fwd(const T x[3], T m, const float* ab, T out[3]) {
   T lab[3], lab2[3], rgb[3], rgb2[3], hsv[3], hsv2[3], res[3];
-  rgb2lab_fwd<T, false, true>(x, lab, nullptr);
-  adjust_self3_fwd<T, false>(lab, ab, lab2, nullptr);
+  rgb2lab_fwd<T, false, true, FWD_SAT12>(x, lab, nullptr);
+  adjust_self3_fwd<T, false, false, FWD_SAT12>(lab, ab, lab2, nullptr);
   if (MK == MASK_F32) vscale3(lab2, m);
-  lab2rgb_fwd<T, false, true>(lab2, rgb, nullptr);
-  adjust_self3_fwd<T, false>(rgb, ab + 6, rgb2, nullptr);
+  lab2rgb_fwd<T, false, true, FWD_SAT12>(lab2, rgb, nullptr);
+  adjust_self3_fwd<T, false, false, FWD_SAT12>(rgb, ab + 6, rgb2, nullptr);
   if (MK == MASK_F32) vscale3(rgb2, m);
   rgb2hsv_fwd<T, false, MK != MASK_F32>(rgb2, hsv, nullptr);
   adjust_hsv_fwd<T, false, true>(hsv, ab + 12, hsv2, nullptr);
