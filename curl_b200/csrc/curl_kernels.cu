@@ -367,12 +367,14 @@ __global__ void FWD_BOUNDS fwd_kernel(const KParams p) {
 // 3 B/px in, 3 B/px out (+ the mask).  VEC == 4: four consecutive pixels per thread (32-bit
 // accesses per plane, or three 32-bit words of an interleaved row); VEC == 1: any size/alignment.
 // ---------------------------------------------------------------------------------------------
-// byte k of w as the float 2^23 + byte (one PRMT; I2F would go through the MUFU pipe, which is the
-// forward kernel's bottleneck); the caller subtracts 2^23, which is exact.
-__device__ __forceinline__ float byte_of(unsigned w, int k) {
-  return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7650u + k));
-}
-constexpr float TWO23 = 8388608.0f;
+// An 8-bit channel has 256 possible values, so x = u8 / 255 (u8_to_unit) and its sRGB linearisation
+// (srgb_linearise_fwd: 2 of the layer's 19 MUFU per channel and pixel on the kernel's busiest pipe) come from two
+// 256-entry tables in shared memory, filled in the block prologue by the SAME device functions the fp32 kernel
+// evaluates per pixel -- bit-identical by construction (tests: the 8-bit kernel must equal the quantised fp32 kernel
+// exactly).  Per channel and pixel: one PRMT (the byte as an index) and two LDS.32 instead of PRMT + the 2^23 trick +
+// u8_to_unit (3 packed) + the linearisation (3 packed, 2 MUFU, compare + select): ~19 instructions and 6 MUFU per
+// pixel less.  The look-ups are data-dependent (bank conflicts happen); the LSU pipe is otherwise idle here.
+__device__ __forceinline__ unsigned byte_at(unsigned w, int k) { return __byte_perm(w, 0u, 0x4440u + k); }
 
 template <int MK, bool IN_HWC, bool OUT_HWC, int VEC>
 __global__ void __launch_bounds__(THREADS) fwd_u8_kernel(const KParams p) {
@@ -380,10 +382,16 @@ __global__ void __launch_bounds__(THREADS) fwd_u8_kernel(const KParams p) {
   __shared__ float s_C[CURL_MAX_KNOTS];
   __shared__ float s_ab[2 * NC];
   __shared__ double s_reg[NC];
+  __shared__ float s_unit[256], s_lin[256];
   const int b = blockIdx.y;
+  for (int t = threadIdx.x; t < 256; t += THREADS) {
+    const float x = u8_to_unit((float)t);
+    s_unit[t] = x;
+    s_lin[t] = srgb_linearise_fwd(x);
+  }
   {
     const bool owner = (blockIdx.x == 0) && (p.reg != nullptr);
-    stage_curves<OpLayer, false>(p, b, s_C, s_ab, s_reg, owner);
+    stage_curves<OpLayer, false>(p, b, s_C, s_ab, s_reg, owner);      // ends with a barrier: the tables are visible too
     if (owner && threadIdx.x == 0) {
       double r = 0.0;
       for (int j = 0; j < NC; ++j) r += s_reg[j];
@@ -396,30 +404,33 @@ __global__ void __launch_bounds__(THREADS) fwd_u8_kernel(const KParams p) {
   const int stride = gridDim.x * THREADS * VEC;
   for (int i = (blockIdx.x * THREADS + threadIdx.x) * VEC; i < HW; i += stride) {
     if constexpr (VEC == 4) {
-      float ch[3][4];
+      unsigned ch[3][4];
       if (IN_HWC) {
         const unsigned* w = reinterpret_cast<const unsigned*>(in + 3 * (size_t)i);
         const unsigned w0 = __ldcs(w), w1 = __ldcs(w + 1), w2 = __ldcs(w + 2);   // r0 g0 b0 r1 | g1 b1 r2 g2 | b2 r3 g3 b3
-        ch[0][0] = byte_of(w0, 0); ch[1][0] = byte_of(w0, 1); ch[2][0] = byte_of(w0, 2);
-        ch[0][1] = byte_of(w0, 3); ch[1][1] = byte_of(w1, 0); ch[2][1] = byte_of(w1, 1);
-        ch[0][2] = byte_of(w1, 2); ch[1][2] = byte_of(w1, 3); ch[2][2] = byte_of(w2, 0);
-        ch[0][3] = byte_of(w2, 1); ch[1][3] = byte_of(w2, 2); ch[2][3] = byte_of(w2, 3);
+        ch[0][0] = byte_at(w0, 0); ch[1][0] = byte_at(w0, 1); ch[2][0] = byte_at(w0, 2);
+        ch[0][1] = byte_at(w0, 3); ch[1][1] = byte_at(w1, 0); ch[2][1] = byte_at(w1, 1);
+        ch[0][2] = byte_at(w1, 2); ch[1][2] = byte_at(w1, 3); ch[2][2] = byte_at(w2, 0);
+        ch[0][3] = byte_at(w2, 1); ch[1][3] = byte_at(w2, 2); ch[2][3] = byte_at(w2, 3);
       } else {
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
           const unsigned w = __ldcs(reinterpret_cast<const unsigned*>(in + (size_t)c * HW + i));
 #pragma unroll
-          for (int k = 0; k < 4; ++k) ch[c][k] = byte_of(w, k);
+          for (int k = 0; k < 4; ++k) ch[c][k] = byte_at(w, k);
         }
       }
       const Group<4> m = load_mask<MK, 4>(p.mask, (size_t)b * HW + i);
       unsigned o[3][4];
 #pragma unroll
       for (int v = 0; v < 2; ++v) {
-        F2 x[3], y[3];
+        F2 x[3], lin[3], y[3];
 #pragma unroll
-        for (int c = 0; c < 3; ++c) x[c] = u8_to_unit(vadd(F2(ch[c][2 * v], ch[c][2 * v + 1]), F2(-TWO23)));
-        layer_fwd<F2, MK>(x, m.v[v], s_ab, y);
+        for (int c = 0; c < 3; ++c) {
+          x[c] = F2(s_unit[ch[c][2 * v]], s_unit[ch[c][2 * v + 1]]);
+          lin[c] = F2(s_lin[ch[c][2 * v]], s_lin[ch[c][2 * v + 1]]);
+        }
+        layer_fwd<F2, MK, true>(x, m.v[v], s_ab, y, lin);
 #pragma unroll
         for (int c = 0; c < 3; ++c) { o[c][2 * v] = unit_to_u8(y[c].lo()); o[c][2 * v + 1] = unit_to_u8(y[c].hi()); }
       }
@@ -435,12 +446,14 @@ __global__ void __launch_bounds__(THREADS) fwd_u8_kernel(const KParams p) {
                  o[c][0] | (o[c][1] << 8) | (o[c][2] << 16) | (o[c][3] << 24));
       }
     } else {
-      float x[3], y[3];
+      float x[3], lin[3], y[3];
 #pragma unroll
-      for (int c = 0; c < 3; ++c)
-        x[c] = u8_to_unit((float)__ldcs(in + (IN_HWC ? 3 * (size_t)i + c : (size_t)c * HW + i)));
+      for (int c = 0; c < 3; ++c) {
+        const unsigned v8 = __ldcs(in + (IN_HWC ? 3 * (size_t)i + c : (size_t)c * HW + i));
+        x[c] = s_unit[v8]; lin[c] = s_lin[v8];
+      }
       const Group<1> m = load_mask<MK, 1>(p.mask, (size_t)b * HW + i);
-      layer_fwd<float, MK>(x, m.v[0], s_ab, y);
+      layer_fwd<float, MK, true>(x, m.v[0], s_ab, y, lin);
 #pragma unroll
       for (int c = 0; c < 3; ++c)
         __stcs(out + (OUT_HWC ? 3 * (size_t)i + c : (size_t)c * HW + i), (unsigned char)unit_to_u8(y[c]));

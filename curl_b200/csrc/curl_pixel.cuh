@@ -147,22 +147,32 @@ constexpr bool FWD_DIRECT_SRGB = true;     // measured (dev/fwd_accuracy.py): me
 // SAT12 (the fused forward only; requires !JAC): a and b leave saturated to [0, 1] -- the pre-clamp of the Lab curves
 // that follow (curves.py:36 after the first curve) taken in the producing multiply-add itself (FFMA.SAT per half
 // instead of FFMA2 + two FADD.SAT: two issue slots less per channel and pixel pair; sat(fl(x)) either way).
-template <class T, bool JAC, bool DIRECT = false, bool SAT12 = false>
-CURL_HD void rgb2lab_fwd(const T x[3], T lab[3], LabJac<T>* jac) {
+// sRGB -> linear of one channel, forward-only form (colors.py:37-38); also what fills the 256-entry table of the
+// 8-bit kernel, so that a table entry and the value computed from the same x are the same bits.
+template <class T>
+CURL_HD T srgb_linearise_fwd(T x) {
+  const T u = vfma(x, T(k::SRGB_A), T(k::SRGB_B));
+  T hi;
+  if (FWD_DIRECT_SRGB) hi = vex2(vmul(vlg2(u), T(2.4f)));
+  else hi = vmul(u, vmul(u, vex2(vmul(vlg2(u), T(0.4f)))));
+  return vsel_le(x, T(k::SRGB_T), vmul(x, T(k::SRGB_INV_SLOPE)), hi);
+}
+
+// LIN_IN (the 8-bit forward; requires DIRECT): lin_in holds the three linearised channels (table look-ups), x is not read.
+template <class T, bool JAC, bool DIRECT = false, bool SAT12 = false, bool LIN_IN = false>
+CURL_HD void rgb2lab_fwd(const T x[3], T lab[3], LabJac<T>* jac, const T* lin_in = nullptr) {
   static_assert(!(JAC && DIRECT), "the derivative records need the shared form");
   static_assert(!(JAC && SAT12), "the clamp gates need the unclamped values");
+  static_assert(!LIN_IN || DIRECT, "pre-linearised inputs exist for the forward-only form");
   T lin[3];
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
+    if (LIN_IN) { lin[c] = lin_in[c]; continue; }
+    if (DIRECT) { lin[c] = srgb_linearise_fwd(x[c]); continue; }
     // colors.py:37-38.  In the pow branch x > 0.04045 so the reference's clamp(min=1e-4) is inert.
     const T u = vfma(x[c], T(k::SRGB_A), T(k::SRGB_B));
-    T u14, hi;
-    if (DIRECT && FWD_DIRECT_SRGB) {
-      hi = vex2(vmul(vlg2(u), T(2.4f)));
-    } else {
-      u14 = vmul(u, vex2(vmul(vlg2(u), T(0.4f))));
-      hi = vmul(u, u14);
-    }
+    const T u14 = vmul(u, vex2(vmul(vlg2(u), T(0.4f))));
+    const T hi = vmul(u, u14);
     lin[c] = vsel_le(x[c], T(k::SRGB_T), vmul(x[c], T(k::SRGB_INV_SLOPE)), hi);
     if (JAC) jac->d_lin[c] = vsel_le(x[c], T(k::SRGB_T), T(k::SRGB_INV_SLOPE_BY_DK), u14);   // (d lin / d x) / SRGB_DK
   }
@@ -646,10 +656,10 @@ constexpr bool FWD_SAT12 = false;
 #else
 constexpr bool FWD_SAT12 = true;      // the curves' pre-clamps taken inside the producing conversions (bit-identical)
 #endif
-template <class T, int MK>
-CURL_HD void layer_fwd(const T x[3], T m, const float* ab, T out[3]) {
+template <class T, int MK, bool LIN_IN = false>
+CURL_HD void layer_fwd(const T x[3], T m, const float* ab, T out[3], const T* lin_in = nullptr) {
   T lab[3], lab2[3], rgb[3], rgb2[3], hsv[3], hsv2[3], res[3];
-  rgb2lab_fwd<T, false, true, FWD_SAT12>(x, lab, nullptr);
+  rgb2lab_fwd<T, false, true, FWD_SAT12, LIN_IN>(x, lab, nullptr, lin_in);
   adjust_self3_fwd<T, false, false, FWD_SAT12>(lab, ab, lab2, nullptr);
   if (MK == MASK_F32) vscale3(lab2, m);
   lab2rgb_fwd<T, false, true, FWD_SAT12>(lab2, rgb, nullptr);
