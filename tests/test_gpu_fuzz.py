@@ -170,3 +170,44 @@ def test_trispace_fuzz_vs_oracle(case):
     for k, c in zip(("gR", "gL", "gH"), cg):
         e = rel_to_max(c.grad.cpu().numpy(), r64[k].numpy())
         assert e <= max(1e-4, 4 * rel_to_max(r32[k].numpy(), r64[k].numpy())), (k, e)
+
+
+TRI_FUZZ_DEG = [(int(_rng.randint(1, 3)), int(_rng.randint(2, 60)), int(_rng.randint(2, 80)), bool(_rng.randint(0, 2)),
+                 bool(_rng.randint(0, 2)), int(_rng.randint(1, 5)), bool(_rng.randint(0, 2)), 4000 + _i) for _i in range(10)]
+
+
+@pytest.mark.parametrize("case", TRI_FUZZ_DEG, ids=lambda c: "B%dx%dx%d-sp%d-cl%d-deg%d-save%d" % c[:7])
+def test_trispace_fuzz_degrees_and_image_gradient(case):
+    """Polynomial degrees 1-4 (ChannelPolyLayer is generic in the degree, model.py:206-333) and the image gradient
+    (autograd of model.py:486-508 w.r.t. img) over random shapes, against the oracle."""
+    import curl_b200
+    import torch.nn as nn
+    import parity
+    from chunked import trispace_fwd_bwd_chunked
+    B, H, W, spatial, clamp, degree, save, seed = case
+    dev = torch.device("cuda:0")
+    gen = torch.Generator().manual_seed(seed)
+    img = torch.rand(B, 3, H, W, generator=gen)
+    nc = len(O.poly_powers(degree, 5 if spatial else 3))
+    co = [0.3 * torch.randn(B, 3, nc, generator=gen) for _ in range(3)]
+    gout = torch.randn(B, 3, H, W, generator=gen)
+    r32 = trispace_fwd_bwd_chunked(img, *co, gout, degree, spatial, clamp, dtype=torch.float32, rows=H)
+    r64 = trispace_fwd_bwd_chunked(img, *co, gout, degree, spatial, clamp, dtype=torch.float64, rows=H)
+    net = curl_b200.TriSpaceRegNet(polynomial_order=degree, spatial=spatial, backbone=nn.Identity()).to(dev)
+    net.save_activations = save
+    x = img.to(dev).requires_grad_(True)
+    cg = [c.to(dev).requires_grad_(True) for c in co]
+    out = net._fused(x, *cg, clamp)
+    out.backward(gout.to(dev))
+    o = out.detach().cpu().numpy()
+    own = float(np.abs(r32["out"] - r64["out"]).max())
+    assert np.abs(o - r64["out"]).max() <= max(3e-5, 3 * own)
+    assert (np.abs(o - r32["out"]) > 2e-5 * np.maximum(1.0, np.abs(r64["out"]))).mean() <= 2e-3
+    for k, c in zip(("gR", "gL", "gH"), cg):
+        e = rel_to_max(c.grad.cpu().numpy(), r64[k])
+        assert e <= max(1e-4, 4 * rel_to_max(r32[k], r64[k])), (k, e)
+    if H * W >= 64:           # the fraction-based criterion needs a few pixels
+        parity.check_trispace_gimg(x.grad.cpu().numpy(), r32["gimg"], r64["gimg"], case)
+    else:
+        scale = np.abs(r64["gimg"]).max()
+        assert np.abs(x.grad.cpu().numpy() - r64["gimg"]).max() <= max(1e-4 * scale, 3 * np.abs(r32["gimg"] - r64["gimg"]).max())
